@@ -1,0 +1,227 @@
+/*
+ * cilqr.h — C ABI of the B200-native CILQR hot path (libcilqr_b200.so).
+ *
+ * This is the drop-in boundary: plain pointers and sizes, no torch / Eigen / ROS types.  Every
+ * entry point names the reference interface it replaces (paths relative to the reference repo
+ * Leo-Liao-Chao/Uncertainty-Aware-CILQR-for-Trajectory-Optimization, directory
+ * CILQR/src/ilqr/include/ilqr/ unless a longer path is given).
+ *
+ * Conventions
+ *   - All solver arrays are FP64 and use the reference's column-major Eigen layouts with the
+ *     batch as the slowest index:  X[b][4*t+s] (4 x (N+1)),  U[b][2*t+c] (2 x N),
+ *     l_x[b][4*t+s], l_xx[b][4*(4*t+c)+r], l_u[b][2*t+c], l_uu[b][2*(2*t+c)+r],
+ *     k[b][2*t+c], K[b][2*(4*t+c)+r]  (Eigen::Tensor<double,3> is column-major).
+ *   - `mem` says where the caller's buffers live: CILQR_MEM_HOST (the library copies to/from the
+ *     device on `stream`, pinned host memory makes those copies asynchronous) or
+ *     CILQR_MEM_DEVICE (pointers are used in place).
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream).
+ *   - Every function returns 0 on success or a negative CILQR_E_* code; cilqr_last_error()
+ *     returns a thread-local message.  There is no CPU fallback: without a usable CUDA device
+ *     every compute entry point fails with CILQR_E_CUDA.
+ */
+#ifndef CILQR_B200_H
+#define CILQR_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CILQR_ABI_VERSION 1
+
+enum { CILQR_MEM_HOST = 0, CILQR_MEM_DEVICE = 1 };
+
+enum {
+    CILQR_OK = 0,
+    CILQR_E_ARG = -1,   /* bad argument (null pointer, size out of range) */
+    CILQR_E_CUDA = -2,  /* CUDA runtime / driver error, or no device */
+    CILQR_E_STATE = -3, /* call order (e.g. solve before set_obstacles with n_obs>0) */
+    CILQR_E_ALLOC = -4
+};
+
+/* Per-scenario termination status written by cilqr_solve_batch (iLQR.cpp:211-239). */
+enum {
+    CILQR_ST_TOLERANCE = 0, /* accepted step with |J_new - J_old| < tolerance  (iLQR.cpp:225) */
+    CILQR_ST_MAX_ITER = 1,  /* max_iterations reached                           (iLQR.cpp:211) */
+    CILQR_ST_LAMB_MAX = 2,  /* lamb > lamb_max after a rejected step            (iLQR.cpp:233) */
+    CILQR_ST_NONFINITE = 3  /* non-finite cost/gains: the reference's EigenSolver failure path (iLQR.cpp:159-162, 214-215) */
+};
+
+/* Line-search merit used when n_alphas > 1 (an extension; the reference has no step size). */
+enum {
+    CILQR_MERIT_TRACKING = 0, /* Constraints::get_J only (Constraints.cpp:534-561) */
+    CILQR_MERIT_TOTAL = 1     /* get_J + w_obstacle * obstacle barriers + control barriers */
+};
+
+/*
+ * POD mirror of class Parameters (Parameters.h:5-92, defaults Parameters.cpp:3-75), plus the two
+ * iLQR constructor constants lamb_factor / lamb_max (iLQR.cpp:17-18).  Members of the reference
+ * class that are never initialised nor read on the hot path (num_obstacle, use_pid, use_mpc,
+ * mpc_horizon, w_guideline) are left out.
+ */
+typedef struct cilqr_params {
+    /* planning */
+    int32_t num_of_local_wpts; /* 20  -> the closest-point polyline has 10*num_of_local_wpts samples */
+    int32_t poly_order;        /* 5   (poly_order <= 7) */
+    double desired_speed;      /* 5.0 */
+    /* iLQR */
+    double timestep;        /* 0.1 */
+    int32_t horizon;        /* 40 in the reference ctor; 50 in every benchmark config */
+    int32_t max_iterations; /* 20 */
+    double tolerance;       /* 1e-4 */
+    int32_t num_states;     /* 4 (fixed) */
+    int32_t num_ctrls;      /* 2 (fixed) */
+    /* cost weights */
+    double w_acc, w_yawrate, w_pos, w_vel, w_obstacle, w_uncertainty;
+    /* barrier q1/q2 */
+    double q1_acc, q2_acc, q1_yawrate, q2_yawrate, q1_front, q2_front, q1_rear, q2_rear;
+    double q1_uncertainty, q2_uncertainty;
+    /* limits */
+    double acc_max, acc_min, steer_angle_min, steer_angle_max;
+    /* ego */
+    double wheelbase, speed_max;
+    double steer_control_max, steer_control_min, throttle_control_max, throttle_control_min;
+    /* obstacle ellipse */
+    double t_safe, s_safe_a, s_safe_b, ego_rad, ego_front, ego_rear;
+    double length, width, safe_length, safe_width;
+    /* iLQR ctor constants (iLQR.cpp:17-18) */
+    double lamb_factor; /* 10 */
+    double lamb_max;    /* 10000 */
+} cilqr_params;
+
+typedef struct cilqr_solver *cilqr_handle;
+
+/* ABI / build introspection. */
+int cilqr_abi_version(void);
+const char *cilqr_last_error(void);
+/* Number of kernel launches issued by this library since load (bench.py's gpu_launches). */
+int64_t cilqr_launch_count(void);
+
+/* Parameters::Parameters()  (Parameters.cpp:3-75) + iLQR ctor constants (iLQR.cpp:17-18). */
+int cilqr_params_default(cilqr_params *p);
+
+/* iLQR::iLQR(const Parameters&) (iLQR.cpp:3-19): allocates device workspaces for up to
+ * max_batch scenarios with up to max_obs obstacles each. */
+int cilqr_create(const cilqr_params *p, int max_batch, int max_obs, cilqr_handle *out);
+int cilqr_destroy(cilqr_handle h);
+
+/* The constructor's initial control sequence (iLQR.cpp:9-15): acc = 0.5, yaw-rate = 0 for
+ * t < N/2 and 0.1 afterwards.  Pure host helper: fills U[2*N]. */
+int cilqr_default_controls(const cilqr_params *p, double *U);
+
+/*
+ * iLQR::set_Obstacle(std::vector<Obstacle>) (iLQR.cpp:20-23) with
+ * Obstacle(Parameters, dimension 2xN, relative_pos_array 4xN) (Obstacle.cpp:8-13).
+ *   dim [B][n_obs][2*N]   per-timestep (length, width)
+ *   pos [B][n_obs][4*N]   per-timestep (x, y, v, theta)
+ * n_obs = 0 is iLQR::clear_Obstacle() (iLQR.cpp:24-27).
+ */
+int cilqr_set_obstacles(cilqr_handle h, int B, int n_obs, const double *dim, const double *pos,
+                        int mem, void *stream);
+
+/*
+ * Compact "Gaussian-uncertain, constant-velocity" obstacle input (extension).
+ * The device generates what the host would hand to Obstacle():
+ *   pos(:,i) = (x0 + v cos(th) i dt, y0 + v sin(th) i dt, v, th)
+ *   dim(0,i) = L + 2 kappa sigma_x,   dim(1,i) = W + 2 kappa sqrt(sigma_y^2 + sigma_th^2 (v i dt)^2)
+ * (lever-arm covariance propagation of map_engine/include/ARBIT.cuh:58-68, kappa = 2.4477 at
+ * ARBIT.cuh:87).
+ *   state0 [B][n_obs][4] (x0, y0, v, theta);  LW [B][n_obs][2];  sigma [B][n_obs][3] (sx, sy, sth)
+ */
+int cilqr_set_obstacles_cv(cilqr_handle h, int B, int n_obs, const double *state0, const double *LW,
+                           const double *sigma, double kappa, int mem, void *stream);
+
+/*
+ * iLQR::get_optimal_control_seq (iLQR.cpp:201-245) for B independent scenarios.
+ *   x0     [B][4]          in      ego state (x, y, v, theta)
+ *   U      [B][2*N]        in/out  warm start in, optimal controls out (control_seq / U_result)
+ *   poly   [B][poly_order+1] in    local-plan polynomial coefficients, ascending powers (poly_order <= 7)
+ *   xlp    [B][2]          in      first and last x of the local plan (the only two entries of
+ *                                  x_local_plan that Constraints.cpp:31-33 reads)
+ *   n_alphas                        1 = reference semantics (full step, one-iteration-lagged accept
+ *                                  test); 2..8 = concurrent line search over alpha = 2^-a
+ *   merit                           CILQR_MERIT_* (only used when n_alphas > 1)
+ *   X      [B][4*(N+1)]    out     X_result
+ *   J      [B]             out     Constraints::get_J(X_result, U_result)
+ *   iters  [B]             out     loop iterations the reference would have run ("Iteration times")
+ *   status [B]             out     CILQR_ST_*
+ * X, J, iters, status may be NULL.
+ */
+int cilqr_solve_batch(cilqr_handle h, int B, const double *x0, double *U, const double *poly,
+                      const double *xlp, int n_alphas, int merit, double *X, double *J,
+                      int32_t *iters, int32_t *status, int mem, void *stream);
+
+/* ---- stage entry points (used by the parity tests; same device code as the fused solve) ---- */
+
+/* iLQR::get_nominal_trajectory (iLQR.cpp:51-62) over Model::forward_simulate (Model.cpp:17-30). */
+int cilqr_rollout(cilqr_handle h, int B, const double *x0, const double *U, double *X, int mem,
+                  void *stream);
+/* Constraints::get_state_cost (Constraints.cpp:145-227) incl. Obstacle::get_obstalce_cost
+ * (Obstacle.cpp:39-112) and find_closest_point (Constraints.cpp:24-59). */
+int cilqr_state_cost(cilqr_handle h, int B, const double *X, const double *poly, const double *xlp,
+                     double *l_x, double *l_xx, int mem, void *stream);
+/* Constraints::get_control_cost (Constraints.cpp:86-137). */
+int cilqr_control_cost(cilqr_handle h, int B, const double *X, const double *U, double *l_u,
+                       double *l_uu, int mem, void *stream);
+/* Constraints::get_J (Constraints.cpp:534-561). */
+int cilqr_cost(cilqr_handle h, int B, const double *X, const double *U, const double *poly,
+               const double *xlp, double *J, int mem, void *stream);
+/* iLQR::backward_pass (iLQR.cpp:91-195): gains k (2xN), K (2x4xN); ok[b]=0 mirrors `return false`. */
+int cilqr_backward(cilqr_handle h, int B, const double *X, const double *U, const double *poly,
+                   const double *xlp, const double *lamb /*[B]*/, double *k, double *K, int32_t *ok,
+                   int mem, void *stream);
+/* iLQR::forward_pass (iLQR.cpp:68-86) with step size alpha[b] on the feed-forward term
+ * (alpha = 1 is the reference). */
+int cilqr_forward(cilqr_handle h, int B, const double *X, const double *U, const double *k,
+                  const double *K, const double *alpha /*[B] or NULL*/, double *X_new, double *U_new,
+                  int mem, void *stream);
+
+/* ---- costmap (map_engine) ---- */
+
+/* grid_map::GridMap geometry after setGeometry() (grid_map_core/src/GridMap.cpp:45-62):
+ * size = round(length/resolution), length := size*resolution, startIndex = 0. */
+typedef struct costmap_geom {
+    double length_x, length_y; /* requested lengths [m] (rounded to whole cells like setGeometry) */
+    double resolution;         /* [m/cell] */
+    double pos_x, pos_y;       /* map centre in its parent frame */
+} costmap_geom;
+
+/* Host helper: rows/cols that setGeometry() would produce. */
+int costmap_geom_size(const costmap_geom *g, int32_t *rows, int32_t *cols);
+
+/*
+ * The ego-frame warp loop of LocalCostmap::odomCallback
+ * (CILQR/src/map_engine/src/local_costmap.cpp:242-264) for P ego poses at once.
+ *   src    [rows_s*cols_s] float, column-major like grid_map's Matrix (index0 fastest)
+ *   poses  [P][4] = (Vx, Vy, sin(theta), cos(theta)) -- sin/cos computed by the caller with libm,
+ *          exactly as local_costmap.cpp:201-202 does
+ *   bbox   NULL or [P][rows_t*cols_t] float "bounding_box_map" overlay (value > 90 wins, :260-263)
+ *   out    [P][rows_t*cols_t] float
+ *   idx    NULL or [P][rows_t*cols_t] int32: linear source index g0 + rows_s*g1, -1 when the cell
+ *          falls outside the source map (the reference throws std::out_of_range there,
+ *          grid_map_core/src/GridMap.cpp:160-166; this library writes NaN / -1 instead)
+ *   variant 0 = automatic, 1 = direct gather kernel, 2 = TMA-staged tile kernel
+ */
+int costmap_warp_batch(const float *src, const costmap_geom *src_geom, const costmap_geom *tgt_geom,
+                       const double *poses, int P, const float *bbox, float *out, int32_t *idx,
+                       int variant, int mem, void *stream);
+
+/*
+ * thrust_propagateUncertainty (CILQR/src/map_engine/include/ARBIT.cuh:109,
+ * src/arbitrary_transformation.cu:8-157; CPU twin local_costmap.cpp:517-648) fused into one kernel:
+ * per cell pose-sigma -> cell covariance -> 95% ellipse -> Gaussian-weighted mean of `map`.
+ *   map    [rows*cols] float (the "vehicle_map" layer), geometry `geom`
+ *   index  first linear cell processed (the reference's `index` argument)
+ *   count  [rows*cols - index] int32   cells visited by the ellipse iterator
+ *   value  [rows*cols - index] double  numerator / denominator
+ */
+int costmap_propagate_uncertainty(const float *map, const costmap_geom *geom, double sin_theta,
+                                  double cos_theta, double sigma_x, double sigma_y,
+                                  double sigma_theta, int index, int32_t *count, double *value,
+                                  int mem, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CILQR_B200_H */
