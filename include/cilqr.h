@@ -94,6 +94,9 @@ typedef struct cilqr_solver *cilqr_handle;
 
 /* ABI / build introspection. */
 int cilqr_abi_version(void);
+/* sizeof(cilqr_params) / sizeof(costmap_geom) as this library was compiled (binding sanity check). */
+int cilqr_sizeof_params(void);
+int cilqr_sizeof_geom(void);
 const char *cilqr_last_error(void);
 /* Number of kernel launches issued by this library since load (bench.py's gpu_launches). */
 int64_t cilqr_launch_count(void);

@@ -301,17 +301,28 @@ double oracle_cost(const cilqr_params *p, const double *X, const double *U, cons
 static double merit_poly(const cilqr_params *p, int merit, int n_obs, const double *dim, const double *pos, const double *X,
                          const double *U, int S, const double *xs, const double *ys)
 {
-    double J = cost_poly(p, X, U, S, xs, ys);
-    if (merit == CILQR_MERIT_TOTAL) {
-        int N = p->horizon;
-        double b = 0.0, bc = 0.0;
-        for (int t = 0; t < N; ++t)
-            for (int j = 0; j < n_obs; ++j) {
-                double g[2] = {0, 0}, H[3] = {0, 0, 0};
-                obstacle_terms(p, dim + (size_t)j * 2 * N + 2 * t, pos + (size_t)j * 4 * N + 4 * t, X + NS * t, g, H, &b);
-            }
-        oracle_control_cost_b(p, X, U, NULL, NULL, &bc);
-        J += p->w_obstacle * b + bc;
+    if (merit != CILQR_MERIT_TOTAL)
+        return cost_poly(p, X, U, S, xs, ys);
+    /* per step: (x_cost + u_cost) + (w_obstacle * sum_obs(b_front + b_rear) + sum of the 4 control barriers) */
+    int N = p->horizon;
+    double tmax = tan(p->steer_angle_max), tmin = tan(p->steer_angle_min);
+    double J = 0;
+    for (int t = 0; t < N; ++t) {
+        const double *x = X + NS * t;
+        int ci = closest_index(S, xs, ys, x[0], x[1]);
+        double d0 = x[0] - xs[ci], d1 = x[1] - ys[ci], d2 = x[2] - p->desired_speed;
+        double a = U[2 * t], w = U[2 * t + 1];
+        double x_cost = d0 * p->w_pos * d0 + d1 * p->w_pos * d1 + d2 * p->w_vel * d2;
+        double u_cost = a * p->w_acc * a + w * p->w_yawrate * w;
+        double bo = 0.0;
+        for (int j = 0; j < n_obs; ++j) {
+            double g[2] = {0, 0}, H[3] = {0, 0, 0};
+            obstacle_terms(p, dim + (size_t)j * 2 * N + 2 * t, pos + (size_t)j * 4 * N + 4 * t, x, g, H, &bo);
+        }
+        double e1 = p->q1_acc * exp(p->q2_acc * (a - p->acc_max)), e2 = p->q1_acc * exp(p->q2_acc * (p->acc_min - a));
+        double e3 = p->q1_yawrate * exp(p->q2_yawrate * (w - x[2] * tmax / p->wheelbase));
+        double e4 = p->q1_yawrate * exp(p->q2_yawrate * (x[2] * tmin / p->wheelbase - w));
+        J += (x_cost + u_cost) + (p->w_obstacle * bo + (e1 + e2 + e3 + e4));
     }
     return J;
 }

@@ -1,0 +1,96 @@
+"""CPU-only host logic: seeded scenario generator, rank sharding, the LocalPlanner restatement against the
+reference's golden output, and the world-size-2 gather over gloo."""
+import os
+import subprocess
+import sys
+
+import numpy as np
+
+import cilqr_b200
+from cilqr_b200 import scenarios, dist
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+
+
+def test_scenarios_are_independent_of_batching(port):
+    p = port.params_default(horizon=50)
+    a = scenarios.make_scenarios(p, 0, 16, 5, curved=True)
+    b = scenarios.make_scenarios(p, 8, 4, 5, curved=True)
+    for k in ("x0", "poly", "xlp", "obs_state0", "dim", "pos"):
+        assert np.array_equal(a[k][8:12], b[k])
+    assert a["x0"][:, 0].min() >= 0 and a["x0"][:, 0].max() < 2 and a["x0"][:, 2].min() >= 2 and a["x0"][:, 2].max() < 6
+    assert a["obs_state0"][..., 0].min() >= 6 and a["obs_state0"][..., 0].max() < 30
+    assert a["dim"].shape == (16, 5, 100) and a["pos"].shape == (16, 5, 200)
+    # covariance inflation: width grows along the horizon, length does not
+    assert np.all(np.diff(a["dim"][0, 0, 1::2]) >= 0) and np.all(a["dim"][0, 0, 0::2] == a["dim"][0, 0, 0])
+    assert np.isclose(a["dim"][0, 0, 0], p.length + 2 * scenarios.KAPPA * 0.16)
+
+
+def test_shard_range_partitions_contiguously():
+    for total, world in [(65536, 8), (10, 3), (7, 8), (4096, 2), (1, 1)]:
+        spans = [dist.shard_range(total, r, world) for r in range(world)]
+        assert spans[0][0] == 0 and spans[-1][1] == total
+        assert all(spans[i][1] == spans[i + 1][0] for i in range(world - 1))
+        sizes = [hi - lo for lo, hi in spans]
+        assert max(sizes) - min(sizes) <= 1
+
+
+def test_local_planner_matches_reference_golden(port):
+    g = np.load(os.path.join(HERE, "golden", "solver_golden.npz"))
+    p = port.params_default(horizon=50)
+    lp = cilqr_b200.LocalPlanner(p)
+    lp.set_global_planner(np.stack([np.arange(200, dtype=np.float64), np.zeros(200)], axis=1))
+    poly, xlp, _ = lp.plan_batch(np.array([[0.3, 0.2, 4.0, 0.01]]))
+    assert np.array_equal(xlp[0], g["run_step/xlp"])
+    xs = np.linspace(xlp[0, 0], xlp[0, 1], 50)
+    y_mine = sum(poly[0, j] * xs ** j for j in range(6))
+    y_ref = sum(g["run_step/poly"][j] * xs ** j for j in range(6))
+    assert np.max(np.abs(y_mine - y_ref)) < 1e-9
+    # a curved plan: coefficients agree to rounding because the same pivoted Householder QR is used
+    t = np.arange(200, dtype=np.float64) * 0.9
+    lp.set_global_planner(np.stack([t, 0.002 * t ** 2], axis=1))
+    poly2, xlp2, _ = lp.plan_batch(np.array([[5.2, 0.4, 3.0, 0.05]]))
+    assert np.array_equal(xlp2[0], g["local_plan_curved/xlp"])
+    xs = np.linspace(xlp2[0, 0], xlp2[0, 1], 50)
+    y_mine = sum(poly2[0, j] * xs ** j for j in range(6))
+    y_ref = sum(g["local_plan_curved/poly"][j] * xs ** j for j in range(6))
+    assert np.max(np.abs(y_mine - y_ref)) < 1e-9 * max(1.0, np.max(np.abs(y_ref)))
+
+
+_GLOO = r"""
+import os, sys
+sys.path.insert(0, %r)
+import numpy as np, torch, torch.distributed as td
+import cilqr_b200
+from cilqr_b200 import dist, scenarios
+import oracle
+rank, local, world = dist.init_process_group("gloo")
+port = oracle.PortOracle()
+p = port.params_default(horizon=50)
+TOTAL = 6
+lo, hi = dist.shard_range(TOTAL, rank, world)
+sc = scenarios.make_scenarios(p, lo, hi - lo, 2)
+# each rank solves its shard (the CPU checker stands in for the GPU here: this test is about the
+# sharding + gather plumbing, which is identical on NCCL)
+r = port.solve_batch(p, hi - lo, 2, sc["dim"], sc["pos"], sc["x0"], sc["U0"], sc["poly"], sc["xlp"], threads=1)
+U = dist.gather_trajectories(torch.from_numpy(r["U"]), counts=[h - l for l, h in (dist.shard_range(TOTAL, q, world) for q in range(world))])
+if rank == 0:
+    full = scenarios.make_scenarios(p, 0, TOTAL, 2)
+    want = port.solve_batch(p, TOTAL, 2, full["dim"], full["pos"], full["x0"], full["U0"], full["poly"], full["xlp"], threads=1)["U"]
+    assert U.shape == (TOTAL, 100), U.shape
+    assert np.array_equal(U.numpy(), want), "sharded + gathered result differs from the unsharded solve"
+    print("GLOO_OK")
+td.barrier()
+td.destroy_process_group()
+"""
+
+
+def test_world_size_2_shard_and_gather_over_gloo(tmp_path, port):
+    script = tmp_path / "gloo_job.py"
+    script.write_text(_GLOO % ROOT)
+    env = dict(os.environ, MASTER_ADDR="127.0.0.1", OMP_NUM_THREADS="1")
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+                        "--master-port", "29611", str(script)], capture_output=True, text=True, env=env, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert "GLOO_OK" in r.stdout

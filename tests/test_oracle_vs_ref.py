@@ -1,0 +1,71 @@
+"""Pins the plain-C restatement against the compiled reference on fresh seeded inputs (skipped where
+oracle/_ref could not be built, i.e. never in this container).  CPU only."""
+import numpy as np
+import pytest
+
+import cilqr_b200
+from cilqr_b200 import scenarios
+
+
+def rel(a, b):
+    a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
+    return float(np.max(np.abs(a - b)) / max(np.max(np.abs(b)), 1e-300))
+
+
+@pytest.mark.parametrize("n_obs,curved", [(0, False), (3, True), (20, False)])
+def test_full_solves(ref, port, n_obs, curved):
+    p = ref.params_default(horizon=50)
+    B = 6
+    sc = scenarios.make_scenarios(p, 1000, B, n_obs, curved=curved)
+    for b in range(B):
+        dim = sc["dim"][b] if n_obs else None
+        pos = sc["pos"][b] if n_obs else None
+        r = ref.solve(p, dim, pos, sc["x0"][b], sc["U0"][b], sc["poly"][b], sc["xlp"][b])
+        o = port.solve(p, dim, pos, sc["x0"][b], sc["U0"][b], sc["poly"][b], sc["xlp"][b])
+        assert r["iters"] == o["iters"]
+        assert rel(o["U"], r["U"]) < 1e-9 and rel(o["X"], r["X"]) < 1e-9 and abs(o["J"] - r["J"]) < 1e-9 * abs(r["J"])
+
+
+def test_stage_functions_on_random_states(ref, port):
+    p = ref.params_default(horizon=50)
+    rng = np.random.default_rng(7)
+    sc = scenarios.make_scenarios(p, 2000, 4, 5, curved=True)
+    for b in range(4):
+        U = sc["U0"][b] + rng.normal(0, 0.3, 100)
+        X = ref.rollout(p, sc["x0"][b], U)
+        assert rel(port.rollout(p, sc["x0"][b], U), X) < 1e-13
+        a, c = ref.state_cost(p, sc["dim"][b], sc["pos"][b], X, sc["poly"][b], sc["xlp"][b]), port.state_cost(p, sc["dim"][b], sc["pos"][b], X, sc["poly"][b], sc["xlp"][b])
+        assert rel(c[0], a[0]) < 1e-12 and rel(c[1], a[1]) < 1e-12
+        a, c = ref.control_cost(p, X, U), port.control_cost(p, X, U)
+        assert rel(c[0], a[0]) < 1e-13 and rel(c[1], a[1]) < 1e-13
+        for lamb in (1.0, 1e-6, 1e3):
+            ok_r, k_r, K_r = ref.backward(p, sc["dim"][b], sc["pos"][b], X, U, sc["poly"][b], sc["xlp"][b], lamb)
+            ok_o, k_o, K_o = port.backward(p, sc["dim"][b], sc["pos"][b], X, U, sc["poly"][b], sc["xlp"][b], lamb)
+            assert ok_r == ok_o == 1 and rel(k_o, k_r) < 1e-10 and rel(K_o, K_r) < 1e-10
+        pt_r = ref.closest_point(p, X[8:12], sc["poly"][b], sc["xlp"][b])
+        assert np.allclose(port.closest_point(p, X[8:12], sc["poly"][b], sc["xlp"][b]), pt_r, rtol=0, atol=1e-13)
+        vx_r, mx_r = ref.obstacle_cost(p, sc["dim"][b][0], sc["pos"][b][0], 7, X[28:32])
+        vx_o, mx_o = port.obstacle_cost(p, sc["dim"][b][0], sc["pos"][b][0], 7, X[28:32])
+        assert rel(vx_o, vx_r) < 1e-12 and rel(mx_o, mx_r) < 1e-12
+
+
+def test_warp_index_maps_bit_exact(ref, port):
+    G = cilqr_b200.CostmapGeom
+    sg, tg = G(40.0, 30.2, 0.2, 10.0, -5.0), G(12.0, 9.0, 0.2, 2.0, 0.0)
+    rs, cs = ref.geom_size(sg)
+    assert (rs, cs) == port.geom_size(sg)
+    src = scenarios.make_source_map(rs, cs)
+    poses = scenarios.make_poses(24, (10.0, -5.0), 16.0)
+    rt, ct = ref.geom_size(tg)
+    bbox = np.where(np.random.default_rng(3).random((24, rt * ct)) > 0.97, 100.0, 0.0).astype(np.float32)
+    v_r, i_r = ref.warp(src, sg, tg, poses, bbox=bbox)
+    v_o, i_o = port.warp(src, sg, tg, poses, bbox=bbox)
+    assert np.array_equal(i_r, i_o) and np.array_equal(v_r.view(np.uint32), v_o.view(np.uint32))
+    assert (i_r < 0).any() and (i_r >= 0).any()
+
+
+def test_expand_obstacles_matches_numpy_generator(port):
+    p = port.params_default(horizon=50)
+    sc = scenarios.make_scenarios(p, 5, 3, 4)
+    dim, pos = port.expand_obstacles_cv(p, sc["obs_state0"][1], sc["obs_LW"][1], sc["obs_sigma"][1], sc["kappa"])
+    assert rel(dim, sc["dim"][1]) < 1e-15 and rel(pos, sc["pos"][1]) < 1e-15

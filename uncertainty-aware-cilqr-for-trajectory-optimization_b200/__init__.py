@@ -1,14 +1,8 @@
-"""B200-native CILQR hot path.  Host-side mirror of the reference's solver interface
-over the C ABI of include/cilqr.h; the CUDA library is loaded lazily and there is no CPU path."""
-from .params import Parameters, CostmapGeom, MEM_HOST, MEM_DEVICE  # noqa: F401
-from . import scenarios  # noqa: F401
-
-
-def __getattr__(name):  # lazy: importing the package must work on a box with no GPU and no built .so
-    if name in ("iLQR", "Obstacle", "Constraints", "Model", "load_library", "LibraryMissing"):
-        from . import solver
-        return getattr(solver, name)
-    if name in ("warp_batch", "propagate_uncertainty", "LocalCostmap"):
-        from . import costmap
-        return getattr(costmap, name)
-    raise AttributeError(name)
+"""B200-native CILQR hot path.  Host-side mirror of the reference's solver / costmap
+interface over the C ABI of include/cilqr.h.  Importing the package needs neither a GPU nor the built
+library; the first compute call dlopens libcilqr_b200.so and raises if it is missing — there is no CPU path."""
+from . import params, scenarios, solver, costmap, local_planner, dist  # noqa: F401
+from .params import Parameters, CostmapGeom, MEM_HOST, MEM_DEVICE, MERIT_TRACKING, MERIT_TOTAL  # noqa: F401
+from .solver import iLQR, Obstacle, load_library, LibraryMissing, CilqrError, launch_count  # noqa: F401
+from .costmap import warp_batch, propagate_uncertainty, geom_size  # noqa: F401
+from .local_planner import LocalPlanner  # noqa: F401

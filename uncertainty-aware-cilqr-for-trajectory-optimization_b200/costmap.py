@@ -1,0 +1,66 @@
+"""Host-side wrappers of the costmap entry points of include/cilqr.h (map_engine side of the hot path).
+
+`warp_batch` replaces the per-cell loop of LocalCostmap::odomCallback
+(CILQR/src/map_engine/src/local_costmap.cpp:242-264); `propagate_uncertainty` replaces
+thrust_propagateUncertainty (CILQR/src/map_engine/include/ARBIT.cuh:109,
+src/arbitrary_transformation.cu:8-157).  Maps are flat float32 arrays in grid_map's column-major order.
+"""
+import ctypes as C
+
+import numpy as np
+
+from .params import CostmapGeom, MEM_HOST, MEM_DEVICE
+from .solver import load_library, _check, _Arg
+
+VARIANT_AUTO, VARIANT_DIRECT, VARIANT_TMA = 0, 1, 2
+
+
+def geom_size(geom):
+    lib = load_library()
+    r, c = C.c_int32(0), C.c_int32(0)
+    _check(lib.costmap_geom_size(C.byref(geom), C.byref(r), C.byref(c)))
+    return r.value, c.value
+
+
+def warp_batch(src, src_geom, tgt_geom, poses, bbox=None, want_idx=True, variant=VARIANT_AUTO, out=None, idx=None):
+    """src: flat source layer; poses [P,4] = (Vx, Vy, sin, cos) with sin/cos from the caller's libm
+    (local_costmap.cpp:201-202).  Returns (out [P, rows*cols] float32, idx [P, rows*cols] int32 or None)."""
+    lib = load_library()
+    a = _Arg()
+    ps = a.inp(src, np.float32)
+    pp = a.inp(poses)
+    P = int(poses.shape[0])
+    pb = a.inp(bbox, np.float32) if bbox is not None else None
+    rt, ct = geom_size(tgt_geom)
+    dev = a.mem == MEM_DEVICE
+    d = getattr(src, "device", None)
+    if out is None:
+        out, po = a.out((P, rt * ct), np.float32, dev, d)
+    else:
+        po = a.inp(out, np.float32) if dev else C.c_void_p(out.ctypes.data)
+    pi = None
+    if idx is not None:
+        pi = a.inp(idx, np.int32) if dev else C.c_void_p(idx.ctypes.data)
+    elif want_idx:
+        idx, pi = a.out((P, rt * ct), np.int32, dev, d)
+    _check(lib.costmap_warp_batch(ps, C.byref(src_geom), C.byref(tgt_geom), pp, C.c_int(P), pb, po, pi, C.c_int(variant),
+                                  C.c_int(a.mem), a.stream_ptr()))
+    return out, idx
+
+
+def propagate_uncertainty(vmap, geom, sin_theta, cos_theta, sigma_x, sigma_y, sigma_theta, index=0):
+    """Returns (count int32 [cells-index], value float64 [cells-index]) — the vector<pair<int,double>> of
+    thrust_propagateUncertainty."""
+    lib = load_library()
+    a = _Arg()
+    pm = a.inp(vmap, np.float32)
+    r, c = geom_size(geom)
+    n = r * c - int(index)
+    dev = a.mem == MEM_DEVICE
+    d = getattr(vmap, "device", None)
+    count, pc = a.out((n,), np.int32, dev, d)
+    value, pv = a.out((n,), np.float64, dev, d)
+    _check(lib.costmap_propagate_uncertainty(pm, C.byref(geom), C.c_double(sin_theta), C.c_double(cos_theta), C.c_double(sigma_x),
+                                             C.c_double(sigma_y), C.c_double(sigma_theta), C.c_int(index), pc, pv, C.c_int(a.mem),
+                                             a.stream_ptr()))
+    return count, value

@@ -1,0 +1,760 @@
+// cilqr_solver.cu — kernels and C ABI of the batched CILQR solver (include/cilqr.h), sm_100a.
+//
+// Kernels
+//   prep_obstacles_dense_kernel / prep_obstacles_cv_kernel : Obstacle ctor inputs -> per-(obstacle, t) records
+//       (x, y, cos, sin, 1/a^2, 1/b^2), Obstacle.cpp:39-48;  the _cv variant also does the covariance-inflated
+//       constant-velocity expansion on the device.
+//   solve_kernel<LS> : the fused driver iLQR::get_optimal_control_seq (iLQR.cpp:201-245), one warp per scenario,
+//       persistent CTAs pulling scenario indices from a global counter.
+//   stage_kernel     : the individual reference stages behind cilqr_rollout / _state_cost / _control_cost /
+//       _cost / _backward / _forward (same device functions as the fused kernel; used by the parity tests).
+#include "common.cuh"
+#include "cilqr_device.cuh"
+#include <cfloat>
+#include <cmath>
+#include <cstring>
+#include <new>
+
+namespace cilqr
+{
+thread_local char g_err[512] = "";
+std::atomic<long long> g_launches{0};
+
+// ------------------------------------------------------------------------------------------------- obstacle prep
+__device__ __forceinline__ void write_obstacle_record(const DevParams &P, double *__restrict__ out, size_t bj, int t, double xo, double yo,
+                                                      double vo, double tho, double dim0, double dim1)
+{
+    double so, co;
+    sincos(tho, &so, &co);
+    const double a = dim0 / 2.0 + fabs(vo * co) * P.t_safe + P.s_safe_a + P.ego_rad;       // Obstacle.cpp:42
+    const double b = dim1 / 2.0 + fabs(vo * so) * P.t_safe + P.s_safe_b + P.ego_rad + 1.0; // Obstacle.cpp:43 (hard-coded +1)
+    double *o = out + bj * OB_FIELDS * P.N + t;
+    o[OB_X * P.N] = xo;
+    o[OB_Y * P.N] = yo;
+    o[OB_C * P.N] = co;
+    o[OB_S * P.N] = so;
+    o[OB_IA2 * P.N] = 1.0 / a / a; // Obstacle.cpp:45
+    o[OB_IB2 * P.N] = 1.0 / b / b; // Obstacle.cpp:46
+}
+
+__global__ void prep_obstacles_dense_kernel(DevParams P, size_t n_bj, const double *__restrict__ dim, const double *__restrict__ pos,
+                                            double *__restrict__ out)
+{
+    const size_t total = n_bj * P.N;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        const size_t bj = i / P.N;
+        const int t = (int)(i - bj * P.N);
+        const double *d = dim + 2 * i, *q = pos + 4 * i; // Obstacle's dimension (2xN) / relative_pos_array (4xN) columns
+        write_obstacle_record(P, out, bj, t, q[0], q[1], q[2], q[3], d[0], d[1]);
+    }
+}
+
+__global__ void prep_obstacles_cv_kernel(DevParams P, size_t n_bj, const double *__restrict__ state0, const double *__restrict__ LW,
+                                         const double *__restrict__ sigma, double kappa, double *__restrict__ out)
+{
+    const size_t total = n_bj * P.N;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        const size_t bj = i / P.N;
+        const int t = (int)(i - bj * P.N);
+        const double x0 = state0[4 * bj], y0 = state0[4 * bj + 1], v = state0[4 * bj + 2], th = state0[4 * bj + 3];
+        const double sx = sigma[3 * bj], sy = sigma[3 * bj + 1], sth = sigma[3 * bj + 2];
+        double s, c;
+        sincos(th, &s, &c);
+        const double tt = t * P.dt, arm = v * tt;
+        const double dim0 = LW[2 * bj] + 2.0 * kappa * sx;
+        const double dim1 = LW[2 * bj + 1] + 2.0 * kappa * sqrt(sy * sy + sth * sth * arm * arm);
+        write_obstacle_record(P, out, bj, t, x0 + v * c * tt, y0 + v * s * tt, v, th, dim0, dim1);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------- fused solve
+struct SolveArgs {
+    DevParams P;
+    int B, n_obs, n_alphas, merit;
+    const double *x0, *poly, *xlp, *obs;
+    double *U, *X, *J, *scratch;
+    int32_t *iters, *status;
+    int *counter;
+};
+
+__device__ __forceinline__ void load_controls(const WarpSmem &W, const double *__restrict__ Ug, int N, int lane)
+{
+    for (int i = lane; i < 2 * N; i += 32)
+        W.U[(i & 1) * N + (i >> 1)] = Ug[i];
+}
+__device__ __forceinline__ void store_controls(const WarpSmem &W, double *__restrict__ Ug, int N, int lane)
+{
+    for (int i = lane; i < 2 * N; i += 32)
+        Ug[i] = W.U[(i & 1) * N + (i >> 1)];
+}
+__device__ __forceinline__ void load_states(const WarpSmem &W, const double *__restrict__ Xg, int N, int lane, bool with_cs)
+{
+    for (int i = lane; i < 4 * (N + 1); i += 32)
+        W.X[(i & 3) * (N + 1) + (i >> 2)] = Xg[i];
+    if (with_cs)
+        for (int t = lane; t <= N; t += 32) {
+            double s, c;
+            sincos(Xg[4 * t + 3], &s, &c);
+            W.cs(0, t) = c;
+            W.cs(1, t) = s;
+        }
+}
+__device__ __forceinline__ void store_states(const WarpSmem &W, double *__restrict__ Xg, int N, int lane)
+{
+    for (int i = lane; i < 4 * (N + 1); i += 32)
+        Xg[i] = W.X[(i & 3) * (N + 1) + (i >> 2)];
+}
+
+template <bool LS>
+__global__ void __launch_bounds__(kWarpsPerBlock * 32, 4) solve_kernel(const SolveArgs A)
+{
+    extern __shared__ double smem[];
+    const DevParams &P = A.P;
+    const int N = P.N;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const WarpSmem W = carve(smem + (size_t)warp * warp_smem_doubles(N, P.S), N, P.S);
+    double *cand = LS ? A.scratch + (size_t)(blockIdx.x * kWarpsPerBlock + warp) * A.n_alphas * traj_doubles(N) : nullptr;
+    const bool merit_total = A.merit == CILQR_MERIT_TOTAL;
+
+    for (;;) {
+        int b = 0;
+        if (lane == 0)
+            b = atomicAdd(A.counter, 1);
+        b = __shfl_sync(0xffffffffu, b, 0);
+        if (b >= A.B)
+            break;
+
+        Polyline pl;
+        pl.x_first = A.xlp[2 * b];
+        pl.dxs = (A.xlp[2 * b + 1] - A.xlp[2 * b]) / P.S; // Constraints.cpp:32
+        build_polyline(P, A.poly + (size_t)b * P.npoly, pl, W.Y, lane);
+        load_controls(W, A.U + (size_t)b * 2 * N, N, lane);
+        if (lane < 4)
+            W.X[lane * (N + 1)] = A.x0[4 * (size_t)b + lane];
+        __syncwarp();
+        phase_rollout(P, W, lane); // X = get_nominal_trajectory(x_0, U)   (iLQR.cpp:203)
+        const double *obs = A.obs + (size_t)b * A.n_obs * OB_FIELDS * N;
+
+        double lamb = 1.0;
+        int iters = 0, status = CILQR_ST_MAX_ITER;
+        if (!LS) {
+            // Reference semantics (iLQR.cpp:211-239).  J_new is the cost of the CURRENT nominal (:217), so the
+            // accept test is known before the candidate is rolled out: accepted -> the in-place rollout IS
+            // `X = X_new; U = U_new`; rejected -> the nominal never changes again, every later iteration
+            // rejects too (same J), so only lamb and the iteration counter advance.
+            double J_old = DBL_MAX;
+            for (int it = 0; it < P.max_iter; ++it) {
+                iters = it + 1;
+                phase_derivs<true>(P, W, pl, obs, A.n_obs, false, lane);
+                const double J_new = sum_sequential(W.Jt, N);
+                if (!(J_new < J_old)) {
+                    lamb = lamb * P.lamb_factor;
+                    for (;;) {
+                        if (lamb > P.lamb_max) { status = CILQR_ST_LAMB_MAX; break; }
+                        if (iters >= P.max_iter) { status = CILQR_ST_MAX_ITER; break; }
+                        ++iters;
+                        lamb = lamb * P.lamb_factor;
+                    }
+                    break;
+                }
+                const bool converged = fabs(J_new - J_old) < P.tol;
+                if (!phase_backward(P, W, lamb, lane)) { status = CILQR_ST_NONFINITE; break; }
+                phase_forward_inplace(P, W, lane);
+                lamb = lamb / P.lamb_factor;
+                if (converged) { status = CILQR_ST_TOLERANCE; break; }
+                J_old = J_new;
+            }
+        } else {
+            // Line-search extension: all alphas rolled out concurrently, warp vote picks the largest that improves.
+            double J_cur = 0.0;
+            for (int it = 0; it < P.max_iter; ++it) {
+                iters = it + 1;
+                phase_derivs<true>(P, W, pl, obs, A.n_obs, merit_total && it == 0, lane);
+                if (it == 0)
+                    J_cur = sum_sequential(W.Jt, N);
+                if (!phase_backward(P, W, lamb, lane)) { status = CILQR_ST_NONFINITE; break; }
+                phase_forward_candidates(P, W, cand, A.n_alphas, nullptr, lane);
+                phase_candidate_merits(P, W, pl, cand, A.n_alphas, obs, A.n_obs, merit_total, W.R, lane);
+                const double Ja = lane < A.n_alphas ? sum_sequential(W.R + lane * N, N) : 0.0;
+                const unsigned ok = __ballot_sync(0xffffffffu, lane < A.n_alphas && Ja < J_cur);
+                if (ok) {
+                    const int a = __ffs(ok) - 1;
+                    const double Jw = __shfl_sync(0xffffffffu, Ja, a);
+                    const double *win = cand + (size_t)a * traj_doubles(N);
+                    for (int i = lane; i < traj_doubles(N); i += 32)
+                        W.X[i] = win[i]; // X, U, CS are contiguous in both layouts
+                    __syncwarp();
+                    const double dJ = J_cur - Jw;
+                    J_cur = Jw;
+                    lamb = lamb / P.lamb_factor;
+                    if (fabs(dJ) < P.tol) { status = CILQR_ST_TOLERANCE; break; }
+                } else {
+                    lamb = lamb * P.lamb_factor;
+                    if (lamb > P.lamb_max) { status = CILQR_ST_LAMB_MAX; break; }
+                }
+            }
+        }
+
+        // results: U (in/out), X_result, J = get_J(X_result, U_result)
+        store_controls(W, A.U + (size_t)b * 2 * N, N, lane);
+        if (A.X)
+            store_states(W, A.X + (size_t)b * 4 * (N + 1), N, lane);
+        if (A.J) {
+            phase_derivs<false>(P, W, pl, obs, 0, false, lane);
+            const double J = sum_sequential(W.Jt, N);
+            if (lane == 0)
+                A.J[b] = J;
+        }
+        if (lane == 0) {
+            if (A.iters) A.iters[b] = iters;
+            if (A.status) A.status[b] = status;
+        }
+        __syncwarp();
+    }
+}
+
+// ------------------------------------------------------------------------------------------------- stage kernel
+enum { STAGE_ROLLOUT = 0, STAGE_STATE_COST, STAGE_CONTROL_COST, STAGE_COST, STAGE_BACKWARD, STAGE_FORWARD };
+
+struct StageArgs {
+    DevParams P;
+    int B, n_obs, stage;
+    const double *x0, *X, *U, *poly, *xlp, *obs, *lamb, *k, *K, *alpha;
+    double *o0, *o1, *scratch; // stage outputs
+    int32_t *ok;
+};
+
+__global__ void __launch_bounds__(kWarpsPerBlock * 32) stage_kernel(const StageArgs A)
+{
+    extern __shared__ double smem[];
+    const DevParams &P = A.P;
+    const int N = P.N;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const WarpSmem W = carve(smem + (size_t)warp * warp_smem_doubles(N, P.S), N, P.S);
+    for (int b = blockIdx.x * kWarpsPerBlock + warp; b < A.B; b += gridDim.x * kWarpsPerBlock) {
+        Polyline pl{0.0, 0.0};
+        if (A.poly) {
+            pl.x_first = A.xlp[2 * b];
+            pl.dxs = (A.xlp[2 * b + 1] - A.xlp[2 * b]) / P.S;
+            build_polyline(P, A.poly + (size_t)b * P.npoly, pl, W.Y, lane);
+        } else {
+            for (int s = lane; s < P.S; s += 32)
+                W.Y[s] = 0.0;
+        }
+        if (A.U)
+            load_controls(W, A.U + (size_t)b * 2 * N, N, lane);
+        else
+            for (int i = lane; i < 2 * N; i += 32)
+                W.U[i] = 0.0;
+        if (A.X)
+            load_states(W, A.X + (size_t)b * 4 * (N + 1), N, lane, true);
+        const double *obs = A.obs ? A.obs + (size_t)b * A.n_obs * OB_FIELDS * N : nullptr;
+        __syncwarp();
+        switch (A.stage) {
+        case STAGE_ROLLOUT:
+            if (lane < 4)
+                W.X[lane * (N + 1)] = A.x0[4 * (size_t)b + lane];
+            __syncwarp();
+            phase_rollout(P, W, lane);
+            store_states(W, A.o0 + (size_t)b * 4 * (N + 1), N, lane);
+            break;
+        case STAGE_STATE_COST: {
+            phase_derivs<true>(P, W, pl, obs, A.n_obs, false, lane);
+            double *lx = A.o0 + (size_t)b * 4 * N, *lxx = A.o1 + (size_t)b * 16 * N;
+            for (int i = lane; i < 16 * N; i += 32)
+                lxx[i] = 0.0;
+            __syncwarp();
+            for (int t = lane; t < N; t += 32) {
+                lx[4 * t + 0] = W.r(0, t); lx[4 * t + 1] = W.r(1, t); lx[4 * t + 2] = W.r(2, t); lx[4 * t + 3] = 0.0;
+                double *L = lxx + 16 * t;
+                L[0] = W.r(3, t); L[1] = W.r(4, t); L[4] = W.r(4, t); L[5] = W.r(5, t); L[10] = 2.0 * P.w_vel;
+            }
+            break;
+        }
+        case STAGE_CONTROL_COST: {
+            phase_derivs<true>(P, W, pl, nullptr, 0, false, lane);
+            double *lu = A.o0 + (size_t)b * 2 * N, *luu = A.o1 + (size_t)b * 4 * N;
+            for (int t = lane; t < N; t += 32) {
+                lu[2 * t] = W.r(6, t); lu[2 * t + 1] = W.r(7, t);
+                luu[4 * t] = W.r(8, t); luu[4 * t + 1] = 0.0; luu[4 * t + 2] = 0.0; luu[4 * t + 3] = W.r(9, t);
+            }
+            break;
+        }
+        case STAGE_COST: {
+            phase_derivs<false>(P, W, pl, nullptr, 0, false, lane);
+            const double J = sum_sequential(W.Jt, N);
+            if (lane == 0)
+                A.o0[b] = J;
+            break;
+        }
+        case STAGE_BACKWARD: {
+            phase_derivs<true>(P, W, pl, obs, A.n_obs, false, lane);
+            const bool fin = phase_backward(P, W, A.lamb[b], lane);
+            double *k = A.o0 + (size_t)b * 2 * N, *K = A.o1 + (size_t)b * 8 * N;
+            for (int t = lane; t < N; t += 32) {
+                k[2 * t] = W.r(0, t); k[2 * t + 1] = W.r(1, t);
+#pragma unroll
+                for (int e = 0; e < 8; ++e)
+                    K[8 * t + e] = W.r(2 + e, t);
+            }
+            if (lane == 0 && A.ok)
+                A.ok[b] = fin ? 1 : 0;
+            break;
+        }
+        case STAGE_FORWARD: {
+            const double *k = A.k + (size_t)b * 2 * N, *K = A.K + (size_t)b * 8 * N;
+            for (int t = lane; t < N; t += 32) {
+                W.r(0, t) = k[2 * t]; W.r(1, t) = k[2 * t + 1];
+#pragma unroll
+                for (int e = 0; e < 8; ++e)
+                    W.r(2 + e, t) = K[8 * t + e];
+            }
+            __syncwarp();
+            if (A.alpha) { // line-search candidate path, one candidate with the caller's alpha
+                double *cand = A.scratch + (size_t)b * traj_doubles(N);
+                phase_forward_candidates(P, W, cand, 1, A.alpha + b, lane);
+                for (int i = lane; i < traj_doubles(N); i += 32)
+                    W.X[i] = cand[i];
+                __syncwarp();
+            } else {
+                phase_forward_inplace(P, W, lane);
+            }
+            store_states(W, A.o0 + (size_t)b * 4 * (N + 1), N, lane);
+            store_controls(W, A.o1 + (size_t)b * 2 * N, N, lane);
+            break;
+        }
+        }
+        __syncwarp();
+    }
+}
+} // namespace cilqr
+
+// ================================================================================================= host side
+using namespace cilqr;
+
+struct cilqr_solver {
+    cilqr_params p;
+    DevParams dp;
+    int max_batch, max_obs;
+    int cur_B = 0, cur_nobs = 0; // obstacle set currently resident
+    int num_sms = 0;
+    DevBuf obs;                  // prepared obstacle records
+    DevBuf counter, scratch;
+    DevBuf stage[12];            // staging for CILQR_MEM_HOST callers / stage outputs
+};
+
+static DevParams derive(const cilqr_params &p)
+{
+    DevParams d;
+    d.N = p.horizon;
+    d.S = p.num_of_local_wpts * 10;
+    d.npoly = p.poly_order + 1;
+    d.max_iter = p.max_iterations;
+    d.dt = p.timestep;
+    d.half_dt2 = p.timestep * p.timestep / 2.0;
+    d.acc_max = p.acc_max;
+    d.acc_min = p.acc_min;
+    d.tanmax_L = std::tan(p.steer_angle_max) / p.wheelbase;
+    d.tanmin_L = std::tan(p.steer_angle_min) / p.wheelbase;
+    d.speed_max = p.speed_max;
+    d.w_pos = p.w_pos;
+    d.w_vel = p.w_vel;
+    d.w_acc = p.w_acc;
+    d.w_yaw = p.w_yawrate;
+    d.v_des = p.desired_speed;
+    d.w_obs = p.w_obstacle;
+    d.q1a = p.q1_acc; d.q2a = p.q2_acc;
+    d.q1y = p.q1_yawrate; d.q2y = p.q2_yawrate;
+    d.q1f = p.q1_front; d.q2f = p.q2_front;
+    d.q1r = p.q1_rear; d.q2r = p.q2_rear;
+    d.ego_front = p.ego_front;
+    d.ego_rear = p.ego_rear;
+    d.t_safe = p.t_safe;
+    d.s_safe_a = p.s_safe_a;
+    d.s_safe_b = p.s_safe_b;
+    d.ego_rad = p.ego_rad;
+    d.tol = p.tolerance;
+    d.lamb_factor = p.lamb_factor;
+    d.lamb_max = p.lamb_max;
+    return d;
+}
+
+// Copies a caller buffer to the device when it lives on the host; returns the device pointer to use.
+template <class T>
+static int stage_in(cilqr_handle h, int slot, const T *src, size_t count, int mem, cudaStream_t st, const T **out)
+{
+    if (!src) { *out = nullptr; return 0; }
+    if (mem == CILQR_MEM_DEVICE) { *out = src; return 0; }
+    if (int rc = h->stage[slot].reserve(count * sizeof(T))) return rc;
+    CILQR_CUDA(cudaMemcpyAsync(h->stage[slot].p, src, count * sizeof(T), cudaMemcpyHostToDevice, st));
+    *out = h->stage[slot].as<T>();
+    return 0;
+}
+template <class T>
+static int stage_out(cilqr_handle h, int slot, T *dst, size_t count, int mem, T **out)
+{
+    if (!dst) { *out = nullptr; return 0; }
+    if (mem == CILQR_MEM_DEVICE) { *out = dst; return 0; }
+    if (int rc = h->stage[slot].reserve(count * sizeof(T))) return rc;
+    *out = h->stage[slot].as<T>();
+    return 0;
+}
+template <class T>
+static int fetch_out(T *dst, const T *dev, size_t count, int mem, cudaStream_t st)
+{
+    if (!dst || mem == CILQR_MEM_DEVICE) return 0;
+    CILQR_CUDA(cudaMemcpyAsync(dst, dev, count * sizeof(T), cudaMemcpyDeviceToHost, st));
+    return 0;
+}
+
+static int check_handle(cilqr_handle h, int B)
+{
+    if (!h) return fail(CILQR_E_ARG, "null handle");
+    if (B < 0 || B > h->max_batch) return fail(CILQR_E_ARG, "batch %d outside [0, %d]", B, h->max_batch);
+    return 0;
+}
+
+extern "C" {
+
+int cilqr_abi_version(void) { return CILQR_ABI_VERSION; }
+int cilqr_sizeof_params(void) { return (int)sizeof(cilqr_params); }
+int cilqr_sizeof_geom(void) { return (int)sizeof(costmap_geom); }
+const char *cilqr_last_error(void) { return g_err; }
+int64_t cilqr_launch_count(void) { return (int64_t)g_launches.load(); }
+
+int cilqr_params_default(cilqr_params *p)
+{
+    if (!p) return fail(CILQR_E_ARG, "null params");
+    std::memset(p, 0, sizeof(*p));
+    // Parameters::Parameters() — Parameters.cpp:3-75
+    p->num_of_local_wpts = 20; p->poly_order = 5; p->desired_speed = 5.0;
+    p->timestep = 0.1; p->horizon = 40; p->tolerance = 1e-4; p->max_iterations = 20; p->num_states = 4; p->num_ctrls = 2;
+    p->w_acc = 1.0; p->w_yawrate = 4.0; p->w_pos = 0.65; p->w_vel = 3.0; p->w_obstacle = 1.0; p->w_uncertainty = 1.0;
+    p->q1_acc = 1.0; p->q2_acc = 1.0; p->q1_yawrate = 1.0; p->q2_yawrate = 1.0;
+    p->q1_front = 2.75; p->q2_front = 2.75; p->q1_rear = 2.5; p->q2_rear = 2.5; p->q1_uncertainty = 2.5; p->q2_uncertainty = 2.5;
+    p->acc_max = 2.0; p->acc_min = -5.5; p->steer_angle_min = -0.75; p->steer_angle_max = 0.75;
+    p->wheelbase = 2.94; p->speed_max = 30.0;
+    p->steer_control_max = 1.0; p->steer_control_min = -1.0; p->throttle_control_max = 1.0; p->throttle_control_min = -1.0;
+    p->t_safe = 0.1; p->s_safe_a = 0; p->s_safe_b = 0; p->ego_rad = 1.35; p->ego_front = 1.47 + 0.925; p->ego_rear = 1.47 + 0.925;
+    p->length = 4.79; p->width = 2.16; p->safe_length = 0.0; p->safe_width = 0.0;
+    // iLQR::iLQR — iLQR.cpp:17-18
+    p->lamb_factor = 10; p->lamb_max = 10000;
+    return 0;
+}
+
+int cilqr_default_controls(const cilqr_params *p, double *U)
+{
+    if (!p || !U) return fail(CILQR_E_ARG, "null argument");
+    const int N = p->horizon, nz = N / 2; // iLQR.cpp:9-15
+    for (int t = 0; t < N; ++t) {
+        U[2 * t] = 0.5;
+        U[2 * t + 1] = t < nz ? 0.0 : 0.1;
+    }
+    return 0;
+}
+
+int cilqr_create(const cilqr_params *p, int max_batch, int max_obs, cilqr_handle *out)
+{
+    if (!p || !out) return fail(CILQR_E_ARG, "null argument");
+    if (p->num_states != 4 || p->num_ctrls != 2) return fail(CILQR_E_ARG, "only the 4-state / 2-control bicycle is supported");
+    if (p->horizon < 1 || p->horizon > 512) return fail(CILQR_E_ARG, "horizon %d outside [1, 512]", p->horizon);
+    if (p->poly_order < 0 || p->poly_order + 1 > kMaxPoly) return fail(CILQR_E_ARG, "poly_order %d outside [0, %d]", p->poly_order, kMaxPoly - 1);
+    if (p->num_of_local_wpts < 1) return fail(CILQR_E_ARG, "num_of_local_wpts must be >= 1");
+    if (max_batch < 1 || max_obs < 0) return fail(CILQR_E_ARG, "max_batch must be >= 1 and max_obs >= 0");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        return fail(CILQR_E_CUDA, "no CUDA device: this library has no CPU path");
+    }
+    cilqr_solver *h = new (std::nothrow) cilqr_solver();
+    if (!h) return fail(CILQR_E_ALLOC, "out of host memory");
+    h->p = *p;
+    h->dp = derive(*p);
+    h->max_batch = max_batch;
+    h->max_obs = max_obs;
+    int dev = 0;
+    CILQR_CUDA(cudaGetDevice(&dev));
+    CILQR_CUDA(cudaDeviceGetAttribute(&h->num_sms, cudaDevAttrMultiProcessorCount, dev));
+    const size_t smem = (size_t)kWarpsPerBlock * warp_smem_doubles(h->dp.N, h->dp.S) * sizeof(double);
+    if (smem > 227 * 1024) { delete h; return fail(CILQR_E_ARG, "horizon/polyline too large for shared memory (%zu B per CTA)", smem); }
+    CILQR_CUDA(cudaFuncSetAttribute(solve_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CILQR_CUDA(cudaFuncSetAttribute(solve_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CILQR_CUDA(cudaFuncSetAttribute(stage_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    if (int rc = h->counter.reserve(sizeof(int))) { delete h; return rc; }
+    *out = h;
+    return 0;
+}
+
+int cilqr_destroy(cilqr_handle h)
+{
+    if (!h) return 0;
+    h->obs.release();
+    h->counter.release();
+    h->scratch.release();
+    for (auto &s : h->stage) s.release();
+    delete h;
+    return 0;
+}
+
+static int prep_grid(size_t total, int num_sms) { return (int)std::min<size_t>((total + 255) / 256, (size_t)num_sms * 8); }
+
+int cilqr_set_obstacles(cilqr_handle h, int B, int n_obs, const double *dim, const double *pos, int mem, void *stream)
+{
+    if (int rc = check_handle(h, B)) return rc;
+    if (n_obs < 0 || n_obs > h->max_obs) return fail(CILQR_E_ARG, "n_obs %d outside [0, %d]", n_obs, h->max_obs);
+    cudaStream_t st = (cudaStream_t)stream;
+    h->cur_B = B;
+    h->cur_nobs = n_obs;
+    if (n_obs == 0 || B == 0) return 0; // clear_Obstacle()
+    if (!dim || !pos) return fail(CILQR_E_ARG, "null obstacle arrays");
+    const size_t n_bj = (size_t)B * n_obs, N = h->dp.N;
+    const double *d_dim, *d_pos;
+    if (int rc = stage_in(h, 0, dim, n_bj * 2 * N, mem, st, &d_dim)) return rc;
+    if (int rc = stage_in(h, 1, pos, n_bj * 4 * N, mem, st, &d_pos)) return rc;
+    if (int rc = h->obs.reserve(n_bj * OB_FIELDS * N * sizeof(double))) return rc;
+    prep_obstacles_dense_kernel<<<prep_grid(n_bj * N, h->num_sms), 256, 0, st>>>(h->dp, n_bj, d_dim, d_pos, h->obs.as<double>());
+    CILQR_LAUNCH_CHECK();
+    if (mem == CILQR_MEM_HOST) CILQR_CUDA(cudaStreamSynchronize(st));
+    return 0;
+}
+
+int cilqr_set_obstacles_cv(cilqr_handle h, int B, int n_obs, const double *state0, const double *LW, const double *sigma, double kappa,
+                           int mem, void *stream)
+{
+    if (int rc = check_handle(h, B)) return rc;
+    if (n_obs < 0 || n_obs > h->max_obs) return fail(CILQR_E_ARG, "n_obs %d outside [0, %d]", n_obs, h->max_obs);
+    cudaStream_t st = (cudaStream_t)stream;
+    h->cur_B = B;
+    h->cur_nobs = n_obs;
+    if (n_obs == 0 || B == 0) return 0;
+    if (!state0 || !LW || !sigma) return fail(CILQR_E_ARG, "null obstacle arrays");
+    const size_t n_bj = (size_t)B * n_obs, N = h->dp.N;
+    const double *d_s, *d_lw, *d_sg;
+    if (int rc = stage_in(h, 0, state0, n_bj * 4, mem, st, &d_s)) return rc;
+    if (int rc = stage_in(h, 1, LW, n_bj * 2, mem, st, &d_lw)) return rc;
+    if (int rc = stage_in(h, 2, sigma, n_bj * 3, mem, st, &d_sg)) return rc;
+    if (int rc = h->obs.reserve(n_bj * OB_FIELDS * N * sizeof(double))) return rc;
+    prep_obstacles_cv_kernel<<<prep_grid(n_bj * N, h->num_sms), 256, 0, st>>>(h->dp, n_bj, d_s, d_lw, d_sg, kappa, h->obs.as<double>());
+    CILQR_LAUNCH_CHECK();
+    if (mem == CILQR_MEM_HOST) CILQR_CUDA(cudaStreamSynchronize(st));
+    return 0;
+}
+
+static int need_obstacles(cilqr_handle h, int B)
+{
+    if (h->cur_nobs > 0 && h->cur_B != B)
+        return fail(CILQR_E_STATE, "obstacles were set for a batch of %d, this call has %d scenarios", h->cur_B, B);
+    return 0;
+}
+
+int cilqr_solve_batch(cilqr_handle h, int B, const double *x0, double *U, const double *poly, const double *xlp, int n_alphas, int merit,
+                      double *X, double *J, int32_t *iters, int32_t *status, int mem, void *stream)
+{
+    if (int rc = check_handle(h, B)) return rc;
+    if (!x0 || !U || !poly || !xlp) return fail(CILQR_E_ARG, "null argument");
+    if (n_alphas < 1 || n_alphas > kMaxAlphas) return fail(CILQR_E_ARG, "n_alphas %d outside [1, %d]", n_alphas, kMaxAlphas);
+    if (merit != CILQR_MERIT_TRACKING && merit != CILQR_MERIT_TOTAL) return fail(CILQR_E_ARG, "unknown merit %d", merit);
+    if (int rc = need_obstacles(h, B)) return rc;
+    if (B == 0) return 0;
+    cudaStream_t st = (cudaStream_t)stream;
+    const int N = h->dp.N;
+    SolveArgs A;
+    A.P = h->dp;
+    A.B = B;
+    A.n_obs = h->cur_nobs;
+    A.n_alphas = n_alphas;
+    A.merit = merit;
+    A.obs = h->obs.as<double>();
+    const double *dU_in;
+    if (int rc = stage_in(h, 3, x0, (size_t)B * 4, mem, st, &A.x0)) return rc;
+    if (int rc = stage_in(h, 4, (const double *)U, (size_t)B * 2 * N, mem, st, &dU_in)) return rc;
+    A.U = const_cast<double *>(dU_in);
+    if (int rc = stage_in(h, 5, poly, (size_t)B * h->dp.npoly, mem, st, &A.poly)) return rc;
+    if (int rc = stage_in(h, 6, xlp, (size_t)B * 2, mem, st, &A.xlp)) return rc;
+    if (int rc = stage_out(h, 7, X, (size_t)B * 4 * (N + 1), mem, &A.X)) return rc;
+    if (int rc = stage_out(h, 8, J, (size_t)B, mem, &A.J)) return rc;
+    if (int rc = stage_out(h, 9, iters, (size_t)B, mem, &A.iters)) return rc;
+    if (int rc = stage_out(h, 10, status, (size_t)B, mem, &A.status)) return rc;
+    A.counter = h->counter.as<int>();
+
+    const size_t smem = (size_t)kWarpsPerBlock * warp_smem_doubles(N, h->dp.S) * sizeof(double);
+    int per_sm = 0;
+    if (n_alphas > 1)
+        CILQR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, solve_kernel<true>, kWarpsPerBlock * 32, smem));
+    else
+        CILQR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, solve_kernel<false>, kWarpsPerBlock * 32, smem));
+    if (per_sm < 1) return fail(CILQR_E_CUDA, "solve kernel does not fit on an SM (smem %zu B)", smem);
+    const int grid = std::min((B + kWarpsPerBlock - 1) / kWarpsPerBlock, h->num_sms * per_sm);
+    A.scratch = nullptr;
+    if (n_alphas > 1) {
+        if (int rc = h->scratch.reserve((size_t)grid * kWarpsPerBlock * n_alphas * traj_doubles(N) * sizeof(double))) return rc;
+        A.scratch = h->scratch.as<double>();
+    }
+    CILQR_CUDA(cudaMemsetAsync(A.counter, 0, sizeof(int), st));
+    if (n_alphas > 1)
+        solve_kernel<true><<<grid, kWarpsPerBlock * 32, smem, st>>>(A);
+    else
+        solve_kernel<false><<<grid, kWarpsPerBlock * 32, smem, st>>>(A);
+    CILQR_LAUNCH_CHECK();
+    if (int rc = fetch_out(U, A.U, (size_t)B * 2 * N, mem, st)) return rc;
+    if (int rc = fetch_out(X, A.X, (size_t)B * 4 * (N + 1), mem, st)) return rc;
+    if (int rc = fetch_out(J, A.J, (size_t)B, mem, st)) return rc;
+    if (int rc = fetch_out(iters, A.iters, (size_t)B, mem, st)) return rc;
+    if (int rc = fetch_out(status, A.status, (size_t)B, mem, st)) return rc;
+    if (mem == CILQR_MEM_HOST) CILQR_CUDA(cudaStreamSynchronize(st));
+    return 0;
+}
+
+// ---- stage entry points -------------------------------------------------------------------------------------
+static int run_stage(cilqr_handle h, StageArgs &A, cudaStream_t st)
+{
+    const size_t smem = (size_t)kWarpsPerBlock * warp_smem_doubles(h->dp.N, h->dp.S) * sizeof(double);
+    const int grid = std::min((A.B + kWarpsPerBlock - 1) / kWarpsPerBlock, h->num_sms * 4);
+    stage_kernel<<<grid, kWarpsPerBlock * 32, smem, st>>>(A);
+    CILQR_LAUNCH_CHECK();
+    return 0;
+}
+static StageArgs stage_args(cilqr_handle h, int B, int stage)
+{
+    StageArgs A;
+    std::memset(&A, 0, sizeof(A));
+    A.P = h->dp;
+    A.B = B;
+    A.stage = stage;
+    A.n_obs = h->cur_nobs;
+    A.obs = h->cur_nobs > 0 ? h->obs.as<double>() : nullptr;
+    return A;
+}
+
+int cilqr_rollout(cilqr_handle h, int B, const double *x0, const double *U, double *X, int mem, void *stream)
+{
+    if (int rc = check_handle(h, B)) return rc;
+    if (!x0 || !U || !X) return fail(CILQR_E_ARG, "null argument");
+    if (B == 0) return 0;
+    cudaStream_t st = (cudaStream_t)stream;
+    const int N = h->dp.N;
+    StageArgs A = stage_args(h, B, STAGE_ROLLOUT);
+    if (int rc = stage_in(h, 3, x0, (size_t)B * 4, mem, st, &A.x0)) return rc;
+    if (int rc = stage_in(h, 4, U, (size_t)B * 2 * N, mem, st, &A.U)) return rc;
+    if (int rc = stage_out(h, 7, X, (size_t)B * 4 * (N + 1), mem, &A.o0)) return rc;
+    if (int rc = run_stage(h, A, st)) return rc;
+    if (int rc = fetch_out(X, A.o0, (size_t)B * 4 * (N + 1), mem, st)) return rc;
+    if (mem == CILQR_MEM_HOST) CILQR_CUDA(cudaStreamSynchronize(st));
+    return 0;
+}
+
+int cilqr_state_cost(cilqr_handle h, int B, const double *X, const double *poly, const double *xlp, double *l_x, double *l_xx, int mem,
+                     void *stream)
+{
+    if (int rc = check_handle(h, B)) return rc;
+    if (!X || !poly || !xlp || !l_x || !l_xx) return fail(CILQR_E_ARG, "null argument");
+    if (int rc = need_obstacles(h, B)) return rc;
+    if (B == 0) return 0;
+    cudaStream_t st = (cudaStream_t)stream;
+    const int N = h->dp.N;
+    StageArgs A = stage_args(h, B, STAGE_STATE_COST);
+    if (int rc = stage_in(h, 3, X, (size_t)B * 4 * (N + 1), mem, st, &A.X)) return rc;
+    if (int rc = stage_in(h, 5, poly, (size_t)B * h->dp.npoly, mem, st, &A.poly)) return rc;
+    if (int rc = stage_in(h, 6, xlp, (size_t)B * 2, mem, st, &A.xlp)) return rc;
+    if (int rc = stage_out(h, 7, l_x, (size_t)B * 4 * N, mem, &A.o0)) return rc;
+    if (int rc = stage_out(h, 8, l_xx, (size_t)B * 16 * N, mem, &A.o1)) return rc;
+    if (int rc = run_stage(h, A, st)) return rc;
+    if (int rc = fetch_out(l_x, A.o0, (size_t)B * 4 * N, mem, st)) return rc;
+    if (int rc = fetch_out(l_xx, A.o1, (size_t)B * 16 * N, mem, st)) return rc;
+    if (mem == CILQR_MEM_HOST) CILQR_CUDA(cudaStreamSynchronize(st));
+    return 0;
+}
+
+int cilqr_control_cost(cilqr_handle h, int B, const double *X, const double *U, double *l_u, double *l_uu, int mem, void *stream)
+{
+    if (int rc = check_handle(h, B)) return rc;
+    if (!X || !U || !l_u || !l_uu) return fail(CILQR_E_ARG, "null argument");
+    if (B == 0) return 0;
+    cudaStream_t st = (cudaStream_t)stream;
+    const int N = h->dp.N;
+    StageArgs A = stage_args(h, B, STAGE_CONTROL_COST);
+    if (int rc = stage_in(h, 3, X, (size_t)B * 4 * (N + 1), mem, st, &A.X)) return rc;
+    if (int rc = stage_in(h, 4, U, (size_t)B * 2 * N, mem, st, &A.U)) return rc;
+    if (int rc = stage_out(h, 7, l_u, (size_t)B * 2 * N, mem, &A.o0)) return rc;
+    if (int rc = stage_out(h, 8, l_uu, (size_t)B * 4 * N, mem, &A.o1)) return rc;
+    if (int rc = run_stage(h, A, st)) return rc;
+    if (int rc = fetch_out(l_u, A.o0, (size_t)B * 2 * N, mem, st)) return rc;
+    if (int rc = fetch_out(l_uu, A.o1, (size_t)B * 4 * N, mem, st)) return rc;
+    if (mem == CILQR_MEM_HOST) CILQR_CUDA(cudaStreamSynchronize(st));
+    return 0;
+}
+
+int cilqr_cost(cilqr_handle h, int B, const double *X, const double *U, const double *poly, const double *xlp, double *J, int mem,
+               void *stream)
+{
+    if (int rc = check_handle(h, B)) return rc;
+    if (!X || !U || !poly || !xlp || !J) return fail(CILQR_E_ARG, "null argument");
+    if (B == 0) return 0;
+    cudaStream_t st = (cudaStream_t)stream;
+    const int N = h->dp.N;
+    StageArgs A = stage_args(h, B, STAGE_COST);
+    if (int rc = stage_in(h, 3, X, (size_t)B * 4 * (N + 1), mem, st, &A.X)) return rc;
+    if (int rc = stage_in(h, 4, U, (size_t)B * 2 * N, mem, st, &A.U)) return rc;
+    if (int rc = stage_in(h, 5, poly, (size_t)B * h->dp.npoly, mem, st, &A.poly)) return rc;
+    if (int rc = stage_in(h, 6, xlp, (size_t)B * 2, mem, st, &A.xlp)) return rc;
+    if (int rc = stage_out(h, 7, J, (size_t)B, mem, &A.o0)) return rc;
+    if (int rc = run_stage(h, A, st)) return rc;
+    if (int rc = fetch_out(J, A.o0, (size_t)B, mem, st)) return rc;
+    if (mem == CILQR_MEM_HOST) CILQR_CUDA(cudaStreamSynchronize(st));
+    return 0;
+}
+
+int cilqr_backward(cilqr_handle h, int B, const double *X, const double *U, const double *poly, const double *xlp, const double *lamb,
+                   double *k, double *K, int32_t *ok, int mem, void *stream)
+{
+    if (int rc = check_handle(h, B)) return rc;
+    if (!X || !U || !poly || !xlp || !lamb || !k || !K) return fail(CILQR_E_ARG, "null argument");
+    if (int rc = need_obstacles(h, B)) return rc;
+    if (B == 0) return 0;
+    cudaStream_t st = (cudaStream_t)stream;
+    const int N = h->dp.N;
+    StageArgs A = stage_args(h, B, STAGE_BACKWARD);
+    if (int rc = stage_in(h, 3, X, (size_t)B * 4 * (N + 1), mem, st, &A.X)) return rc;
+    if (int rc = stage_in(h, 4, U, (size_t)B * 2 * N, mem, st, &A.U)) return rc;
+    if (int rc = stage_in(h, 5, poly, (size_t)B * h->dp.npoly, mem, st, &A.poly)) return rc;
+    if (int rc = stage_in(h, 6, xlp, (size_t)B * 2, mem, st, &A.xlp)) return rc;
+    if (int rc = stage_in(h, 2, lamb, (size_t)B, mem, st, &A.lamb)) return rc;
+    if (int rc = stage_out(h, 7, k, (size_t)B * 2 * N, mem, &A.o0)) return rc;
+    if (int rc = stage_out(h, 8, K, (size_t)B * 8 * N, mem, &A.o1)) return rc;
+    if (int rc = stage_out(h, 9, ok, (size_t)B, mem, &A.ok)) return rc;
+    if (int rc = run_stage(h, A, st)) return rc;
+    if (int rc = fetch_out(k, A.o0, (size_t)B * 2 * N, mem, st)) return rc;
+    if (int rc = fetch_out(K, A.o1, (size_t)B * 8 * N, mem, st)) return rc;
+    if (int rc = fetch_out(ok, A.ok, (size_t)B, mem, st)) return rc;
+    if (mem == CILQR_MEM_HOST) CILQR_CUDA(cudaStreamSynchronize(st));
+    return 0;
+}
+
+int cilqr_forward(cilqr_handle h, int B, const double *X, const double *U, const double *k, const double *K, const double *alpha,
+                  double *X_new, double *U_new, int mem, void *stream)
+{
+    if (int rc = check_handle(h, B)) return rc;
+    if (!X || !U || !k || !K || !X_new || !U_new) return fail(CILQR_E_ARG, "null argument");
+    if (B == 0) return 0;
+    cudaStream_t st = (cudaStream_t)stream;
+    const int N = h->dp.N;
+    StageArgs A = stage_args(h, B, STAGE_FORWARD);
+    if (int rc = stage_in(h, 3, X, (size_t)B * 4 * (N + 1), mem, st, &A.X)) return rc;
+    if (int rc = stage_in(h, 4, U, (size_t)B * 2 * N, mem, st, &A.U)) return rc;
+    if (int rc = stage_in(h, 5, k, (size_t)B * 2 * N, mem, st, &A.k)) return rc;
+    if (int rc = stage_in(h, 6, K, (size_t)B * 8 * N, mem, st, &A.K)) return rc;
+    if (int rc = stage_in(h, 2, alpha, (size_t)B, mem, st, &A.alpha)) return rc;
+    if (int rc = stage_out(h, 7, X_new, (size_t)B * 4 * (N + 1), mem, &A.o0)) return rc;
+    if (int rc = stage_out(h, 8, U_new, (size_t)B * 2 * N, mem, &A.o1)) return rc;
+    if (alpha) {
+        if (int rc = h->scratch.reserve((size_t)B * traj_doubles(N) * sizeof(double))) return rc;
+        A.scratch = h->scratch.as<double>();
+    }
+    if (int rc = run_stage(h, A, st)) return rc;
+    if (int rc = fetch_out(X_new, A.o0, (size_t)B * 4 * (N + 1), mem, st)) return rc;
+    if (int rc = fetch_out(U_new, A.o1, (size_t)B * 2 * N, mem, st)) return rc;
+    if (mem == CILQR_MEM_HOST) CILQR_CUDA(cudaStreamSynchronize(st));
+    return 0;
+}
+
+} // extern "C"
