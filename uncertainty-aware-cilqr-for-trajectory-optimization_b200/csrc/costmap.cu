@@ -17,6 +17,7 @@
 #include <cuda.h>
 #include <climits>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 
 namespace cilqr
@@ -353,9 +354,12 @@ int costmap_warp_batch(const float *src, const costmap_geom *src_geom, const cos
         const cuuint64_t gstride[1] = {(cuuint64_t)G.rows_s * sizeof(float)};
         const cuuint32_t box[2] = {kBox, kBox};
         const cuuint32_t estr[2] = {1, 1};
+        const char *dbg = getenv("CILQR_TMA_DEBUG"); // bring-up knob: 1 = zero OOB fill, 2 = no L2 promotion
+        const int dbgv = dbg ? atoi(dbg) : 0;
         CUresult cr = encode_tiled_fn()(&tmap, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float *>(d_src), gdim, gstride, box, estr,
-                                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
-                                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NAN_REQUEST_ZERO_FMA);
+                                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                                        (dbgv & 2) ? CU_TENSOR_MAP_L2_PROMOTION_NONE : CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                                        (dbgv & 1) ? CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE : CU_TENSOR_MAP_FLOAT_OOB_FILL_NAN_REQUEST_ZERO_FMA);
         if (cr != CUDA_SUCCESS) return fail(CILQR_E_CUDA, "cuTensorMapEncodeTiled failed (%d)", (int)cr);
         warp_tma_kernel<<<grid, kWarpThreads, 0, st>>>(tmap, G, d_src, d_poses, d_bbox, d_out, d_idx);
     } else {
