@@ -1,0 +1,430 @@
+"""bench.py — the driver's measurement contract for the CILQR hot path.
+
+    python bench.py --gpus 1 --steps K --warmup W                  (this repo's CUDA path)
+    torchrun ... bench.py --gpus N --steps K --warmup W            (one rank per GPU, NCCL gather of U*)
+    python bench.py --impl reference --steps K --warmup W          (the reference's own CPU code, oracle/_ref)
+
+A "step" is one pass of the hot path over one batch of synthetic scenarios of BASELINE.json config 4 (the
+configuration the target is quoted on): 65 536 independent scenarios per GPU, horizon N = 50, 20 Gaussian-uncertain
+constant-velocity obstacles each with covariance propagation over the horizon on the device
+(cilqr_set_obstacles_cv), then the fused batched solve (cilqr_solve_batch, reference semantics n_alphas = 1), then
+— for N > 1 — the single NCCL all-gather of the optimal control sequences.  Scenarios shard by batch index with no
+data-path collective, so per-GPU work is fixed as N grows ("scaling": "weak").
+
+`value`   whole-job solves/s with the inputs resident in HBM (CUDA events, max over ranks).
+`e2e`     the same metric through the C ABI with HOST (pinned) buffers: host->device copies of every input and
+          device->host copies of U*, X*, J, iterations, status are inside the timed region.
+`roofline` the dominant kernel (solve_kernel): mandatory HBM bytes per launch / its CUDA-event duration against the
+          measured copy bandwidth of MEASURED_PEAKS.json; the solver is FP64-issue bound, so `fp64` reports the
+          algorithmic FP64 flop rate against an FMA micro-benchmark run on the same GPU.
+`costmap_warp` the second half of BASELINE.json's metric: HBM GB/s of costmap_warp_batch (config 5, one grid size).
+`cpu_baseline` the reference's own CPU solver (oracle/_ref, unmodified sources) on the host cores of this box, on a
+          bounded sample of the same workload (rank 0, N = 1 only).
+Nothing here reads /root/reference.  oracle/ is only executed by the cpu_baseline leg and by --impl reference.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "batched CILQR solves/sec (N=50)"
+UNIT = "solves/s"
+HORIZON = 50
+N_OBS = 20
+BATCH_PER_GPU = 65536
+WARP_T = 2048          # config 5 grid edge timed by the default run (source 2T x 2T = 67 MB, poses x 16.8 MB targets)
+WARP_POSES = 1024      # BASELINE config 5: 1024 poses, processed in chunks
+WARP_CHUNK = 64
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--batch", type=int, default=BATCH_PER_GPU, help="scenarios per GPU")
+    ap.add_argument("--n-obs", type=int, default=N_OBS)
+    ap.add_argument("--n-alphas", type=int, default=1)
+    ap.add_argument("--warp-T", type=int, default=WARP_T)
+    ap.add_argument("--no-warp", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def measured_peaks():
+    """HBM GB/s from the driver-written MEASURED_PEAKS.json, else the fallback B200_PROFILING.md states."""
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+# ------------------------------------------------------------------------------------------------ algorithmic counts
+def solver_bytes_per_solve(N, n_obs):
+    """Mandatory HBM traffic of one solve with the compact obstacle form:
+    in: x0 32 + U 16N + poly 48 + xlp 16 + obstacles 72 n_obs (state0 4, LW 2, sigma 3 doubles);
+    out: X 32(N+1) + U 16N + J 8 + iterations 4 + status 4."""
+    return 32 + 16 * N + 48 + 16 + 72 * n_obs + 32 * (N + 1) + 16 * N + 16
+
+
+def solver_flops_per_iteration(N, n_obs, S=200):
+    """Algorithmic FP64 flops of one iLQR iteration of one scenario, each operation counted once (the warp-replicated
+    Riccati / rollout arithmetic is NOT multiplied by 32); exp / sincos counted as 20 flops:
+      closest point   N * S * 6        (2 sub, 2 mul, 1 add, 1 compare per polyline sample; get_J shares the pass)
+      obstacles       N * n_obs * 2 * (46 + 20)   (two ellipses per obstacle, one exp each)
+      control cost    N * (4 * 22 + 16)
+      Riccati sweep   N * 330          (sparse A, B; symmetric V_xx; closed-form 2x2 inverse)
+      rollout         N * (40 + 20)    (gain application, bicycle step, one sincos)"""
+    return N * S * 6 + N * n_obs * 2 * 66 + N * 104 + N * 330 + N * 60
+
+
+# ------------------------------------------------------------------------------------------------ clocks during the timed region
+class ClockSampler:
+    """nvidia-smi sampler running DURING the timed region (B200_PROFILING.md's clocks line)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.tmp = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.proc = None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(gpu_index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=self.tmp, stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.proc is None:
+            return out
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        self.tmp.flush()
+        self.tmp.seek(0)
+        sm, mx, pw, reasons = [], [], [], set()
+        for line in self.tmp.read().splitlines():
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2])); pw.append(float(f[3]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        try:
+            os.unlink(self.tmp.name)
+        except OSError:
+            pass
+        if sm:
+            busy = [s for s, p in zip(sm, pw) if p >= 0.5 * max(pw)] or sm
+            out.update(sm_mhz=float(np.median(busy)), sm_max_mhz=float(max(mx)), power_w_max=float(max(pw)), samples=len(sm))
+        out["reasons"] = sorted(reasons)
+        return out
+
+
+# ------------------------------------------------------------------------------------------------ CPU legs (the only users of oracle/)
+def cpu_solver():
+    import oracle
+    if oracle.ref_available():
+        return oracle.RefOracle()
+    oracle.build(("port",))
+    return oracle.PortOracle()
+
+
+def cpu_solve_sample(chk, p, sc, n, threads=0):
+    """Times chk.solve_batch on the first n scenarios of `sc` with every host thread; returns (seconds, threads)."""
+    t0 = time.perf_counter()
+    r = chk.solve_batch(p, n, sc["n_obs"], sc["dim"][:n], sc["pos"][:n], sc["x0"][:n], sc["U0"][:n], sc["poly"][:n], sc["xlp"][:n],
+                        threads=threads, want_X=False)
+    return time.perf_counter() - t0, int(r["threads"])
+
+
+def cpu_sample_size(chk, p, sc, target_s, cap):
+    """Pilot run -> number of scenarios that take about `target_s` seconds on all host threads."""
+    cores = os.cpu_count() or 1
+    pilot = min(cap, max(2 * cores, 8))
+    dt, used = cpu_solve_sample(chk, p, sc, pilot)
+    n = int(max(pilot, min(cap, pilot * target_s / max(dt, 1e-3))))
+    return n, used
+
+
+def run_reference_arm(args):
+    """--impl reference: the reference's own CPU implementation (oracle/_ref = unmodified sources, Eigen kernels, no MKL)
+    on all host threads; each step is a bounded sample of the same workload.  Rank 0 only."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import cilqr_b200
+    from cilqr_b200 import scenarios
+    chk = cpu_solver()
+    p = chk.params_default(horizon=HORIZON)
+    cap = 4096
+    sc = scenarios.make_scenarios(p, 0, cap, args.n_obs, dense=True)
+    n, used = cpu_sample_size(chk, p, sc, target_s=max(1.0, min(6.0, 90.0 / max(1, args.steps + args.warmup))), cap=cap)
+    for _ in range(args.warmup):
+        cpu_solve_sample(chk, p, sc, n)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        cpu_solve_sample(chk, p, sc, n)
+    dt = time.perf_counter() - t0
+    value = n * args.steps / dt
+    sample = "%d of the %d scenarios per step (config 4 inputs: N=50, %d covariance-inflated obstacles, host-expanded)" % (n, args.batch, args.n_obs)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": 1e3 * dt / max(1, args.steps), "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic",
+        "config": {"workload": "config4: 65536 scenarios x 20 uncertain obstacles, N=50 (bounded sample per step)", "horizon": HORIZON,
+                   "n_obs": args.n_obs, "n_alphas": 1, "sample_per_step": n},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": used, "kind": chk.kind, "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def cpu_baseline_leg(p, args):
+    """cpu_baseline of the main arm: ~15 s of the reference CPU solver on all host threads (rank 0, N = 1)."""
+    from cilqr_b200 import scenarios
+    chk = cpu_solver()
+    cap = 4096
+    sc = scenarios.make_scenarios(p, 0, cap, args.n_obs, dense=True)
+    n, used = cpu_sample_size(chk, p, sc, target_s=15.0, cap=cap)
+    dt, used = cpu_solve_sample(chk, p, sc, n)
+    out = {"value": n / dt, "unit": UNIT, "cores": used, "kind": chk.kind,
+           "sample": "first %d scenarios of the step's %d (same inputs, obstacles host-expanded), %.1f s, all host threads, Eigen kernels without MKL"
+                     % (n, args.batch, dt)}
+    # single-thread figure for context (the reference itself is single-threaded)
+    n1 = max(4, min(64, n // max(1, used)))
+    dt1, _ = cpu_solve_sample(chk, p, sc, n1, threads=1)
+    out["single_thread_value"] = n1 / dt1
+    return out
+
+
+# ------------------------------------------------------------------------------------------------ the CUDA arm
+def event_pair():
+    import torch
+    return torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+
+
+def max_over_ranks(x, world, device):
+    import torch
+    import torch.distributed as dist
+    if world == 1:
+        return float(x)
+    t = torch.tensor([float(x)], dtype=torch.float64, device=device)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def bench_warp(args, device, hbm_peak, peak_kind):
+    """costmap_warp_batch, BASELINE config 5 at one grid size: target T x T, source 2T x 2T (both larger than L2 once the
+    64-pose chunk of outputs is counted), 1024 poses in chunks of 64, value + index map emitted (12 B per cell)."""
+    import torch
+    import cilqr_b200
+    from cilqr_b200 import scenarios
+    T, S = args.warp_T, 2 * args.warp_T
+    G = cilqr_b200.CostmapGeom
+    sg, tg = G(S * 0.2, S * 0.2, 0.2, 0.0, 0.0), G(T * 0.2, T * 0.2, 0.2, 0.0, 0.0)
+    src = torch.from_numpy(scenarios.make_source_map(S, S, nan_band=False)).to(device)
+    chunk = max(1, min(WARP_CHUNK, (3 << 30) // (T * T * 8)))
+    poses = torch.from_numpy(scenarios.make_poses(WARP_POSES, (0.0, 0.0), 0.05 * T * 0.2)).to(device)
+    out = torch.empty((chunk, T * T), dtype=torch.float32, device=device)
+    idx = torch.empty((chunk, T * T), dtype=torch.int32, device=device)
+    res = {}
+    for name, with_idx in (("value_only", False), ("value_and_index", True)):
+        def sweep():
+            for c in range(0, WARP_POSES, chunk):
+                cilqr_b200.warp_batch(src, sg, tg, poses[c:c + chunk], out=out[:min(chunk, WARP_POSES - c)],
+                                      idx=idx[:min(chunk, WARP_POSES - c)] if with_idx else None, want_idx=False)
+        sweep()
+        torch.cuda.synchronize()
+        e0, e1 = event_pair()
+        e0.record()
+        sweep()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1)
+        by = WARP_POSES * T * T * (12 if with_idx else 8)
+        res[name] = {"gbs": by / ms / 1e6, "ms_per_pose": ms / WARP_POSES, "bytes_per_cell": 12 if with_idx else 8}
+    best = res["value_and_index"]
+    return {"metric": "costmap warp HBM GB/s", "value": best["gbs"], "unit": "GB/s",
+            "config": {"workload": "config5: target %dx%d from source %dx%d, %d poses in chunks of %d, float value + int32 index map"
+                                   % (T, T, S, S, WARP_POSES, chunk), "l2": "working set per chunk larger than L2"},
+            "value_only_gbs": res["value_only"]["gbs"],
+            "roofline": {"bound": "hbm", "achieved": best["gbs"], "peak": hbm_peak, "unit": "GB/s", "frac": best["gbs"] / hbm_peak,
+                         "traffic": None, "peak_source": peak_kind,
+                         "algorithmic_bytes_per_cell": "4 B source read + 4 B value write + 4 B index write"},
+            "launches": 2 * 2 * ((WARP_POSES + chunk - 1) // chunk)}
+
+
+def run_b200_arm(args):
+    import ctypes as C
+    import torch
+    import cilqr_b200
+    from cilqr_b200 import scenarios, dist as cdist
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device - this arm has no CPU path (use --impl reference for the CPU reference)")
+    rank, local_rank, world = cdist.init_process_group("nccl")
+    torch.cuda.set_device(local_rank)
+    device = torch.device("cuda", local_rank)
+    lib = cilqr_b200.load_library()
+    p = cilqr_b200.Parameters()
+    lib.cilqr_params_default(C.byref(p))
+    p = p.replace(horizon=HORIZON)
+    N, B, n_obs = HORIZON, args.batch, args.n_obs
+    hbm_peak, peak_kind = measured_peaks()
+
+    # ---- inputs: this rank's contiguous shard of scenario ids, generated on the host, resident in HBM before timing
+    sc = scenarios.make_scenarios(p, rank * B, B, n_obs, dense=False)
+    keys = ("x0", "U0", "poly", "xlp", "obs_state0", "obs_LW", "obs_sigma")
+    d = {k: torch.from_numpy(sc[k]).to(device) for k in keys}
+    U = torch.empty_like(d["U0"])
+    gathered = torch.empty((world * B, 2 * N), dtype=torch.float64, device=device) if world > 1 else None
+    solver = cilqr_b200.iLQR(p, max_batch=B, max_obs=n_obs)
+    merit = cilqr_b200.MERIT_TOTAL if args.n_alphas > 1 else cilqr_b200.MERIT_TRACKING
+    kern_ev = []
+
+    def step(timed):
+        solver.set_obstacles_cv(d["obs_state0"], d["obs_LW"], d["obs_sigma"], sc["kappa"])  # covariance propagation on device
+        U.copy_(d["U0"])
+        if timed:
+            ev = event_pair()
+            ev[0].record()
+        solver.get_optimal_control_seq(d["x0"], U, d["poly"], d["xlp"], n_alphas=args.n_alphas, merit=merit)
+        if timed:
+            ev[1].record()
+            kern_ev.append(ev)
+        if world > 1:
+            torch.distributed.all_gather_into_tensor(gathered, U)  # the one exchange step
+
+    for _ in range(max(args.warmup, 0)):
+        step(False)
+    torch.cuda.synchronize()
+    launches0 = cilqr_b200.launch_count()
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    if world > 1:
+        torch.distributed.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = event_pair()
+    e0.record()
+    for _ in range(args.steps):
+        step(True)
+    e1.record()
+    torch.cuda.synchronize()
+    if world > 1:
+        torch.distributed.barrier()
+    total_ms = max_over_ranks(e0.elapsed_time(e1), world, device)
+    clocks = sampler.stop() if sampler else None
+    launches = cilqr_b200.launch_count() - launches0
+    kernel_ms = float(np.mean([a.elapsed_time(b) for a, b in kern_ev]))
+    iters = solver.iterations.cpu().numpy()
+    status = solver.status.cpu().numpy()
+    value = world * B * args.steps / (total_ms * 1e-3)
+
+    # ---- end to end through the C ABI with pinned HOST buffers (copies inside the timed region)
+    e2e = None
+    if not args.no_e2e:
+        pin = {k: torch.from_numpy(sc[k]).pin_memory() for k in keys}
+        Uh = torch.empty((B, 2 * N), dtype=torch.float64).pin_memory()
+        outs = {"X": torch.empty((B, 4 * (N + 1)), dtype=torch.float64).pin_memory().numpy(), "J": torch.empty(B, dtype=torch.float64).pin_memory().numpy(),
+                "iters": torch.empty(B, dtype=torch.int32).pin_memory().numpy(), "status": torch.empty(B, dtype=torch.int32).pin_memory().numpy()}
+        hs = cilqr_b200.iLQR(p, max_batch=B, max_obs=n_obs)
+
+        def e2e_step():
+            hs.set_obstacles_cv(pin["obs_state0"].numpy(), pin["obs_LW"].numpy(), pin["obs_sigma"].numpy(), sc["kappa"])
+            Uh.copy_(pin["U0"])
+            hs.get_optimal_control_seq(pin["x0"].numpy(), Uh.numpy(), pin["poly"].numpy(), pin["xlp"].numpy(),
+                                       n_alphas=args.n_alphas, merit=merit, outputs=outs)
+
+        for _ in range(max(1, min(args.warmup, 3))):
+            e2e_step()
+        torch.cuda.synchronize()
+        if world > 1:
+            torch.distributed.barrier()
+        ksteps = max(1, min(args.steps, 10))
+        t0 = time.perf_counter()
+        for _ in range(ksteps):
+            e2e_step()
+        torch.cuda.synchronize()
+        dt = max_over_ranks(time.perf_counter() - t0, world, device)
+        h2d = 8 * (B * (4 + 2 * N + (p.poly_order + 1) + 2) + B * n_obs * 9)
+        d2h = 8 * B * (2 * N + 4 * (N + 1) + 1) + 4 * B * 2
+        assert np.array_equal(Uh.numpy(), U.cpu().numpy()), "host-buffer path and device-resident path disagree"
+        e2e = {"value": world * B * ksteps / dt, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+               "steps": ksteps, "path": "cilqr_set_obstacles_cv + cilqr_solve_batch with CILQR_MEM_HOST pinned buffers"}
+        hs.close()
+
+    if rank != 0:
+        solver.close()
+        if world > 1:
+            torch.distributed.destroy_process_group()
+        return
+
+    # ---- roofline of the dominant kernel + FP64 rate
+    mean_iters = float(iters.mean())
+    bytes_launch = B * solver_bytes_per_solve(N, n_obs)
+    achieved = bytes_launch / (kernel_ms * 1e-3) / 1e9
+    flops_launch = B * mean_iters * solver_flops_per_iteration(N, n_obs)
+    fp64_peak = C.c_double(0.0)
+    fp64 = None
+    if hasattr(lib, "cilqr_measure_fp64_peak") and lib.cilqr_measure_fp64_peak(C.byref(fp64_peak)) == 0:
+        tf = flops_launch / (kernel_ms * 1e-3) / 1e12
+        fp64 = {"achieved": tf, "peak": fp64_peak.value, "unit": "TFLOP/s", "frac": tf / fp64_peak.value,
+                "peak_source": "DFMA micro-benchmark on this GPU (cilqr_measure_fp64_peak)",
+                "flops_per_iteration": solver_flops_per_iteration(N, n_obs), "mean_iterations": mean_iters}
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic",
+        "config": {"workload": "config4: 65536 scenarios x 20 Gaussian-uncertain obstacles (covariance propagated on device), N=50, "
+                               "n_alphas=%d, per GPU" % args.n_alphas,
+                   "batch_per_gpu": B, "horizon": N, "n_obs": n_obs, "n_alphas": args.n_alphas, "parallelism": "scenario shards x%d" % world,
+                   "l2": "inputs larger than L2 (%.1f GB of obstacle records re-generated and re-read every step)" % (B * n_obs * 48 * N / 1e9),
+                   "collective": "all_gather U* (NCCL)" if world > 1 else "none"},
+        "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches),
+        "roofline": {"kernel": "solve_kernel<false>" if args.n_alphas == 1 else "solve_kernel<true>", "bound": "hbm", "achieved": achieved,
+                     "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": None, "peak_source": peak_kind,
+                     "kernel_ms": kernel_ms, "algorithmic_bytes_per_solve": solver_bytes_per_solve(N, n_obs),
+                     "note": "the solver is FP64-issue/latency bound, not HBM bound: see fp64"},
+        "fp64": fp64,
+        "solver": {"mean_iterations": mean_iters, "status_hist": {"tolerance": int((status == 0).sum()), "max_iter": int((status == 1).sum()),
+                                                                 "lamb_max": int((status == 2).sum()), "nonfinite": int((status == 3).sum())}},
+    }
+    solver.close()
+    if world > 1:
+        torch.distributed.destroy_process_group()
+    if not args.no_warp:
+        line["costmap_warp"] = bench_warp(args, device, hbm_peak, peak_kind)
+    if world == 1 and not args.no_cpu:
+        line["cpu_baseline"] = cpu_baseline_leg(p, args)
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference_arm(args)
+    else:
+        run_b200_arm(args)
+
+
+if __name__ == "__main__":
+    main()

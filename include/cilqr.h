@@ -101,6 +101,10 @@ const char *cilqr_last_error(void);
 /* Number of kernel launches issued by this library since load (bench.py's gpu_launches). */
 int64_t cilqr_launch_count(void);
 
+/* Measurement helper (no reference counterpart): FP64 FMA throughput of the current device in TFLOP/s, the denominator
+ * of the solver's FP64-pipe roofline fraction in bench.py. */
+int cilqr_measure_fp64_peak(double *tflops);
+
 /* Parameters::Parameters()  (Parameters.cpp:3-75) + iLQR ctor constants (iLQR.cpp:17-18). */
 int cilqr_params_default(cilqr_params *p);
 

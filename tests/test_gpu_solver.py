@@ -1,0 +1,289 @@
+"""GPU parity tests of the CILQR solver (run on the B200 box: pytest -m gpu).
+
+Every call goes through the C ABI of include/cilqr.h (via the ctypes host mirror).  The checker is the compiled
+reference itself (oracle/_ref, built from the unmodified sources; the prebuilt .so travels to the GPU box) where it
+exists, else the plain-C port; committed golden vectors generated from the reference are checked as well.
+
+Tolerance: BASELINE.json north_star — optimal control sequence and cost within 1e-9 relative in FP64."""
+import os
+
+import numpy as np
+import pytest
+
+import cilqr_b200
+from cilqr_b200 import scenarios
+from cilqr_b200.params import ST_TOLERANCE, ST_MAX_ITER, ST_LAMB_MAX
+
+pytestmark = pytest.mark.gpu
+HERE = os.path.dirname(os.path.abspath(__file__))
+TOL = 1e-9
+CASES = ["n50_obs3", "n50_obs0_curved", "n40_obs2_curved", "n50_obs10"]
+
+
+def rel(a, b):
+    a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
+    return float(np.max(np.abs(a - b)) / max(np.max(np.abs(b)), 1e-300))
+
+
+@pytest.fixture(scope="module")
+def gold():
+    return np.load(os.path.join(HERE, "golden", "solver_golden.npz"))
+
+
+def make_solver(p, sc, B, n_obs):
+    s = cilqr_b200.iLQR(p, max_batch=max(B, 1), max_obs=max(n_obs, 1))
+    if n_obs:
+        s.set_obstacles_dense(sc["dim"], sc["pos"])
+    return s
+
+
+def case_inputs(checker, gold, name):
+    N, n_obs, curved, B = (int(gold[name + "/" + k]) for k in ("horizon", "n_obs", "curved", "B"))
+    p = checker.params_default(horizon=N)
+    return p, scenarios.make_scenarios(p, 0, B, n_obs, curved=bool(curved)), n_obs, B
+
+
+# ------------------------------------------------------------------------------------------------ golden vectors
+@pytest.mark.parametrize("name", CASES)
+def test_solve_matches_reference_golden(checker, gold, name):
+    p, sc, n_obs, B = case_inputs(checker, gold, name)
+    s = make_solver(p, sc, B, n_obs)
+    U = sc["U0"].copy()
+    s.get_optimal_control_seq(sc["x0"], U, sc["poly"], sc["xlp"])
+    assert np.array_equal(s.iterations, gold[name + "/iters"])
+    for b in range(B):
+        assert rel(U[b], gold[name + "/U"][b]) < TOL
+        assert rel(s.X_result[b], gold[name + "/X"][b]) < TOL
+        assert abs(s.J_result[b] - gold[name + "/J"][b]) <= TOL * abs(gold[name + "/J"][b])
+    s.close()
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_stages_match_reference_golden(checker, gold, name):
+    p, sc, n_obs, B = case_inputs(checker, gold, name)
+    s = make_solver(p, sc, B, n_obs)
+    g = lambda k: np.tile(gold[name + "/stage/" + k], (B, 1))  # noqa: E731  (scenario 0's stage vectors in every slot)
+    sc0 = {k: np.tile(sc[k][0], (B,) + (1,) * (sc[k].ndim - 1)) for k in ("x0", "U0", "poly", "xlp")}
+    if n_obs:
+        s.set_obstacles_dense(np.tile(sc["dim"][0], (B, 1, 1)), np.tile(sc["pos"][0], (B, 1, 1)))
+    X0 = s.get_nominal_trajectory(sc0["x0"], sc0["U0"])
+    assert rel(X0, g("X0")) < 1e-12
+    lx, lxx = s.get_state_cost(g("X0"), sc0["poly"], sc0["xlp"])
+    assert rel(lx, g("l_x")) < 1e-11 and rel(lxx, g("l_xx")) < 1e-11
+    lu, luu = s.get_control_cost(g("X0"), sc0["U0"])
+    assert rel(lu, g("l_u")) < 1e-12 and rel(luu, g("l_uu")) < 1e-12
+    J = s.get_J(g("X0"), sc0["U0"], sc0["poly"], sc0["xlp"])
+    assert rel(J, np.full(B, float(gold[name + "/stage/J0"]))) < 1e-12
+    ok = s.backward_pass(g("X0"), sc0["U0"], sc0["poly"], sc0["xlp"], 1.0)
+    assert np.all(ok == 1) and rel(s.k, g("k")) < 1e-10 and rel(s.K, g("K")) < 1e-10
+    Xn, Un = s.forward_pass(g("X0"), sc0["U0"], g("k"), g("K"))
+    assert rel(Xn, g("X_new")) < 1e-12 and rel(Un, g("U_new")) < 1e-12
+    Xh, Uh = s.forward_pass(g("X0"), sc0["U0"], g("k"), g("K"), alpha=0.25)
+    assert rel(Xh, g("X_new_a025")) < 1e-12 and rel(Uh, g("U_new_a025")) < 1e-12
+    s.close()
+
+
+def test_alpha_extension_matches_reference_pinned_wrapper(checker, gold):
+    """n_alphas = 8 with the tracking merit, pinned on a wrapper that only calls reference functions."""
+    p = checker.params_default(horizon=50)
+    sc = scenarios.make_scenarios(p, 100, 3, 3)
+    s = make_solver(p, sc, 3, 3)
+    U = sc["U0"].copy()
+    s.get_optimal_control_seq(sc["x0"], U, sc["poly"], sc["xlp"], n_alphas=8, merit=cilqr_b200.MERIT_TRACKING)
+    for b in range(3):
+        assert int(s.iterations[b]) == int(gold["alpha8/%d/iters" % b])
+        assert rel(U[b], gold["alpha8/%d/U" % b]) < TOL
+        assert abs(s.J_result[b] - float(gold["alpha8/%d/J" % b])) < TOL * abs(float(gold["alpha8/%d/J" % b]))
+    s.close()
+
+
+# ------------------------------------------------------------------------------------------------ fresh seeded inputs vs the checker
+@pytest.mark.parametrize("n_obs,curved,first", [(0, False, 5000), (3, True, 6000), (20, False, 7000), (7, True, 8000)])
+def test_batched_solve_matches_checker(checker, n_obs, curved, first):
+    p = checker.params_default(horizon=50)
+    B = 48
+    sc = scenarios.make_scenarios(p, first, B, n_obs, curved=curved)
+    s = make_solver(p, sc, B, n_obs)
+    U = sc["U0"].copy()
+    s.get_optimal_control_seq(sc["x0"], U, sc["poly"], sc["xlp"])
+    flips = []
+    for b in range(B):
+        dim = sc["dim"][b] if n_obs else None
+        pos = sc["pos"][b] if n_obs else None
+        r = checker.solve(p, dim, pos, sc["x0"][b], sc["U0"][b], sc["poly"][b], sc["xlp"][b])
+        if int(s.iterations[b]) != r["iters"]:
+            flips.append(b)  # a discrete decision (accept test / arg-min) flipped by a last-ulp difference
+            continue
+        assert rel(U[b], r["U"]) < TOL, b
+        assert rel(s.X_result[b], r["X"]) < TOL, b
+        assert abs(s.J_result[b] - r["J"]) <= TOL * abs(r["J"]), b
+    assert flips == [], "branch flips in scenarios %s" % flips
+    st = np.asarray(s.status)
+    assert np.all((st == ST_TOLERANCE) | (st == ST_MAX_ITER) | (st == ST_LAMB_MAX))
+    s.close()
+
+
+@pytest.mark.parametrize("merit", [0, 1])
+def test_line_search_matches_port(port, merit):
+    """n_alphas = 8 (extension): parity with the plain-C port, which test_oracle_golden pins on reference functions."""
+    p = port.params_default(horizon=50)
+    B, n_obs = 24, 10
+    sc = scenarios.make_scenarios(p, 9000, B, n_obs, curved=True)
+    s = make_solver(p, sc, B, n_obs)
+    U = sc["U0"].copy()
+    s.get_optimal_control_seq(sc["x0"], U, sc["poly"], sc["xlp"], n_alphas=8, merit=merit)
+    r = port.solve_batch(p, B, n_obs, sc["dim"], sc["pos"], sc["x0"], sc["U0"], sc["poly"], sc["xlp"], n_alphas=8, merit=merit)
+    same = np.asarray(s.iterations) == r["iters"]
+    assert same.all(), np.nonzero(~same)
+    assert np.array_equal(np.asarray(s.status), r["status"])
+    for b in range(B):
+        assert rel(U[b], r["U"][b]) < TOL and abs(s.J_result[b] - r["J"][b]) <= TOL * abs(r["J"][b])
+    s.close()
+
+
+def test_covariance_inflated_obstacles_on_device_match_host_expansion(checker):
+    """cilqr_set_obstacles_cv (device-side constant-velocity prediction + covariance inflation) against the unmodified
+    Obstacle class fed with host-inflated per-timestep dimensions."""
+    p = checker.params_default(horizon=50)
+    B, n_obs = 32, 20
+    sc = scenarios.make_scenarios(p, 12000, B, n_obs)
+    s = cilqr_b200.iLQR(p, max_batch=B, max_obs=n_obs)
+    s.set_obstacles_cv(sc["obs_state0"], sc["obs_LW"], sc["obs_sigma"], sc["kappa"])
+    U = sc["U0"].copy()
+    s.get_optimal_control_seq(sc["x0"], U, sc["poly"], sc["xlp"])
+    for b in range(B):
+        r = checker.solve(p, sc["dim"][b], sc["pos"][b], sc["x0"][b], sc["U0"][b], sc["poly"][b], sc["xlp"][b])
+        assert int(s.iterations[b]) == r["iters"], b
+        assert rel(U[b], r["U"]) < TOL and abs(s.J_result[b] - r["J"]) <= TOL * abs(r["J"])
+    s.close()
+
+
+def test_warm_start_is_carried_unshifted_like_the_reference(checker):
+    """run_step twice: the second solve starts from the first one's U (iLQR.cpp:201,222,253)."""
+    p = checker.params_default(horizon=50)
+    sc = scenarios.make_scenarios(p, 300, 4, 3)
+    s = make_solver(p, sc, 4, 3)
+    U = sc["U0"].copy()
+    s.get_optimal_control_seq(sc["x0"], U, sc["poly"], sc["xlp"])
+    x1 = np.asarray(s.X_result)[:, 4:8].copy()  # the state one step ahead
+    U2 = U.copy()
+    s.get_optimal_control_seq(x1, U2, sc["poly"], sc["xlp"])
+    for b in range(4):
+        r1 = checker.solve(p, sc["dim"][b], sc["pos"][b], sc["x0"][b], sc["U0"][b], sc["poly"][b], sc["xlp"][b])
+        r2 = checker.solve(p, sc["dim"][b], sc["pos"][b], r1["X"][4:8], r1["U"], sc["poly"][b], sc["xlp"][b])
+        assert int(s.iterations[b]) == r2["iters"] and rel(U2[b], r2["U"]) < TOL
+    s.close()
+
+
+def test_run_step_matches_reference_golden(checker, gold):
+    p = checker.params_default(horizon=50)
+    s = cilqr_b200.iLQR(p, max_batch=1, max_obs=0)
+    s.set_global_plan(np.stack([np.arange(200, dtype=np.float64), np.zeros(200)], axis=1))
+    X, U = s.run_step(np.array([0.3, 0.2, 4.0, 0.01]))
+    assert rel(U[0], gold["run_step/U"]) < 1e-7  # looser: the polynomial fit feeds in at ~1e-12 and the solve amplifies it
+    assert rel(X[0], gold["run_step/X"]) < 1e-7
+    s.close()
+
+
+# ------------------------------------------------------------------------------------------------ memory spaces, edge cases, errors
+def test_device_resident_and_host_buffers_give_identical_bits():
+    import torch
+    p = cilqr_b200.Parameters()
+    cilqr_b200.load_library().cilqr_params_default(__import__("ctypes").byref(p))
+    p = p.replace(horizon=50)
+    B, n_obs = 257, 5  # not a multiple of the warps per CTA
+    sc = scenarios.make_scenarios(p, 0, B, n_obs, curved=True)
+    s = make_solver(p, sc, B, n_obs)
+    Uh = sc["U0"].copy()
+    s.get_optimal_control_seq(sc["x0"], Uh, sc["poly"], sc["xlp"])
+    Xh, Jh, ih = s.X_result.copy(), s.J_result.copy(), s.iterations.copy()
+    dev = torch.device("cuda:0")
+    t = {k: torch.from_numpy(sc[k]).to(dev) for k in ("x0", "U0", "poly", "xlp", "dim", "pos")}
+    s.set_obstacles_dense(t["dim"], t["pos"])
+    Ud = t["U0"].clone()
+    s.get_optimal_control_seq(t["x0"], Ud, t["poly"], t["xlp"])
+    torch.cuda.synchronize()
+    assert np.array_equal(Ud.cpu().numpy(), Uh) and np.array_equal(s.X_result.cpu().numpy(), Xh)
+    assert np.array_equal(s.J_result.cpu().numpy(), Jh) and np.array_equal(s.iterations.cpu().numpy(), ih)
+    s.close()
+
+
+def test_edge_cases_and_error_codes(checker):
+    p = checker.params_default(horizon=50)
+    sc = scenarios.make_scenarios(p, 0, 4, 2)
+    s = cilqr_b200.iLQR(p, max_batch=4, max_obs=2)
+    # empty batch is a no-op
+    U = np.zeros((0, 100))
+    s.get_optimal_control_seq(np.zeros((0, 4)), U, np.zeros((0, 6)), np.zeros((0, 2)))
+    # batch larger than the handle was created for
+    big = scenarios.make_scenarios(p, 0, 5, 0)
+    with pytest.raises(cilqr_b200.CilqrError, match="batch"):
+        s.get_optimal_control_seq(big["x0"], big["U0"].copy(), big["poly"], big["xlp"])
+    # more obstacles than max_obs
+    sc3 = scenarios.make_scenarios(p, 0, 4, 3)
+    with pytest.raises(cilqr_b200.CilqrError, match="n_obs"):
+        s.set_obstacles_dense(sc3["dim"], sc3["pos"])
+    # obstacles set for another batch size
+    s.set_obstacles_dense(sc["dim"][:2], sc["pos"][:2])
+    with pytest.raises(cilqr_b200.CilqrError, match="obstacles were set"):
+        s.get_optimal_control_seq(sc["x0"], sc["U0"].copy(), sc["poly"], sc["xlp"])
+    # clear_Obstacle() -> the obstacle-free solve
+    s.clear_Obstacle()
+    U = sc["U0"].copy()
+    s.get_optimal_control_seq(sc["x0"], U, sc["poly"], sc["xlp"])
+    r = checker.solve(p, None, None, sc["x0"][0], sc["U0"][0], sc["poly"][0], sc["xlp"][0])
+    assert int(s.iterations[0]) == r["iters"] and rel(U[0], r["U"]) < TOL
+    with pytest.raises(cilqr_b200.CilqrError, match="n_alphas"):
+        s.get_optimal_control_seq(sc["x0"], sc["U0"].copy(), sc["poly"], sc["xlp"], n_alphas=9)
+    s.close()
+
+
+@pytest.mark.parametrize("horizon", [1, 7, 33, 64, 100])
+def test_other_horizons(checker, horizon):
+    p = checker.params_default(horizon=horizon)
+    B, n_obs = 6, 2
+    sc = scenarios.make_scenarios(p, 40, B, n_obs, curved=True)
+    s = make_solver(p, sc, B, n_obs)
+    U = sc["U0"].copy()
+    s.get_optimal_control_seq(sc["x0"], U, sc["poly"], sc["xlp"])
+    for b in range(B):
+        r = checker.solve(p, sc["dim"][b], sc["pos"][b], sc["x0"][b], sc["U0"][b], sc["poly"][b], sc["xlp"][b])
+        assert int(s.iterations[b]) == r["iters"] and rel(U[b], r["U"]) < TOL and rel(s.X_result[b], r["X"]) < TOL
+    s.close()
+
+
+# ------------------------------------------------------------------------------------------------ full BASELINE sizes: size-independent properties
+def test_full_size_properties_config4_shard(checker):
+    """One rank's shard of config 4 (65 536 / 8 = 8 192 scenarios, 20 uncertain obstacles): determinism, independence of
+    batch composition (the property rank-sharding relies on), status histogram, and a sample against the checker."""
+    import torch
+    p = checker.params_default(horizon=50)
+    B, n_obs = 8192, 20
+    sc = scenarios.make_scenarios(p, 0, B, n_obs, dense=False)
+    dev = torch.device("cuda:0")
+    t = {k: torch.from_numpy(sc[k]).to(dev) for k in ("x0", "U0", "poly", "xlp", "obs_state0", "obs_LW", "obs_sigma")}
+    s = cilqr_b200.iLQR(p, max_batch=B, max_obs=n_obs)
+    s.set_obstacles_cv(t["obs_state0"], t["obs_LW"], t["obs_sigma"], sc["kappa"])
+    U1 = t["U0"].clone()
+    s.get_optimal_control_seq(t["x0"], U1, t["poly"], t["xlp"])
+    J1, it1, st1 = s.J_result.clone(), s.iterations.clone(), s.status.clone()
+    U2 = t["U0"].clone()
+    s.get_optimal_control_seq(t["x0"], U2, t["poly"], t["xlp"])
+    assert torch.equal(U1, U2) and torch.equal(J1, s.J_result) and torch.equal(it1, s.iterations)  # deterministic
+    # a sub-batch taken from the middle gives the same bits as inside the full batch
+    lo, hi = 3000, 3512
+    s.set_obstacles_cv(t["obs_state0"][lo:hi].contiguous(), t["obs_LW"][lo:hi].contiguous(), t["obs_sigma"][lo:hi].contiguous(), sc["kappa"])
+    U3 = t["U0"][lo:hi].clone()
+    s.get_optimal_control_seq(t["x0"][lo:hi].contiguous(), U3, t["poly"][lo:hi].contiguous(), t["xlp"][lo:hi].contiguous())
+    assert torch.equal(U3, U1[lo:hi]) and torch.equal(s.J_result, J1[lo:hi])
+    hist = np.bincount(st1.cpu().numpy(), minlength=4)
+    assert hist.sum() == B and hist[3] == 0
+    assert torch.isfinite(U1).all() and torch.isfinite(J1).all()
+    assert int(it1.min()) >= 1 and int(it1.max()) <= p.max_iterations
+    Uh, Jh, ih = U1.cpu().numpy(), J1.cpu().numpy(), it1.cpu().numpy()
+    for b in range(0, B, B // 32):
+        dim, pos = scenarios.expand_obstacles_cv(p, sc["obs_state0"][b], sc["obs_LW"][b], sc["obs_sigma"][b], sc["kappa"])
+        r = checker.solve(p, dim, pos, sc["x0"][b], sc["U0"][b], sc["poly"][b], sc["xlp"][b])
+        assert int(ih[b]) == r["iters"], b
+        assert rel(Uh[b], r["U"]) < TOL and abs(Jh[b] - r["J"]) <= TOL * abs(r["J"]), b
+    s.close()

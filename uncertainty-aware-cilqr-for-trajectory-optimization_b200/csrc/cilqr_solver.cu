@@ -67,6 +67,22 @@ __global__ void prep_obstacles_cv_kernel(DevParams P, size_t n_bj, const double 
     }
 }
 
+// ------------------------------------------------------------------------------------------------- FP64 roofline probe
+// 8 independent DFMA chains per thread: the denominator of the solver's FP64-pipe fraction, measured on the GPU the
+// bench runs on.
+__global__ void __launch_bounds__(256) fp64_peak_kernel(double *out, int iters, double seed)
+{
+    double a0 = seed + threadIdx.x, a1 = a0 + 1, a2 = a0 + 2, a3 = a0 + 3, a4 = a0 + 4, a5 = a0 + 5, a6 = a0 + 6, a7 = a0 + 7;
+    const double m = 0.999999, c = 1e-9;
+    for (int i = 0; i < iters; ++i) {
+        a0 = fma(a0, m, c); a1 = fma(a1, m, c); a2 = fma(a2, m, c); a3 = fma(a3, m, c);
+        a4 = fma(a4, m, c); a5 = fma(a5, m, c); a6 = fma(a6, m, c); a7 = fma(a7, m, c);
+    }
+    const double r = ((a0 + a1) + (a2 + a3)) + ((a4 + a5) + (a6 + a7));
+    if (r == 12345.678)
+        out[0] = r; // never true: keeps the chains alive
+}
+
 // ------------------------------------------------------------------------------------------------- fused solve
 struct SolveArgs {
     DevParams P;
@@ -421,6 +437,37 @@ int cilqr_sizeof_params(void) { return (int)sizeof(cilqr_params); }
 int cilqr_sizeof_geom(void) { return (int)sizeof(costmap_geom); }
 const char *cilqr_last_error(void) { return g_err; }
 int64_t cilqr_launch_count(void) { return (int64_t)g_launches.load(); }
+
+int cilqr_measure_fp64_peak(double *tflops)
+{
+    if (!tflops) return fail(CILQR_E_ARG, "null argument");
+    int dev = 0, sms = 0;
+    CILQR_CUDA(cudaGetDevice(&dev));
+    CILQR_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    double *d = nullptr;
+    CILQR_CUDA(cudaMalloc(&d, sizeof(double)));
+    cudaEvent_t e0, e1;
+    CILQR_CUDA(cudaEventCreate(&e0));
+    CILQR_CUDA(cudaEventCreate(&e1));
+    const int iters = 1 << 14, grid = sms * 8, block = 256;
+    double best = 0.0;
+    for (int rep = 0; rep < 4; ++rep) { // first repetition warms up
+        CILQR_CUDA(cudaEventRecord(e0, 0));
+        fp64_peak_kernel<<<grid, block>>>(d, iters, 1.0 + rep);
+        g_launches.fetch_add(1, std::memory_order_relaxed);
+        CILQR_CUDA(cudaEventRecord(e1, 0));
+        CILQR_CUDA(cudaEventSynchronize(e1));
+        float ms = 0.f;
+        CILQR_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+        const double tf = 2.0 * 8.0 * iters * (double)grid * block / (ms * 1e-3) / 1e12;
+        if (rep > 0 && tf > best) best = tf;
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaFree(d);
+    *tflops = best;
+    return 0;
+}
 
 int cilqr_params_default(cilqr_params *p)
 {

@@ -200,9 +200,11 @@ __global__ void __launch_bounds__(kWarpThreads) warp_tma_kernel(const __grid_con
             lo0 = min(lo0, source_index(px, G.hLx, G.Psx, G.r_s, G.rinv_s));
             lo1 = min(lo1, source_index(py, G.hLy, G.Psy, G.r_s, G.rinv_s));
         }
-        // keep the box origin a multiple of 4 elements is not required by TMA (only the global stride is), so use min-1
-        lo0 -= 1;
-        lo1 -= 1;
+        // The truncating index map is monotone per axis, so the corner minimum is the exact lower bound and the tile
+        // spans at most ceil(63*sqrt(2)) + 1 = 91 source cells per axis.  TMA needs the innermost start coordinate on a
+        // 16-byte boundary (a misaligned one raises "illegal instruction", measured on B200): round index 0 down to a
+        // multiple of 4 floats (two's complement: also correct for negative, out-of-map coordinates) -> <= 94 <= kBox.
+        lo0 &= ~3;
         s_box[0] = lo0;
         s_box[1] = lo1;
         const unsigned bytes = kBox * kBox * sizeof(float);

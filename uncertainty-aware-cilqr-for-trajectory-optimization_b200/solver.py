@@ -274,9 +274,11 @@ class iLQR:
         return Xn, Un
 
     # ------------------------------------------------------------------ driver (iLQR.cpp:201-245)
-    def get_optimal_control_seq(self, x_0, U, poly_coeffs, x_local_plan, n_alphas=1, merit=0, want=("X", "J", "iters", "status")):
+    def get_optimal_control_seq(self, x_0, U, poly_coeffs, x_local_plan, n_alphas=1, merit=0, want=("X", "J", "iters", "status"),
+                                outputs=None):
         """U is updated IN PLACE (it is the reference's `Eigen::MatrixXd &U`); results in X_result, U_result,
-        J_result, iterations, status."""
+        J_result, iterations, status.  `outputs` may hold preallocated result arrays ("X", "J", "iters", "status"),
+        e.g. pinned host buffers."""
         a = _Arg()
         B, N = self._batch(x_0), self.params.horizon
         px = a.inp(x_0)
@@ -292,10 +294,21 @@ class iLQR:
         pp, pl = a.inp(poly_coeffs), a.inp(x_local_plan)
         dev = a.mem == MEM_DEVICE
         d = getattr(x_0, "device", None)
-        X, pX = a.out((B, 4 * (N + 1)), np.float64, dev, d) if "X" in want else (None, None)
-        J, pJ = a.out((B,), np.float64, dev, d) if "J" in want else (None, None)
-        it, pit = a.out((B,), np.int32, dev, d) if "iters" in want else (None, None)
-        stt, pst = a.out((B,), np.int32, dev, d) if "status" in want else (None, None)
+        def result(name, shape, dtype):
+            if outputs is not None and name in outputs:
+                o = outputs[name]
+                if _is_torch(o):
+                    return o, a.inp(o, dtype)
+                if not (isinstance(o, np.ndarray) and o.dtype == dtype and o.flags.c_contiguous and o.size == int(np.prod(shape))):
+                    raise ValueError("outputs[%r] must be a C-contiguous %s array of %d elements" % (name, np.dtype(dtype).name, int(np.prod(shape))))
+                a._set_mem(MEM_HOST)
+                return o, C.c_void_p(o.ctypes.data)
+            return a.out(shape, dtype, dev, d) if name in want else (None, None)
+
+        X, pX = result("X", (B, 4 * (N + 1)), np.float64)
+        J, pJ = result("J", (B,), np.float64)
+        it, pit = result("iters", (B,), np.int32)
+        stt, pst = result("status", (B,), np.int32)
         _check(self.lib.cilqr_solve_batch(self._h, C.c_int(B), px, pU, pp, pl, C.c_int(n_alphas), C.c_int(merit), pX, pJ, pit, pst,
                                           C.c_int(a.mem), a.stream_ptr()))
         self.X_result, self.U_result, self.J_result, self.iterations, self.status = X, Uarr, J, it, stt
