@@ -2,16 +2,26 @@
 //
 // Replaces the per-cell loop of LocalCostmap::odomCallback (CILQR/src/map_engine/src/local_costmap.cpp:242-264),
 // which walks a grid_map::GridMapIterator, rotates each cell centre by the ego pose and reads the global map
-// through GridMap::atPosition.  The index arithmetic of grid_map_core (src/GridMapMath.cpp:114-157, GridMap.cpp:45-62)
-// is reproduced operation by operation with explicitly rounded FP64 intrinsics (no FMA contraction), so the
-// source-index map is bit-identical to the reference's; the payload is a 4-byte copy, which makes the kernel
-// HBM-bound: 4 B read + 4 B written per cell (+ 4 B when the index map is emitted).
+// through GridMap::atPosition.  The payload is a 4-byte copy, so the kernel is meant to be HBM-bound: 4 B read +
+// 4 B written per cell (+ 4 B when the index map is emitted).
 //
-// Two kernels, same arithmetic:
+// Bit-exact index maps at copy speed
+//   The reference's index is a chain of separately rounded FP64 operations (grid_map_core/src/GridMapMath.cpp:114-157,
+//   GridMap.cpp:45-62) followed by a truncation.  Evaluating that chain per cell costs ~80 instructions and made the
+//   first version of this kernel issue-bound (profiles/r01a_full.txt).  Now: the map (i, j) -> source coordinate is
+//   affine up to those roundings, so each tile evaluates it in 7.25 fixed point relative to the tile's source bounding
+//   box (32-bit integer adds: the integer part IS the index, the fraction says how far the cell centre is from a
+//   source-cell border).  Whenever the fraction is within 2^-17 cell of a border — where the reference's own roundings could decide the truncation — the cell is
+//   re-evaluated with the exact chain (__dmul_rn/__dadd_rn/__dsub_rn/__ddiv_rn, no FMA contraction, both subtraction
+//   orders of GridMapMath.cpp:139 vs :150).  The predictor's total error is bounded by 2^-18.8 cell (derivation at
+//   tile_setup), so both paths give the reference's integer; tests compare every cell of 10^7..10^8-cell maps.
+//
+// Two kernels, same index code:
 //   warp_direct_kernel : 64x64-cell target tile per CTA, gathers straight from global/L2 through the read-only path.
 //   warp_tma_kernel    : one elected thread issues a TMA tile load (cp.async.bulk.tensor.2d + mbarrier) of the
 //                        bounding box of the tile's rotated footprint in the source map into shared memory
-//                        (out-of-map elements are NaN-filled by the TMA unit); cells are gathered from smem.
+//                        (out-of-map elements are NaN-filled by the TMA unit); cells are gathered from smem with a
+//                        lane mapping / row pitch chosen for few bank conflicts at every rotation angle.
 // Both write 128-bit vectors along index 0 (the contiguous direction of grid_map's column-major layers).
 #include "common.cuh"
 #include <cuda.h>
@@ -22,9 +32,15 @@
 
 namespace cilqr
 {
-constexpr int kTile = 64;        // target tile edge (cells)
-constexpr int kBox = 96;         // TMA box edge (source cells): ceil(64*sqrt(2)) + margins, multiple of 4
+constexpr int kTile = 64;         // target tile edge (cells)
+constexpr int kBoxW = 108;        // TMA box, index-0 extent (floats): >= 91 + 3 (16-byte alignment); 108 = 12 mod 32 keeps
+                                  // the rotated gather at ~2.7 shared-memory wavefronts per warp load (96 gave 3.4+, worst 16)
+constexpr int kBoxH = 92;         // TMA box, index-1 extent: ceil(63*sqrt(2)) + 2
 constexpr int kWarpThreads = 256;
+constexpr int kFrac = 25;                        // 7.25 unsigned fixed point: box-local source coordinates are < 108 < 2^7
+constexpr unsigned kFracMask = (1u << kFrac) - 1;
+constexpr unsigned kDelta = 1u << (kFrac - 17);  // 2^-17 cell: fractions closer than this to a source-cell border go exact
+constexpr double kMaxCells = 33554432.0;         // 2^25: coordinate magnitude (in source cells) up to which the predictor bound holds
 
 struct WarpGeom {
     int rows_t, cols_t, rows_s, cols_s;
@@ -32,6 +48,8 @@ struct WarpGeom {
     double base_x, base_y, r_t;                 // target: position + (0.5*length - 0.5*resolution), resolution
     double hLx, hLy, Psx, Psy, r_s, rinv_s;     // source: 0.5*length, position, resolution, 1/resolution
     double Lx, Ly;                              // source length (size*resolution)
+    double ratio;                               // r_t / r_s
+    double mag;                                 // (|base| + target extent + |0.5 L_s| + |P_s|) / r_s, pose offset added per CTA
 };
 
 // getPositionFromIndex (GridMapMath.cpp:114-127): position = (mapPosition + offset) + resolution * (-index).
@@ -40,41 +58,57 @@ __device__ __forceinline__ double cell_centre(double base, double r, int index)
     return __dadd_rn(base, __dmul_rn(r, -(double)index));
 }
 
-// One coordinate of getIndexFromPosition (GridMapMath.cpp:129-142): (int)( -(((p - 0.5*L) - P) / r) ), C++ truncation.
-// Fast path: multiply by 1/r and take the integer part with the 2^52 trick; whenever the product is within 2^-23 of
-// an integer (where the last-ulp difference between n*(1/r) and n/r could change the truncation) or negative, the
-// exact IEEE division is evaluated instead, so the result always equals the reference's.
-__device__ __forceinline__ int source_index(double p, double hL, double Ps, double r, double rinv)
+// One coordinate of getIndexFromPosition (GridMapMath.cpp:129-142): (int)( -(((p - 0.5*L) - P) / r) ), C++ truncation,
+// evaluated exactly as the reference does (IEEE division).
+__device__ __noinline__ int source_index_exact(double p, double hL, double Ps, double r)
 {
-    const double n = __dsub_rn(__dsub_rn(p, hL), Ps);
-    const double t = -__dmul_rn(n, rinv);
-    const double magic = 6755399441055744.0; // 2^52 + 2^51
-    const double tm = __dadd_rn(t, magic);
-    const double d = __dsub_rn(t, __dsub_rn(tm, magic)); // t - nearest integer, exact
-    const int hi = __double2hiint(d);
-    const bool near_int = (hi & 0x7fffffff) < 0x3E800000; // |d| < 2^-23 (also d == 0)
-    if (near_int || t < 0.0 || !(t < 2.0e9))
-        return __double2int_rz(-__ddiv_rn(n, r));
-    return __double2loint(tm) - (hi < 0 ? 1 : 0); // floor(t) for t >= 0
+    const double t = -__ddiv_rn(__dsub_rn(__dsub_rn(p, hL), Ps), r);
+    if (!(fabs(t) < 2.0e9))
+        return t < 0.0 ? INT_MIN : INT_MAX; // NaN / out of int range: invalid either way
+    return __double2int_rz(t);
+}
+
+__device__ __noinline__ int source_floor_exact(double p, double hL, double Ps, double r)
+{
+    const double t = -__ddiv_rn(__dsub_rn(__dsub_rn(p, hL), Ps), r);
+    if (!(fabs(t) < 2.0e9))
+        return t < 0.0 ? INT_MIN : INT_MAX;
+    return __double2int_rd(t);
 }
 
 // checkIfPositionWithinMap (GridMapMath.cpp:144-157) && checkIfIndexInRange (:191-198).  Note the different
 // subtraction order ((p - P) - 0.5*L) from the index computation.
-__device__ __forceinline__ bool source_valid(const WarpGeom &G, double px, double py, int g0, int g1)
+__device__ __forceinline__ bool source_valid_exact(const WarpGeom &G, double px, double py, int g0, int g1)
 {
-    if (g0 >= 1 && g1 >= 1 && g0 <= G.rows_s - 2 && g1 <= G.cols_s - 2)
-        return true; // a whole cell away from every border: the position test cannot fail
     const double qx = -__dsub_rn(__dsub_rn(px, G.Psx), G.hLx), qy = -__dsub_rn(__dsub_rn(py, G.Psy), G.hLy);
     return qx >= 0.0 && qy >= 0.0 && qx < G.Lx && qy < G.Ly && g0 >= 0 && g1 >= 0 && g0 < G.rows_s && g1 < G.cols_s;
 }
 
-struct TileTerms {
-    double rowC[kTile], rowS[kTile], colS[kTile], colC[kTile];
+struct TileShared {
+    double rowC[kTile], rowS[kTile], colS[kTile], colC[kTile]; // Cx*cos, Cx*sin, Cy*sin, Cy*cos: one rounded multiply each
+    unsigned Tx0, Ty0;    // 7.25 fixed-point source coordinate of tile cell (0,0), relative to (org0, org1)
+    int org0, org1;       // origin of the tile's source bounding box (org0 is a multiple of 4)
+    int exact_only;       // predictor bound does not hold for this pose/geometry: every cell takes the exact chain
+    int inside;           // the whole bounding box lies inside the source map: no validity tests needed
 };
 
-// Cx*cos, Cx*sin per tile row and Cy*sin, Cy*cos per tile column (local_costmap.cpp:249-250); each is one rounded
-// multiply in the reference as well, so sharing them across the tile does not change a single bit.
-__device__ __forceinline__ void fill_tile_terms(const WarpGeom &G, TileTerms &T, int i0, int j0, double sn, double cn, int tid)
+__device__ __forceinline__ void cell_position(const TileShared &T, int li, int lj, double Vx, double Vy, double &px, double &py)
+{
+    px = __dadd_rn(__dsub_rn(T.rowC[li], T.colS[lj]), Vx); // (Cx*cos - Cy*sin) + Vx     local_costmap.cpp:249
+    py = __dadd_rn(__dadd_rn(T.rowS[li], T.colC[lj]), Vy); // (Cx*sin + Cy*cos) + Vy     local_costmap.cpp:250
+}
+
+// Per-tile setup.  Threads 0..127 fill the shared row/column products (identical bits to the reference: each is a single
+// rounded multiply there as well); thread 0 then derives the bounding-box origin from the exact indices of the four tile
+// corners (floor of the reference's coordinate is monotone per axis, so the corner minimum is the exact lower bound and the tile
+// spans at most ceil(63*sqrt(2)) + 1 = 91 source cells per axis) and the fixed-point start value.
+//
+// Predictor error budget (source cells).  The reference's t(i,j) differs from the exact affine map by at most
+// ~8 roundings of magnitude <= M = (|coordinates|)/r_s, i.e. 8 * 2^-53 * M.  The predictor starts from the reference's own
+// t at tile cell (0,0) (same bound, floored to 2^-25), and adds li*A + lj*B with A, B rounded to 2^-26 each:
+// <= 126 * 2^-26 + 2^-25 < 2^-18.9.  For M < 2^25 cells the total is < 2^-18.9 + 2^-24 < 2^-18.8, under 30 % of the 2^-17
+// guard band; about 3e-5 of all cells fall in the band and are recomputed exactly.
+__device__ __forceinline__ void tile_setup(const WarpGeom &G, TileShared &T, int i0, int j0, double Vx, double Vy, double sn, double cn, int tid)
 {
     if (tid < kTile) {
         const double Cx = cell_centre(G.base_x, G.r_t, i0 + tid);
@@ -86,50 +120,135 @@ __device__ __forceinline__ void fill_tile_terms(const WarpGeom &G, TileTerms &T,
         T.colS[q] = __dmul_rn(Cy, sn);
         T.colC[q] = __dmul_rn(Cy, cn);
     }
+    __syncthreads();
+    if (tid == 0) {
+        const int li1 = min(kTile, G.rows_t - i0) - 1, lj1 = min(kTile, G.cols_t - j0) - 1;
+        int lo0 = INT_MAX, lo1 = INT_MAX, hi0 = INT_MIN, hi1 = INT_MIN;
+#pragma unroll 1
+        for (int cnr = 0; cnr < 4; ++cnr) {
+            double px, py;
+            cell_position(T, (cnr & 1) ? li1 : 0, (cnr & 2) ? lj1 : 0, Vx, Vy, px, py);
+            // FLOOR of the reference's coordinate (its index truncates toward zero, which is not monotone below zero)
+            const int g0 = source_floor_exact(px, G.hLx, G.Psx, G.r_s), g1 = source_floor_exact(py, G.hLy, G.Psy, G.r_s);
+            lo0 = min(lo0, g0); hi0 = max(hi0, g0);
+            lo1 = min(lo1, g1); hi1 = max(hi1, g1);
+        }
+        const double mag = G.mag + (fabs(Vx) + fabs(Vy)) * G.rinv_s;
+        bool exact_only = !(mag < kMaxCells) || !(G.ratio <= 1.0 + 1e-9);
+        // TMA needs the innermost start coordinate on a 16-byte boundary (a misaligned one raises "illegal instruction",
+        // measured on B200): round index 0 down to a multiple of 4 floats (two's complement: right for negatives too).
+        if (!exact_only) {
+            lo0 &= ~3;
+            exact_only = (long long)hi0 - lo0 >= kBoxW || (long long)hi1 - lo1 >= kBoxH;
+        }
+        if (exact_only) { lo0 = 0; lo1 = 0; }
+        double px, py;
+        cell_position(T, 0, 0, Vx, Vy, px, py);
+        const double tx = -__ddiv_rn(__dsub_rn(__dsub_rn(px, G.hLx), G.Psx), G.r_s), ty = -__ddiv_rn(__dsub_rn(__dsub_rn(py, G.hLy), G.Psy), G.r_s);
+        T.Tx0 = exact_only ? 0u : (unsigned)__double2ll_rd((tx - (double)lo0) * (double)(1u << kFrac));
+        T.Ty0 = exact_only ? 0u : (unsigned)__double2ll_rd((ty - (double)lo1) * (double)(1u << kFrac));
+        T.org0 = lo0;
+        T.org1 = lo1;
+        T.exact_only = exact_only ? 1 : 0;
+        T.inside = (!exact_only && lo0 >= 0 && lo1 >= 0 && lo0 + kBoxW <= G.rows_s && lo1 + kBoxH <= G.cols_s) ? 1 : 0;
+    }
+    __syncthreads();
 }
 
-__device__ __forceinline__ void cell_position(const TileTerms &T, int li, int lj, double Vx, double Vy, double &px, double &py)
+// The reference's own arithmetic for one cell (used for the few cells within 2^-20 cell of a source-cell border, and for
+// every cell when the predictor bound does not hold).
+struct CellResult {
+    float v;
+    int gidx;
+};
+__device__ __forceinline__ CellResult exact_cell(const WarpGeom &G, const TileShared &T, const float *__restrict__ src, int li, int lj, double Vx, double Vy)
 {
-    px = __dadd_rn(__dsub_rn(T.rowC[li], T.colS[lj]), Vx); // (Cx*cos - Cy*sin) + Vx
-    py = __dadd_rn(__dadd_rn(T.rowS[li], T.colC[lj]), Vy); // (Cx*sin + Cy*cos) + Vy
+    float v;
+    int gidx;
+    double px, py;
+    cell_position(T, li, lj, Vx, Vy, px, py);
+    const int g0 = source_index_exact(px, G.hLx, G.Psx, G.r_s), g1 = source_index_exact(py, G.hLy, G.Psy, G.r_s);
+    const bool ok = source_valid_exact(G, px, py, g0, g1);
+    gidx = ok ? g0 + G.rows_s * g1 : -1;
+    v = ok ? __ldg(src + gidx) : __int_as_float(0x7fc00000); // the reference throws for out-of-map cells (GridMap.cpp:160-166)
+    return CellResult{v, gidx};
 }
 
-template <bool TMA>
-__device__ __forceinline__ void warp_tile_body(const WarpGeom &G, const TileTerms &T, const float *__restrict__ src, const float *sbox,
-                                               int box0, int box1, double Vx, double Vy, int i0, int j0, const float *__restrict__ bbox,
+// Overwrites the cells of one quad flagged in `unc` with exactly evaluated ones (same thread wrote the fast-path values just
+// before, so program order makes these stores win).
+__device__ __noinline__ void fixup_exact(const WarpGeom &G, const TileShared &T, const float *__restrict__ src, unsigned unc, int li0, int lj, int i,
+                                         size_t l, double Vx, double Vy, const float *__restrict__ bbox, float *__restrict__ out,
+                                         int32_t *__restrict__ idx)
+{
+    for (int e = 0; e < 4; ++e) {
+        if (!((unc >> e) & 1u) || i + e >= G.rows_t)
+            continue;
+        const CellResult r = exact_cell(G, T, src, li0 + e, lj, Vx, Vy);
+        float val = r.v;
+        if (bbox) {
+            const float b = bbox[l + e];
+            if (b > 90.f) val = b;
+        }
+        out[l + e] = val;
+        if (idx) idx[l + e] = r.gidx;
+    }
+}
+
+template <bool TMA, bool INSIDE>
+__device__ __forceinline__ void warp_tile_body(const WarpGeom &G, const TileShared &T, const float *__restrict__ src, const float *sbox, double Vx,
+                                               double Vy, double sn, double cn, int i0, int j0, const float *__restrict__ bbox,
                                                float *__restrict__ out, int32_t *__restrict__ idx, int tid)
 {
     const bool vec_ok = (G.rows_t & 3) == 0; // 16-byte aligned quads along index 0
     const float qnan = __int_as_float(0x7fc00000);
-    for (int item = tid; item < (kTile / 4) * kTile; item += kWarpThreads) {
-        const int lq = item % (kTile / 4), lj = item / (kTile / 4);
+    // d(source coordinate)/d(target index) in 7.25 fixed point (wrapping unsigned arithmetic): Cx = base - r_t*i,
+    // Cy = base - r_t*j, p = R(theta) C + V, t = -(p - ..)/r_s
+    const double sc = G.ratio * (double)(1u << kFrac);
+    const unsigned Axi = (unsigned)__double2int_rn(sc * cn), Axj = (unsigned)__double2int_rn(-sc * sn);
+    const unsigned Ayi = (unsigned)__double2int_rn(sc * sn), Ayj = Axi;
+    const int warp = tid >> 5, lane = tid & 31;
+    const int org0 = T.org0, org1 = T.org1;
+    const int gbase = org1 * G.rows_s + org0;
+    const bool exact_only = T.exact_only != 0;
+    unsigned unc_all = 0;
+    // lane mapping: 4 quads (16 cells along index 0) x 8 rows per warp instruction — compact in the source for every rotation
+#pragma unroll 1
+    for (int k = 0; k < 4; ++k) {
+        const int wi = warp + 8 * k;
+        const int lq = 4 * (wi & 3) + (lane & 3), lj = 8 * (wi >> 2) + (lane >> 2);
         const int i = i0 + 4 * lq, j = j0 + lj;
         if (j >= G.cols_t || i >= G.rows_t)
             continue;
         float v[4];
         int gidx[4];
+        unsigned unc = exact_only ? 0xFu : 0u;
+        if (!exact_only) {
+            unsigned tx = T.Tx0 + (unsigned)(4 * lq) * Axi + (unsigned)lj * Axj;
+            unsigned ty = T.Ty0 + (unsigned)(4 * lq) * Ayi + (unsigned)lj * Ayj;
 #pragma unroll
-        for (int e = 0; e < 4; ++e) {
-            double px, py;
-            cell_position(T, 4 * lq + e, lj, Vx, Vy, px, py);
-            const int g0 = source_index(px, G.hLx, G.Psx, G.r_s, G.rinv_s);
-            const int g1 = source_index(py, G.hLy, G.Psy, G.r_s, G.rinv_s);
-            const bool ok = (i + e < G.rows_t) && source_valid(G, px, py, g0, g1);
-            gidx[e] = ok ? g0 + G.rows_s * g1 : -1;
-            if (TMA) {
-                const int l0 = g0 - box0, l1 = g1 - box1;
-                if (ok && (unsigned)l0 < (unsigned)kBox && (unsigned)l1 < (unsigned)kBox)
-                    v[e] = sbox[l1 * kBox + l0];
-                else
+            for (int e = 0; e < 4; ++e) {
+                const int ix = (int)(tx >> kFrac), iy = (int)(ty >> kFrac);
+                if (((tx + kDelta) & kFracMask) < 2 * kDelta || ((ty + kDelta) & kFracMask) < 2 * kDelta) // within 2^-17 cell of a border
+                    unc |= 1u << e;
+                bool ok = true;
+                if (!INSIDE)
+                    ok = (unsigned)(ix + org0) < (unsigned)G.rows_s && (unsigned)(iy + org1) < (unsigned)G.cols_s;
+                gidx[e] = ok ? iy * G.rows_s + ix + gbase : -1;
+                if (TMA) {
+                    const unsigned a = (unsigned)(iy * kBoxW + ix);
+                    // out-of-map cells: the TMA unit NaN-fills them, but with its own NaN bit pattern; the ABI promises 0x7fc00000
+                    v[e] = (ok && (unsigned)ix < (unsigned)kBoxW && a < (unsigned)(kBoxW * kBoxH)) ? sbox[a] : qnan;
+                } else {
                     v[e] = ok ? __ldg(src + gidx[e]) : qnan;
-            } else {
-                v[e] = ok ? __ldg(src + gidx[e]) : qnan; // the reference throws for out-of-map cells (GridMap.cpp:160-166)
+                }
+                tx += Axi;
+                ty += Ayi;
             }
         }
         const size_t l = (size_t)j * G.rows_t + i;
         if (vec_ok) {
             if (bbox) { // local_costmap.cpp:260-263: bounding-box layer wins when > 90
-                const float4 bb = *reinterpret_cast<const float4 *>(bbox + l);
+                const float4 bb = __ldcs(reinterpret_cast<const float4 *>(bbox + l));
                 if (bb.x > 90.f) v[0] = bb.x;
                 if (bb.y > 90.f) v[1] = bb.y;
                 if (bb.z > 90.f) v[2] = bb.z;
@@ -148,73 +267,71 @@ __device__ __forceinline__ void warp_tile_body(const WarpGeom &G, const TileTerm
                     if (idx) idx[l + e] = gidx[e];
                 }
         }
+        unc_all |= unc << (4 * k);
+    }
+    // Rare second pass, kept out of the loop above so that the call does not cost the fast path any registers: cells on (or
+    // within 2^-17 cell of) a source-cell border are redone with the reference's own chain.
+    if (unc_all) {
+#pragma unroll 1
+        for (int k = 0; k < 4; ++k) {
+            const unsigned unc = (unc_all >> (4 * k)) & 0xFu;
+            if (!unc)
+                continue;
+            const int wi = warp + 8 * k;
+            const int lq = 4 * (wi & 3) + (lane & 3), lj = 8 * (wi >> 2) + (lane >> 2);
+            const int i = i0 + 4 * lq, j = j0 + lj;
+            fixup_exact(G, T, src, unc, 4 * lq, lj, i, (size_t)j * G.rows_t + i, Vx, Vy, bbox, out, idx);
+        }
     }
 }
 
-__global__ void __launch_bounds__(kWarpThreads) warp_direct_kernel(const WarpGeom G, const float *__restrict__ src,
+__global__ void __launch_bounds__(kWarpThreads, 4) warp_direct_kernel(const __grid_constant__ WarpGeom G, const float *__restrict__ src,
                                                                    const double *__restrict__ poses, const float *__restrict__ bbox,
                                                                    float *__restrict__ out, int32_t *__restrict__ idx)
 {
-    __shared__ TileTerms T;
+    __shared__ TileShared T;
     const int tid = threadIdx.x;
     const int tile = blockIdx.x, pose = blockIdx.y;
     const int i0 = (tile % G.tiles_i) * kTile, j0 = (tile / G.tiles_i) * kTile;
     const double Vx = poses[4 * pose], Vy = poses[4 * pose + 1], sn = poses[4 * pose + 2], cn = poses[4 * pose + 3];
-    fill_tile_terms(G, T, i0, j0, sn, cn, tid);
-    __syncthreads();
+    tile_setup(G, T, i0, j0, Vx, Vy, sn, cn, tid);
     const size_t cells = (size_t)G.rows_t * G.cols_t;
-    warp_tile_body<false>(G, T, src, nullptr, 0, 0, Vx, Vy, i0, j0, bbox ? bbox + pose * cells : nullptr, out + pose * cells,
-                          idx ? idx + pose * cells : nullptr, tid);
+    const float *bb = bbox ? bbox + pose * cells : nullptr;
+    int32_t *ix = idx ? idx + pose * cells : nullptr;
+    if (T.inside)
+        warp_tile_body<false, true>(G, T, src, nullptr, Vx, Vy, sn, cn, i0, j0, bb, out + pose * cells, ix, tid);
+    else
+        warp_tile_body<false, false>(G, T, src, nullptr, Vx, Vy, sn, cn, i0, j0, bb, out + pose * cells, ix, tid);
 }
 
 __device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
 
-__global__ void __launch_bounds__(kWarpThreads) warp_tma_kernel(const __grid_constant__ CUtensorMap tmap, const WarpGeom G,
+__global__ void __launch_bounds__(kWarpThreads, 4) warp_tma_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ WarpGeom G,
                                                                 const float *__restrict__ src, const double *__restrict__ poses,
                                                                 const float *__restrict__ bbox, float *__restrict__ out,
                                                                 int32_t *__restrict__ idx)
 {
-    __shared__ __align__(128) float sbox[kBox * kBox];
-    __shared__ TileTerms T;
+    __shared__ __align__(128) float sbox[kBoxW * kBoxH];
+    __shared__ TileShared T;
     __shared__ __align__(8) unsigned long long bar;
-    __shared__ int s_box[2];
     const int tid = threadIdx.x;
     const int tile = blockIdx.x, pose = blockIdx.y;
     const int i0 = (tile % G.tiles_i) * kTile, j0 = (tile / G.tiles_i) * kTile;
     const double Vx = poses[4 * pose], Vy = poses[4 * pose + 1], sn = poses[4 * pose + 2], cn = poses[4 * pose + 3];
-    fill_tile_terms(G, T, i0, j0, sn, cn, tid);
     if (tid == 0) {
         asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&bar)));
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    __syncthreads();
-    if (tid == 0) {
-        // Bounding box of the tile's footprint: the map (i,j) -> source index is affine up to truncation, so its
-        // extremes over the tile are attained at the four corners; one cell of margin absorbs the truncation.
-        const int li1 = min(kTile, G.rows_t - i0) - 1, lj1 = min(kTile, G.cols_t - j0) - 1;
-        int lo0 = INT_MAX, lo1 = INT_MAX;
-#pragma unroll
-        for (int cnr = 0; cnr < 4; ++cnr) {
-            double px, py;
-            cell_position(T, (cnr & 1) ? li1 : 0, (cnr & 2) ? lj1 : 0, Vx, Vy, px, py);
-            lo0 = min(lo0, source_index(px, G.hLx, G.Psx, G.r_s, G.rinv_s));
-            lo1 = min(lo1, source_index(py, G.hLy, G.Psy, G.r_s, G.rinv_s));
-        }
-        // The truncating index map is monotone per axis, so the corner minimum is the exact lower bound and the tile
-        // spans at most ceil(63*sqrt(2)) + 1 = 91 source cells per axis.  TMA needs the innermost start coordinate on a
-        // 16-byte boundary (a misaligned one raises "illegal instruction", measured on B200): round index 0 down to a
-        // multiple of 4 floats (two's complement: also correct for negative, out-of-map coordinates) -> <= 94 <= kBox.
-        lo0 &= ~3;
-        s_box[0] = lo0;
-        s_box[1] = lo1;
-        const unsigned bytes = kBox * kBox * sizeof(float);
+    tile_setup(G, T, i0, j0, Vx, Vy, sn, cn, tid); // ends with __syncthreads(): barrier init and box origin are visible
+    const bool staged = !T.exact_only;
+    if (staged && tid == 0) {
+        const unsigned bytes = kBoxW * kBoxH * sizeof(float);
         asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(&bar)), "r"(bytes) : "memory");
         asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
-                     ::"r"(smem_u32(sbox)), "l"(&tmap), "r"(lo0), "r"(lo1), "r"(smem_u32(&bar))
+                     ::"r"(smem_u32(sbox)), "l"(&tmap), "r"(T.org0), "r"(T.org1), "r"(smem_u32(&bar))
                      : "memory");
     }
-    __syncthreads();
-    { // wait for the TMA bytes (phase 0)
+    if (staged) { // wait for the TMA bytes (phase 0)
         unsigned done = 0;
         while (!done) {
             asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\n\tselp.u32 %0, 1, 0, p;\n\t}"
@@ -224,8 +341,12 @@ __global__ void __launch_bounds__(kWarpThreads) warp_tma_kernel(const __grid_con
         }
     }
     const size_t cells = (size_t)G.rows_t * G.cols_t;
-    warp_tile_body<true>(G, T, src, sbox, s_box[0], s_box[1], Vx, Vy, i0, j0, bbox ? bbox + pose * cells : nullptr, out + pose * cells,
-                         idx ? idx + pose * cells : nullptr, tid);
+    const float *bb = bbox ? bbox + pose * cells : nullptr;
+    int32_t *ix = idx ? idx + pose * cells : nullptr;
+    if (T.inside)
+        warp_tile_body<true, true>(G, T, src, sbox, Vx, Vy, sn, cn, i0, j0, bb, out + pose * cells, ix, tid);
+    else
+        warp_tile_body<true, false>(G, T, src, sbox, Vx, Vy, sn, cn, i0, j0, bb, out + pose * cells, ix, tid);
 }
 
 // ------------------------------------------------------------------------------------------------- host helpers
@@ -312,6 +433,8 @@ int costmap_warp_batch(const float *src, const costmap_geom *src_geom, const cos
     G.hLy = 0.5 * G.Ly;
     G.Psx = src_geom->pos_x;
     G.Psy = src_geom->pos_y;
+    G.ratio = G.r_t / G.r_s;
+    G.mag = (std::fabs(G.base_x) + std::fabs(G.base_y) + Ltx + Lty + G.hLx + G.hLy + std::fabs(G.Psx) + std::fabs(G.Psy)) / G.r_s;
     G.tiles_i = (G.rows_t + kTile - 1) / kTile;
     G.tiles_j = (G.cols_t + kTile - 1) / kTile;
 
@@ -354,7 +477,7 @@ int costmap_warp_batch(const float *src, const costmap_geom *src_geom, const cos
         CUtensorMap tmap;
         const cuuint64_t gdim[2] = {(cuuint64_t)G.rows_s, (cuuint64_t)G.cols_s};
         const cuuint64_t gstride[1] = {(cuuint64_t)G.rows_s * sizeof(float)};
-        const cuuint32_t box[2] = {kBox, kBox};
+        const cuuint32_t box[2] = {kBoxW, kBoxH};
         const cuuint32_t estr[2] = {1, 1};
         const char *dbg = getenv("CILQR_TMA_DEBUG"); // bring-up knob: 1 = zero OOB fill, 2 = no L2 promotion
         const int dbgv = dbg ? atoi(dbg) : 0;
