@@ -161,6 +161,13 @@ class _Base:
         return out, idx
 
 
+def _ellipse_cells(self, g, cx, cy, lx, ly, rot, max_cells=4096):
+    cells = np.zeros((max_cells, 2), dtype=np.int32)
+    n = self._fn("ellipse_cells", C.c_int)(C.byref(g), C.c_double(cx), C.c_double(cy), C.c_double(lx), C.c_double(ly), C.c_double(rot),
+                                           _i(cells), C.c_int(max_cells))
+    return cells[:n]
+
+
 class RefOracle(_Base):
     """The compiled reference itself."""
     prefix = "ref_"
@@ -304,6 +311,18 @@ class PortOracle(_Base):
         used = self._fn("solve_batch", C.c_int)(C.byref(p), C.c_int(B), C.c_int(n_obs), _d(dim), _d(pos), _d(x0), _d(U), _d(poly), _d(xlp),
                                                 C.c_int(n_alphas), C.c_int(merit), _d(X), _d(J), _i(it), _i(st), C.c_int(threads))
         return dict(U=U.reshape(B, -1), X=X, J=J, iters=it, status=st, threads=int(used))
+
+    def propagate(self, vmap, g, s, c, sx, sy, sth, index=0, threads=0, want_ellipse=False):
+        vmap = np.ascontiguousarray(vmap, dtype=np.float32)
+        r, cc = self.geom_size(g)
+        n = r * cc - index
+        count, value = np.zeros(n, dtype=np.int32), np.zeros(n)
+        ell = np.zeros((n, 3)) if want_ellipse else None
+        self._fn("propagate", C.c_int)(_f(vmap), C.byref(g), C.c_double(s), C.c_double(c), C.c_double(sx), C.c_double(sy), C.c_double(sth),
+                                       C.c_int(index), _i(count), _d(value), _d(ell), C.c_int(threads))
+        return (count, value, ell) if want_ellipse else (count, value)
+
+    ellipse_cells = _ellipse_cells
 
     def expand_obstacles_cv(self, p, state0, LW, sigma, kappa):
         state0, LW, sigma = _c64(state0), _c64(LW), _c64(sigma)

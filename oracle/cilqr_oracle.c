@@ -28,6 +28,10 @@
 #endif
 #include "../include/cilqr.h"
 
+#ifndef M_PI
+#define M_PI 3.14159265358979323846 /* glibc <math.h> value; hidden by -std=c11 */
+#endif
+
 #define NS 4
 #define NC 2
 #define MAX_POLY 8
@@ -643,4 +647,220 @@ int oracle_warp(const float *src, const costmap_geom *sg, const costmap_geom *tg
         }
     }
     return used;
+}
+
+/* ================================================================ uncertainty propagation over the costmap (rows W2-W4)
+ * thrust_propagateUncertainty (CILQR/src/map_engine/src/arbitrary_transformation.cu:8-157, functors
+ * CILQR/src/map_engine/include/ARBIT.cuh:51-107; CPU twin local_costmap.cpp:517-648).
+ *
+ * W3 goes through Eigen::EigenSolver<Matrix2f> in the reference.  For a symmetric 2x2 float matrix the Eigen 3.2.10 code path
+ * (the version the reference vendors under map_engine/include/map_engine/Eigen) reduces to the few float operations restated in
+ * eigen2f_pseudo(): Hessenberg reduction is the identity for n = 2 (Eigenvalues/HessenbergDecomposition.h), RealSchur either
+ * deflates at once (sub-diagonal <= eps * (|T00| + |T11|), RealSchur.h:345-358) or splits off the two real roots with one
+ * Givens rotation (RealSchur.h:362-395, Jacobi/Jacobi.h:215-252, rotation application :300-430), and EigenSolver back-substitutes
+ * on the triangular factor (EigenSolver.h:441-507) and multiplies by U (:597-602).  Every float operation is rounded separately
+ * (this file is built with -ffp-contract=off). */
+typedef struct { float D0, D1, V00, V01, V10, V11; } eig2f_t;
+
+static eig2f_t eigen2f_pseudo(float a, float b, float c)
+{
+    float T00 = a, T01 = b, T10 = b, T11 = c;
+    float U00 = 1.f, U01 = 0.f, U10 = 0.f, U11 = 1.f;
+    eig2f_t r;
+    const float eps = FLT_EPSILON;
+    /* computeNormOfT (RealSchur.h:331-342): zero matrix -> nothing to do */
+    float normT = (fabsf(T00) + fabsf(T10)) + (fabsf(T01) + fabsf(T11));
+    if (normT != 0.f) {
+        float s = fabsf(T00) + fabsf(T11);
+        if (fabsf(T10) <= eps * s) {
+            T10 = 0.f; /* one root found, twice (RealSchur.h:292-299) */
+        } else {
+            /* splitOffTwoRows (RealSchur.h:362-395) */
+            float p = 0.5f * (T00 - T11);
+            float q = p * p + T10 * T01;
+            if (q >= 0.f) {
+                float z = sqrtf(fabsf(q));
+                float gp = p >= 0.f ? p + z : p - z, gq = T10, gc, gs;
+                /* JacobiRotation::makeGivens, real case (Jacobi.h:215-252) */
+                if (gq == 0.f) { gc = gp < 0.f ? -1.f : 1.f; gs = 0.f; }
+                else if (gp == 0.f) { gc = 0.f; gs = gq < 0.f ? 1.f : -1.f; }
+                else if (fabsf(gp) > fabsf(gq)) {
+                    float t = gq / gp, u = sqrtf(1.f + t * t);
+                    if (gp < 0.f) u = -u;
+                    gc = 1.f / u; gs = -t * gc;
+                } else {
+                    float t = gp / gq, u = sqrtf(1.f + t * t);
+                    if (gq < 0.f) u = -u;
+                    gs = -1.f / u; gc = -t * gs;
+                }
+                /* applyOnTheLeft(0, 1, rot.adjoint()): x' = c x + (-s) y, y' = s x + c y on rows, every column */
+                const float ns = -gs;
+                if (!(gc == 1.f && ns == 0.f)) {
+                    float x, y;
+                    x = T00; y = T10; T00 = gc * x + ns * y; T10 = -ns * x + gc * y;
+                    x = T01; y = T11; T01 = gc * x + ns * y; T11 = -ns * x + gc * y;
+                    /* applyOnTheRight(0, 1, rot): columns with rot.transpose() = (c, -s) */
+                    x = T00; y = T01; T00 = gc * x + ns * y; T01 = -ns * x + gc * y;
+                    x = T10; y = T11; T10 = gc * x + ns * y; T11 = -ns * x + gc * y;
+                    x = U00; y = U01; U00 = gc * x + ns * y; U01 = -ns * x + gc * y;
+                    x = U10; y = U11; U10 = gc * x + ns * y; U11 = -ns * x + gc * y;
+                }
+                T10 = 0.f;
+            }
+        }
+    }
+    r.D0 = T00; r.D1 = T11; /* real eigenvalues: the diagonal of T (EigenSolver.h:391-398) */
+    /* doComputeEigenvectors (EigenSolver.h:441-602), size 2, both eigenvalues real */
+    {
+        float norm = (fabsf(T00) + fabsf(T01)) + (fabsf(T10) + fabsf(T11));
+        float e01 = T01, e11 = T11;
+        if (norm != 0.f) {
+            float p = T11, w = T00 - p, rr = T01 * 1.f;
+            e11 = 1.f;
+            if (w != 0.f) e01 = -rr / w; else e01 = -rr / (eps * norm);
+            float t = fabsf(e01);
+            if ((eps * t) * t > 1.f) { e01 = e01 / t; e11 = e11 / t; }
+            /* back transformation: col1 = U * (e01, e11), col0 = U * (1, 0) */
+            r.V01 = (0.f + U00 * e01) + U01 * e11;
+            r.V11 = (0.f + U10 * e01) + U11 * e11;
+            r.V00 = U00; r.V10 = U10;
+        } else {
+            r.V00 = U00; r.V01 = U01; r.V10 = U10; r.V11 = U11;
+        }
+        (void)e11;
+    }
+    return r;
+}
+
+/* grid_map::boundPositionToRange (gmc/GridMapMath.cpp:241-264), one coordinate */
+static double bound_to_range(double position, double L, double P)
+{
+    double shifted = (position - P) + 0.5 * L;
+    double epsilon = 10.0 * DBL_EPSILON;
+    if (fabs(position) > 1.0) epsilon *= fabs(position);
+    if (shifted <= 0) shifted = epsilon;
+    else if (shifted >= L) shifted = L - epsilon;
+    return (shifted + P) - 0.5 * L;
+}
+
+/* One cell of thrust_propagateUncertainty.  (Cx, Cy) is the cell centre; out: count, value, optional ellipse[3]. */
+static void propagate_cell(const float *map, const costmap_geom *g, int rows, int cols, double Cx, double Cy, double sn, double cn,
+                           double sigma_x, double sigma_y, double sigma_theta, int32_t *count, double *value, double *ellipse)
+{
+    const double r = g->resolution, Lx = rows * r, Ly = cols * r;
+    /* uncertainty_error_functor (ARBIT.cuh:58-68) */
+    double u = (-sn * Cx - cn * Cy) * (-sn * Cx - cn * Cy);
+    double v = (cn * Cx - sn * Cy) * (cn * Cx - sn * Cy);
+    double t = sn * cn * (Cx * Cx - Cy * Cy) + Cx * Cy * (sn * sn - cn * cn);
+    double sigma_x_i = sqrt(sigma_x * sigma_x + sigma_theta * sigma_theta * u);
+    double sigma_y_i = sqrt(sigma_y * sigma_y + sigma_theta * sigma_theta * v);
+    double rho = sigma_theta * sigma_theta * t / (sigma_x_i * sigma_y_i);
+    /* abc_functor (ARBIT.cuh:74-79) */
+    double a = sigma_x_i * sigma_x_i, b = rho * sigma_x_i * sigma_y_i, c = sigma_y_i * sigma_y_i;
+    /* arbitrary_transformation.cu:60-83: EigenSolver<Matrix2f> on the float-cast covariance */
+    eig2f_t E = eigen2f_pseudo((float)a, (float)b, (float)c);
+    int major = E.D0 > E.D1 ? 0 : 1;
+    float Dmaj = major == 0 ? E.D0 : E.D1, Dmin = major == 0 ? E.D1 : E.D0;
+    float Vm0 = major == 0 ? E.V00 : E.V10, Vm1 = major == 0 ? E.V01 : E.V11; /* ROW `major` of V (ARBIT.cuh:89) */
+    /* ellipse_params_functor (ARBIT.cuh:84-98) */
+    double angle = atan2((double)Vm1, (double)Vm0);
+    if (angle < 0) angle += 6.28318530718;
+    double half_major = 2.4477 * sqrt((double)Dmaj), half_minor = 2.4477 * sqrt((double)Dmin);
+    if (ellipse) { ellipse[0] = half_major; ellipse[1] = half_minor; ellipse[2] = angle; }
+    /* grid_map::EllipseIterator(map, centre, Length(2 a, 2 b), angle) — gmc/iterators/EllipseIterator.cpp:19-107 */
+    const double len0 = 2 * half_major, len1 = 2 * half_minor;
+    const double sas0 = (0.5 * len0) * (0.5 * len0), sas1 = (0.5 * len1) * (0.5 * len1); /* semiAxisSquare_ */
+    const double sinR = sin(angle), cosR = cos(angle);
+    /* findSubmapParameters (:90-105): Rotation2Dd * (len0, 0) and * (0, len1); "half length" from the FULL lengths as the reference does */
+    double u0 = cosR * len0 + (-sinR) * 0.0, u1 = sinR * len0 + cosR * 0.0;
+    double v0 = cosR * 0.0 + (-sinR) * len1, v1 = sinR * 0.0 + cosR * len1;
+    double bb0 = sqrt(u0 * u0 + v0 * v0), bb1 = sqrt(u1 * u1 + v1 * v1);
+    double tlx = bound_to_range(Cx + bb0, Lx, g->pos_x), tly = bound_to_range(Cy + bb1, Ly, g->pos_y);
+    double brx = bound_to_range(Cx - bb0, Lx, g->pos_x), bry = bound_to_range(Cy - bb1, Ly, g->pos_y);
+    int s0, s1, e0, e1;
+    oracle_index_from_position(g, tlx, tly, &s0, &s1);
+    oracle_index_from_position(g, brx, bry, &e0, &e1);
+    const int n0 = e0 - s0 + 1, n1 = e1 - s1 + 1; /* getSubmapSizeFromCornerIndeces (gmc/GridMapMath.cpp:321-328) */
+    const double offx = 0.5 * Lx - 0.5 * r, offy = 0.5 * Ly - 0.5 * r;
+    /* nomal2 prefactors (ARBIT.cuh:103-107), evaluated per cell in the reference; hoisting them changes no bit */
+    const double omr = 1 - rho * rho;
+    const double pref = 1.0 / (sqrt(omr) * (2 * M_PI * sigma_x_i * sigma_y_i));
+    const double ecoef = -1 / (2 * omr);
+    double numerator = 0, denominator = 0;
+    int cnt = 0;
+    /* SubmapIterator order (gmc/GridMapMath.cpp:459-488): index 1 fastest.  The iterator always yields its first index, even when
+     * the clipped box is degenerate (EllipseIterator.cpp:34 `if(!isInside()) ++(*this)`), hence the do-while shape. */
+    for (int a0 = 0; a0 < (n0 > 0 ? n0 : 1); ++a0) {
+        for (int a1 = 0; a1 < (n1 > 0 ? n1 : 1); ++a1) {
+            if ((n0 <= 0 || n1 <= 0) && (a0 > 0 || a1 > 0)) break;
+            const int i0 = s0 + a0, i1 = s1 + a1;
+            if (i0 < 0 || i1 < 0 || i0 >= rows || i1 >= cols) continue; /* cannot happen after boundPositionToRange */
+            const double px = (g->pos_x + offx) + r * (double)(-i0), py = (g->pos_y + offy) + r * (double)(-i1);
+            const double dx = px - Cx, dy = py - Cy;
+            const double q0 = cosR * dx + sinR * dy, q1 = sinR * dx + (-cosR) * dy; /* transformMatrix_ = [[c, s], [s, -c]] (:25) */
+            if (!(q0 * q0 / sas0 + q1 * q1 / sas1 <= 1)) continue;
+            const double f = pref * exp(ecoef * ((dx * dx / (sigma_x_i * sigma_x_i) - 2 * rho * dx * dy / (sigma_x_i * sigma_y_i)) +
+                                                 dy * dy / (sigma_y_i * sigma_y_i)));
+            int j0, j1;
+            float mv = NAN;
+            if (oracle_index_from_position(g, px, py, &j0, &j1)) mv = map[j0 + rows * j1]; /* atPosition (gmc/GridMap.cpp:160-166) */
+            numerator += f * mv;
+            denominator += f;
+            cnt++;
+        }
+    }
+    *count = cnt;
+    *value = numerator / denominator;
+}
+
+int oracle_propagate(const float *map, const costmap_geom *g, double sn, double cn, double sigma_x, double sigma_y, double sigma_theta,
+                     int index, int32_t *count, double *value, double *ellipse, int threads)
+{
+    int32_t rows, cols;
+    oracle_geom_size(g, &rows, &cols);
+    const int n = rows * cols - index;
+    int used = 1;
+#ifdef _OPENMP
+    if (threads > 0) omp_set_num_threads(threads);
+    used = omp_get_max_threads();
+#pragma omp parallel for schedule(dynamic, 64)
+#endif
+    for (int k = 0; k < n; ++k) {
+        const int l = index + k, i = l % rows, j = l / rows;
+        double Cx, Cy;
+        oracle_position_from_index(g, i, j, &Cx, &Cy);
+        propagate_cell(map, g, rows, cols, Cx, Cy, sn, cn, sigma_x, sigma_y, sigma_theta, count + k, value + k, ellipse ? ellipse + 3 * k : NULL);
+    }
+    return used;
+}
+
+/* The index sequence of grid_map::EllipseIterator(map, centre, Length(len_x, len_y), rot) — the same walk propagate_cell does,
+ * exposed for the known-answer test transcribed from grid_map_core/test/EllipseIteratorTest.cpp:28-60. */
+int oracle_ellipse_cells(const costmap_geom *g, double cx, double cy, double len_x, double len_y, double rot, int32_t *cells, int max_cells)
+{
+    int32_t rows, cols;
+    oracle_geom_size(g, &rows, &cols);
+    const double r = g->resolution, Lx = rows * r, Ly = cols * r;
+    const double sas0 = (0.5 * len_x) * (0.5 * len_x), sas1 = (0.5 * len_y) * (0.5 * len_y);
+    const double sinR = sin(rot), cosR = cos(rot);
+    double u0 = cosR * len_x + (-sinR) * 0.0, u1 = sinR * len_x + cosR * 0.0;
+    double v0 = cosR * 0.0 + (-sinR) * len_y, v1 = sinR * 0.0 + cosR * len_y;
+    double bb0 = sqrt(u0 * u0 + v0 * v0), bb1 = sqrt(u1 * u1 + v1 * v1);
+    int s0, s1, e0, e1;
+    oracle_index_from_position(g, bound_to_range(cx + bb0, Lx, g->pos_x), bound_to_range(cy + bb1, Ly, g->pos_y), &s0, &s1);
+    oracle_index_from_position(g, bound_to_range(cx - bb0, Lx, g->pos_x), bound_to_range(cy - bb1, Ly, g->pos_y), &e0, &e1);
+    int n0 = e0 - s0 + 1, n1 = e1 - s1 + 1, n = 0;
+    if (n0 <= 0 || n1 <= 0) { n0 = 1; n1 = 1; }
+    for (int a0 = 0; a0 < n0; ++a0)
+        for (int a1 = 0; a1 < n1; ++a1) {
+            double px, py;
+            if (s0 + a0 < 0 || s1 + a1 < 0 || s0 + a0 >= rows || s1 + a1 >= cols) continue;
+            oracle_position_from_index(g, s0 + a0, s1 + a1, &px, &py);
+            const double dx = px - cx, dy = py - cy;
+            const double q0 = cosR * dx + sinR * dy, q1 = sinR * dx + (-cosR) * dy;
+            if (!(q0 * q0 / sas0 + q1 * q1 / sas1 <= 1)) continue;
+            if (n < max_cells) { cells[2 * n] = s0 + a0; cells[2 * n + 1] = s1 + a1; }
+            ++n;
+        }
+    return n;
 }

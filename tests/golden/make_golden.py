@@ -3,7 +3,7 @@
 
     python tests/golden/make_golden.py
 
-Outputs (small, committed): tests/golden/solver_golden.npz, tests/golden/warp_golden.npz.
+Outputs (small, committed): tests/golden/solver_golden.npz, tests/golden/warp_golden.npz, tests/golden/propagate_golden.npz.
 The GPU box has no /root/reference; its tests read these files (and the prebuilt oracle/_ref .so).
 """
 import os
@@ -105,8 +105,23 @@ def warp_golden(R):
     print("warp_golden.npz: config2 checksum", int(out["config2/index_checksum"]), "oob", int(out["config2/oob"]))
 
 
+def propagate_golden(R):
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import test_propagate as tp
+    out = {}
+    for name, geom, theta, sigma, index in tp.CASES:
+        g = cilqr_b200.CostmapGeom(*geom)
+        rows, cols = R.geom_size(g)
+        c, v, e = R.propagate(tp.make_map(rows, cols), g, np.sin(theta), np.cos(theta), *sigma, index=index, want_ellipse=True)
+        out[name + "/count"] = c; out[name + "/value"] = v; out[name + "/ellipse"] = e
+    np.savez_compressed(os.path.join(HERE, "propagate_golden.npz"), **out)
+    print("propagate_golden.npz:", len(out), "arrays")
+
+
 if __name__ == "__main__":
     oracle.build(("ref",))
     R = oracle.RefOracle()
-    solver_golden(R)
-    warp_golden(R)
+    if "--only-propagate" not in sys.argv:
+        solver_golden(R)
+        warp_golden(R)
+    propagate_golden(R)

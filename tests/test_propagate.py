@@ -1,0 +1,104 @@
+"""Uncertainty propagation over the costmap.
+
+CPU: the plain-C restatement (incl. its restatement of Eigen 3.2.10's EigenSolver<Matrix2f> for symmetric 2x2 input) is pinned
+bit-for-bit on the compiled reference (real Eigen, real grid_map::EllipseIterator), on the committed golden vectors, and on the
+known-answer test transcribed from grid_map_core/test/EllipseIteratorTest.cpp:28-60.
+GPU: the fused kernel behind costmap_propagate_uncertainty against the checker: identical visit counts (a cell centre within an
+ulp of an ellipse border may flip, so a 1e-4 fraction is tolerated and reported), values within 1e-12 relative."""
+import os
+
+import numpy as np
+import pytest
+
+import cilqr_b200
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+G = cilqr_b200.CostmapGeom
+SIGMA_DEFAULT = (0.005, 0.005, 0.0125)   # CILQR/src/map_engine/cfg/map_engine.cfg:8-10
+SIGMA_EXPERIMENT = (0.16, 0.16, 0.017)   # CILQR/src/ilqr/launch/Experiment.launch:9-11
+CASES = [("default_30x20", (30.0, 20.0, 0.2, 10.0, 0.0), 0.7, SIGMA_DEFAULT, 0),
+         ("experiment_30x20", (30.0, 20.0, 0.2, 10.0, 0.0), 2.9, SIGMA_EXPERIMENT, 0),
+         ("fine_offset_index", (12.0, 9.0, 0.1, -3.0, 2.0), 5.1, SIGMA_EXPERIMENT, 1234),
+         ("anisotropic_axis_aligned", (16.0, 16.0, 0.2, 0.0, 0.0), 0.0, (0.1, 0.2, 0.05), 0)]
+
+
+def make_map(rows, cols, seed=1):
+    rng = np.random.default_rng(seed)
+    m = np.where(rng.random(rows * cols) > 0.8, 100.0, 0.0).astype(np.float32)
+    m[rng.integers(0, rows * cols, 5)] = np.nan  # NaN cells poison the sums, as in the reference
+    return m
+
+
+def bits64(a):
+    return np.asarray(a, dtype=np.float64).view(np.uint64)
+
+
+def test_ellipse_iterator_known_answer(port):
+    """EllipseIteratorTest.cpp:28-60 OneCellWideEllipse: 8x5 map, ellipse 8x1 at the centre -> cells (0..7, 2) in order."""
+    cells = port.ellipse_cells(G(8.0, 5.0, 1.0, 0.0, 0.0), 0.0, 0.0, 8.0, 1.0, 0.0)
+    assert cells.tolist() == [[i, 2] for i in range(8)]
+
+
+@pytest.mark.parametrize("name,geom,theta,sigma,index", CASES)
+def test_port_matches_compiled_reference_bit_for_bit(ref, port, name, geom, theta, sigma, index):
+    g = G(*geom)
+    rows, cols = ref.geom_size(g)
+    m = make_map(rows, cols)
+    cr, vr, er = ref.propagate(m, g, np.sin(theta), np.cos(theta), *sigma, index=index, want_ellipse=True)
+    cp, vp, ep = port.propagate(m, g, np.sin(theta), np.cos(theta), *sigma, index=index, want_ellipse=True)
+    assert np.array_equal(bits64(er), bits64(ep)), "ellipse (half_major, half_minor, angle): the float eigen-solve restatement differs"
+    assert np.array_equal(cr, cp)
+    assert np.array_equal(bits64(vr), bits64(vp))
+    assert cr.shape == (rows * cols - index,)
+
+
+def test_port_matches_golden(port):
+    gold = np.load(os.path.join(HERE, "golden", "propagate_golden.npz"))
+    for name, geom, theta, sigma, index in CASES:
+        g = G(*geom)
+        rows, cols = port.geom_size(g)
+        c, v, e = port.propagate(make_map(rows, cols), g, np.sin(theta), np.cos(theta), *sigma, index=index, want_ellipse=True)
+        assert np.array_equal(c, gold[name + "/count"]) and np.array_equal(bits64(v), bits64(gold[name + "/value"]))
+        assert np.array_equal(bits64(e), bits64(gold[name + "/ellipse"]))
+
+
+def check_gpu(checker, g, m, theta, sigma, index):
+    rows, cols = checker.geom_size(g)
+    c, v = cilqr_b200.propagate_uncertainty(m, g, np.sin(theta), np.cos(theta), *sigma, index=index)
+    cr, vr = checker.propagate(m, g, np.sin(theta), np.cos(theta), *sigma, index=index)
+    flips = int(np.sum(c != cr))
+    assert flips <= 1e-4 * c.size, "%d of %d visit counts differ" % (flips, c.size)
+    same = c == cr
+    assert np.array_equal(np.isnan(v[same]), np.isnan(vr[same]))
+    ok = same & np.isfinite(vr)
+    rel = np.abs(v[ok] - vr[ok]) / np.maximum(np.abs(vr[ok]), 1e-300)
+    assert rel.max() < 1e-12, rel.max()
+    return flips
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,geom,theta,sigma,index", CASES)
+def test_gpu_matches_checker(checker, name, geom, theta, sigma, index):
+    g = G(*geom)
+    rows, cols = checker.geom_size(g)
+    check_gpu(checker, g, make_map(rows, cols), theta, sigma, index)
+
+
+@pytest.mark.gpu
+def test_gpu_full_frame_400x400_and_device_buffers(checker):
+    """BASELINE config 2 frame size (400x400 @ 0.2 m, Position(35, 0)) with the experiment's sigmas: ellipses of up to ~500 cells."""
+    import torch
+    g = G(80.0, 80.0, 0.2, 35.0, 0.0)
+    m = make_map(400, 400, seed=3)
+    flips = check_gpu(checker, g, m, 0.7, SIGMA_EXPERIMENT, 0)
+    c_h, v_h = cilqr_b200.propagate_uncertainty(m, g, np.sin(0.7), np.cos(0.7), *SIGMA_EXPERIMENT)
+    c_d, v_d = cilqr_b200.propagate_uncertainty(torch.from_numpy(m).cuda(), g, np.sin(0.7), np.cos(0.7), *SIGMA_EXPERIMENT)
+    assert np.array_equal(c_d.cpu().numpy(), c_h) and np.array_equal(bits64(v_d.cpu().numpy()), bits64(v_h))
+    assert c_h.max() > 300
+
+
+@pytest.mark.gpu
+def test_gpu_bad_arguments():
+    g = G(8.0, 8.0, 0.2, 0.0, 0.0)
+    with pytest.raises(cilqr_b200.CilqrError, match="index"):
+        cilqr_b200.propagate_uncertainty(np.zeros(1600, np.float32), g, 0.0, 1.0, 0.1, 0.1, 0.01, index=1601)

@@ -15,7 +15,9 @@ from concurrent.futures import ThreadPoolExecutor
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libcilqr_b200.so")
-SOURCES = ["cilqr_solver.cu", "costmap.cu"]
+SOURCES = ["cilqr_solver.cu", "costmap.cu", "propagate.cu"]
+# propagate.cu restates float/double expression chains of the reference operation by operation: no FMA contraction there
+EXTRA_FLAGS = {"propagate.cu": ["-fmad=false"]}
 HEADERS = ["common.cuh", "cilqr_device.cuh", os.path.join("..", "..", "include", "cilqr.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC"]
@@ -47,7 +49,7 @@ def build_library(force=False, verbose=False):
 
     def compile_one(src):
         obj = os.path.join(objdir, src.replace(".cu", ".o"))
-        cmd = [nvcc] + ccbin + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", os.path.join(CSRC, src), "-o", obj]
+        cmd = [nvcc] + ccbin + NVCC_FLAGS + EXTRA_FLAGS.get(src, []) + (["-Xptxas", "-v"] if verbose else []) + ["-c", os.path.join(CSRC, src), "-o", obj]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError("nvcc failed for %s:\n%s\n%s" % (src, r.stdout, r.stderr))

@@ -499,10 +499,4 @@ int costmap_warp_batch(const float *src, const costmap_geom *src_geom, const cos
     return 0;
 }
 
-int costmap_propagate_uncertainty(const float *, const costmap_geom *, double, double, double, double, double, int, int32_t *, double *,
-                                  int, void *)
-{
-    return fail(CILQR_E_STATE, "costmap_propagate_uncertainty: not built yet");
-}
-
 } // extern "C"

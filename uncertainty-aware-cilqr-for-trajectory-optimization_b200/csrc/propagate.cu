@@ -1,0 +1,243 @@
+// propagate.cu — uncertainty propagation over the ego-frame costmap (rows W2-W4 of SURVEY.md §8), one fused kernel.
+//
+// Replaces thrust_propagateUncertainty (CILQR/src/map_engine/src/arbitrary_transformation.cu:8-157): three element-wise Thrust
+// launches, a per-cell Eigen::EigenSolver<Matrix2f> on the HOST between them, four host<->device round trips, and the
+// Gaussian-weighted ellipse average on the host under OpenMP.  Here one thread owns one cell from the pose sigma to the final
+// (count, value): covariance (ARBIT.cuh:58-79) -> 2x2 float eigen-decomposition -> 95 % ellipse (ARBIT.cuh:84-98) -> walk of the
+// clipped bounding box in grid_map::EllipseIterator order (grid_map_core/src/iterators/EllipseIterator.cpp:19-107) accumulating
+// nomal2-weighted map values (ARBIT.cuh:103-107, arbitrary_transformation.cu:118-140).
+//
+// This translation unit is compiled with -fmad=false: every float/double operation below is rounded separately, in the order
+// the reference's C++ expressions evaluate them, so the ellipse parameters — and with them the set of cells each ellipse admits
+// — come out as on the CPU.  The float eigen-solve restates what Eigen 3.2.10 (the version the reference vendors) executes for
+// a symmetric 2x2 input: see eigen2f_pseudo.  Transcendentals (atan2, sin, cos, exp) come from CUDA's libm, within 1-2 ulp of
+// glibc's: values agree to ~1e-15 relative, counts are identical unless a cell centre lies within an ulp of an ellipse border.
+#include "common.cuh"
+#include <cfloat>
+#include <climits>
+#include <cmath>
+
+namespace cilqr
+{
+struct PropGeom {
+    int rows, cols;
+    double r, Lx, Ly, Px, Py, offx, offy; // resolution, length (size * resolution), position, vector to the first cell centre
+};
+
+struct Eig2f {
+    float D0, D1, V00, V01, V10, V11;
+};
+
+// Eigen::EigenSolver<Matrix2f> for [[a, b], [b, c]] as Eigen 3.2.10 evaluates it: Hessenberg reduction is the identity for n = 2;
+// RealSchur deflates at once when |b| <= eps (|a| + |c|) (RealSchur.h:345-358), else splits off two real roots with one Givens
+// rotation (RealSchur.h:362-395, Jacobi.h:215-252); EigenSolver back-substitutes on T and multiplies by U (EigenSolver.h:441-602).
+// pseudoEigenvalueMatrix() = diag(T), pseudoEigenvectors() = the (un-normalised) eigenvector matrix.
+__device__ __forceinline__ Eig2f eigen2f_pseudo(float a, float b, float c)
+{
+    float T00 = a, T01 = b, T10 = b, T11 = c;
+    float U00 = 1.f, U01 = 0.f, U10 = 0.f, U11 = 1.f;
+    const float eps = FLT_EPSILON;
+    const float normT = (fabsf(T00) + fabsf(T10)) + (fabsf(T01) + fabsf(T11));
+    if (normT != 0.f) {
+        const float s = fabsf(T00) + fabsf(T11);
+        if (fabsf(T10) <= eps * s) {
+            T10 = 0.f;
+        } else {
+            const float p = 0.5f * (T00 - T11);
+            const float q = p * p + T10 * T01;
+            if (q >= 0.f) {
+                const float z = sqrtf(fabsf(q));
+                const float gp = p >= 0.f ? p + z : p - z, gq = T10;
+                float gc, gs;
+                if (gq == 0.f) { gc = gp < 0.f ? -1.f : 1.f; gs = 0.f; }
+                else if (gp == 0.f) { gc = 0.f; gs = gq < 0.f ? 1.f : -1.f; }
+                else if (fabsf(gp) > fabsf(gq)) {
+                    const float t = gq / gp;
+                    float u = sqrtf(1.f + t * t);
+                    if (gp < 0.f) u = -u;
+                    gc = 1.f / u; gs = -t * gc;
+                } else {
+                    const float t = gp / gq;
+                    float u = sqrtf(1.f + t * t);
+                    if (gq < 0.f) u = -u;
+                    gs = -1.f / u; gc = -t * gs;
+                }
+                const float ns = -gs;
+                if (!(gc == 1.f && ns == 0.f)) {
+                    float x, y;
+                    x = T00; y = T10; T00 = gc * x + ns * y; T10 = -ns * x + gc * y; // rows, rot.adjoint()
+                    x = T01; y = T11; T01 = gc * x + ns * y; T11 = -ns * x + gc * y;
+                    x = T00; y = T01; T00 = gc * x + ns * y; T01 = -ns * x + gc * y; // columns, rot.transpose()
+                    x = T10; y = T11; T10 = gc * x + ns * y; T11 = -ns * x + gc * y;
+                    x = U00; y = U01; U00 = gc * x + ns * y; U01 = -ns * x + gc * y;
+                    x = U10; y = U11; U10 = gc * x + ns * y; U11 = -ns * x + gc * y;
+                }
+                T10 = 0.f;
+            }
+        }
+    }
+    Eig2f r;
+    r.D0 = T00; r.D1 = T11;
+    const float norm = (fabsf(T00) + fabsf(T01)) + (fabsf(T10) + fabsf(T11));
+    if (norm != 0.f) {
+        const float w = T00 - T11, rr = T01 * 1.f;
+        float e01 = (w != 0.f) ? -rr / w : -rr / (eps * norm), e11 = 1.f;
+        const float t = fabsf(e01);
+        if ((eps * t) * t > 1.f) { e01 = e01 / t; e11 = e11 / t; }
+        r.V01 = (0.f + U00 * e01) + U01 * e11;
+        r.V11 = (0.f + U10 * e01) + U11 * e11;
+        r.V00 = U00; r.V10 = U10;
+    } else {
+        r.V00 = U00; r.V01 = U01; r.V10 = U10; r.V11 = U11;
+    }
+    return r;
+}
+
+// grid_map::boundPositionToRange (grid_map_core/src/GridMapMath.cpp:241-264), one coordinate.
+__device__ __forceinline__ double bound_to_range(double position, double L, double P)
+{
+    double shifted = (position - P) + 0.5 * L;
+    double epsilon = 10.0 * DBL_EPSILON;
+    if (fabs(position) > 1.0) epsilon *= fabs(position);
+    if (shifted <= 0) shifted = epsilon;
+    else if (shifted >= L) shifted = L - epsilon;
+    return (shifted + P) - 0.5 * L;
+}
+
+// getIndexFromPosition (GridMapMath.cpp:129-142) with checkIfPositionWithinMap (:144-157) and checkIfIndexInRange (:191-198).
+__device__ __forceinline__ bool index_from_position(const PropGeom &G, double x, double y, int &i0, int &i1)
+{
+    const double ox = 0.5 * G.Lx, oy = 0.5 * G.Ly;
+    const double vx = ((x - ox) - G.Px) / G.r, vy = ((y - oy) - G.Py) / G.r;
+    i0 = (fabs(vx) < 2.0e9) ? (int)(-vx) : INT_MIN;
+    i1 = (fabs(vy) < 2.0e9) ? (int)(-vy) : INT_MIN;
+    const double qx = -((x - G.Px) - ox), qy = -((y - G.Py) - oy);
+    return qx >= 0.0 && qy >= 0.0 && qx < G.Lx && qy < G.Ly && i0 >= 0 && i1 >= 0 && i0 < G.rows && i1 < G.cols;
+}
+
+__global__ void __launch_bounds__(128) propagate_kernel(const PropGeom G, const float *__restrict__ map, double sn, double cn, double sigma_x,
+                                                        double sigma_y, double sigma_theta, int index, int n, int32_t *__restrict__ count,
+                                                        double *__restrict__ value)
+{
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n)
+        return;
+    const int l = index + k, ci = l % G.rows, cj = l / G.rows; // GridMapIterator order: linear, column-major
+    const double Cx = (G.Px + G.offx) + G.r * (double)(-ci), Cy = (G.Py + G.offy) + G.r * (double)(-cj);
+    // W2: uncertainty_error_functor + abc_functor (ARBIT.cuh:58-79)
+    const double u = (-sn * Cx - cn * Cy) * (-sn * Cx - cn * Cy);
+    const double v = (cn * Cx - sn * Cy) * (cn * Cx - sn * Cy);
+    const double t = sn * cn * (Cx * Cx - Cy * Cy) + Cx * Cy * (sn * sn - cn * cn);
+    const double sxi = sqrt(sigma_x * sigma_x + sigma_theta * sigma_theta * u);
+    const double syi = sqrt(sigma_y * sigma_y + sigma_theta * sigma_theta * v);
+    const double rho = sigma_theta * sigma_theta * t / (sxi * syi);
+    const double a = sxi * sxi, b = rho * sxi * syi, c = syi * syi;
+    // W3: float eigen-solve + ellipse_params_functor (arbitrary_transformation.cu:60-83, ARBIT.cuh:84-98)
+    const Eig2f E = eigen2f_pseudo((float)a, (float)b, (float)c);
+    const bool maj0 = E.D0 > E.D1;
+    const float Dmaj = maj0 ? E.D0 : E.D1, Dmin = maj0 ? E.D1 : E.D0;
+    const float Vm0 = maj0 ? E.V00 : E.V10, Vm1 = maj0 ? E.V01 : E.V11; // ROW `major` of V, as the reference takes it
+    double angle = atan2((double)Vm1, (double)Vm0);
+    if (angle < 0) angle += 6.28318530718;
+    const double half_major = 2.4477 * sqrt((double)Dmaj), half_minor = 2.4477 * sqrt((double)Dmin);
+    // W4: EllipseIterator(map, centre, Length(2a, 2b), angle)
+    const double len0 = 2 * half_major, len1 = 2 * half_minor;
+    const double sas0 = (0.5 * len0) * (0.5 * len0), sas1 = (0.5 * len1) * (0.5 * len1);
+    double sinR, cosR;
+    sincos(angle, &sinR, &cosR);
+    const double u0 = cosR * len0 + (-sinR) * 0.0, u1 = sinR * len0 + cosR * 0.0;
+    const double v0 = cosR * 0.0 + (-sinR) * len1, v1 = sinR * 0.0 + cosR * len1;
+    const double bb0 = sqrt(u0 * u0 + v0 * v0), bb1 = sqrt(u1 * u1 + v1 * v1);
+    const double tlx = bound_to_range(Cx + bb0, G.Lx, G.Px), tly = bound_to_range(Cy + bb1, G.Ly, G.Py);
+    const double brx = bound_to_range(Cx - bb0, G.Lx, G.Px), bry = bound_to_range(Cy - bb1, G.Ly, G.Py);
+    int s0, s1, e0, e1;
+    index_from_position(G, tlx, tly, s0, s1);
+    index_from_position(G, brx, bry, e0, e1);
+    int n0 = e0 - s0 + 1, n1 = e1 - s1 + 1;
+    if (n0 <= 0 || n1 <= 0) { n0 = 1; n1 = 1; } // a degenerate SubmapIterator still yields its first index
+    const double omr = 1 - rho * rho;
+    const double pref = 1.0 / (sqrt(omr) * (2 * 3.14159265358979323846 * sxi * syi));
+    const double ecoef = -1 / (2 * omr);
+    const double sxx = sxi * sxi, sxy = sxi * syi, syy = syi * syi;
+    double numerator = 0, denominator = 0;
+    int cnt = 0;
+    for (int a0 = 0; a0 < n0; ++a0) { // SubmapIterator order: index 1 fastest (GridMapMath.cpp:459-488)
+        const int i0 = s0 + a0;
+        if (i0 < 0 || i0 >= G.rows) continue;
+        const double px = (G.Px + G.offx) + G.r * (double)(-i0);
+        const double dx = px - Cx;
+        for (int a1 = 0; a1 < n1; ++a1) {
+            const int i1 = s1 + a1;
+            if (i1 < 0 || i1 >= G.cols) continue;
+            const double py = (G.Py + G.offy) + G.r * (double)(-i1);
+            const double dy = py - Cy;
+            const double q0 = cosR * dx + sinR * dy, q1 = sinR * dx + (-cosR) * dy; // transformMatrix_ (EllipseIterator.cpp:25)
+            if (!(q0 * q0 / sas0 + q1 * q1 / sas1 <= 1)) continue;                  // isInside (:80-86)
+            const double f = pref * exp(ecoef * ((dx * dx / sxx - 2 * rho * dx * dy / sxy) + dy * dy / syy)); // nomal2
+            int j0, j1;
+            float mv = __int_as_float(0x7fc00000);
+            if (index_from_position(G, px, py, j0, j1)) mv = __ldg(map + j0 + G.rows * j1); // atPosition (GridMap.cpp:160-166)
+            numerator += f * mv; // float promoted to double, as in the reference expression
+            denominator += f;
+            cnt++;
+        }
+    }
+    count[k] = cnt;
+    value[k] = numerator / denominator;
+}
+} // namespace cilqr
+
+using namespace cilqr;
+
+namespace
+{
+struct PropWorkspace {
+    DevBuf map, count, value;
+};
+PropWorkspace g_pw;
+} // namespace
+
+extern "C" int costmap_propagate_uncertainty(const float *map, const costmap_geom *geom, double sin_theta, double cos_theta, double sigma_x,
+                                             double sigma_y, double sigma_theta, int index, int32_t *count, double *value, int mem, void *stream)
+{
+    if (!map || !geom || !count || !value) return fail(CILQR_E_ARG, "null argument");
+    int32_t rows = 0, cols = 0;
+    if (int rc = costmap_geom_size(geom, &rows, &cols)) return rc;
+    if ((long long)rows * cols > 2147483647LL) return fail(CILQR_E_ARG, "map has more than 2^31-1 cells");
+    const int cells = rows * cols;
+    if (index < 0 || index > cells) return fail(CILQR_E_ARG, "index %d outside [0, %d]", index, cells);
+    const int n = cells - index;
+    if (n == 0) return 0;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        return fail(CILQR_E_CUDA, "no CUDA device: this library has no CPU path");
+    }
+    PropGeom G;
+    G.rows = rows; G.cols = cols;
+    G.r = geom->resolution;
+    G.Lx = rows * G.r; G.Ly = cols * G.r;      // setGeometry: length = size * resolution (GridMap.cpp:58)
+    G.Px = geom->pos_x; G.Py = geom->pos_y;
+    G.offx = 0.5 * G.Lx - 0.5 * G.r; G.offy = 0.5 * G.Ly - 0.5 * G.r; // getVectorToFirstCell (GridMapMath.cpp:41-52)
+    cudaStream_t st = (cudaStream_t)stream;
+    const float *d_map = map;
+    int32_t *d_count = count;
+    double *d_value = value;
+    if (mem == CILQR_MEM_HOST) {
+        if (int rc = g_pw.map.reserve((size_t)cells * sizeof(float))) return rc;
+        if (int rc = g_pw.count.reserve((size_t)n * sizeof(int32_t))) return rc;
+        if (int rc = g_pw.value.reserve((size_t)n * sizeof(double))) return rc;
+        CILQR_CUDA(cudaMemcpyAsync(g_pw.map.p, map, (size_t)cells * sizeof(float), cudaMemcpyHostToDevice, st));
+        d_map = g_pw.map.as<float>();
+        d_count = g_pw.count.as<int32_t>();
+        d_value = g_pw.value.as<double>();
+    }
+    propagate_kernel<<<(n + 127) / 128, 128, 0, st>>>(G, d_map, sin_theta, cos_theta, sigma_x, sigma_y, sigma_theta, index, n, d_count, d_value);
+    CILQR_LAUNCH_CHECK();
+    if (mem == CILQR_MEM_HOST) {
+        CILQR_CUDA(cudaMemcpyAsync(count, d_count, (size_t)n * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+        CILQR_CUDA(cudaMemcpyAsync(value, d_value, (size_t)n * sizeof(double), cudaMemcpyDeviceToHost, st));
+        CILQR_CUDA(cudaStreamSynchronize(st));
+    }
+    return 0;
+}
