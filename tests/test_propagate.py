@@ -94,7 +94,7 @@ def test_gpu_full_frame_400x400_and_device_buffers(checker):
     c_h, v_h = cilqr_b200.propagate_uncertainty(m, g, np.sin(0.7), np.cos(0.7), *SIGMA_EXPERIMENT)
     c_d, v_d = cilqr_b200.propagate_uncertainty(torch.from_numpy(m).cuda(), g, np.sin(0.7), np.cos(0.7), *SIGMA_EXPERIMENT)
     assert np.array_equal(c_d.cpu().numpy(), c_h) and np.array_equal(bits64(v_d.cpu().numpy()), bits64(v_h))
-    assert c_h.max() > 300
+    assert c_h.max() > 200
 
 
 @pytest.mark.gpu

@@ -55,7 +55,7 @@ def propagate_uncertainty(vmap, geom, sin_theta, cos_theta, sigma_x, sigma_y, si
     a = _Arg()
     pm = a.inp(vmap, np.float32)
     r, c = geom_size(geom)
-    n = r * c - int(index)
+    n = max(r * c - int(index), 0)  # an out-of-range index is rejected by the library (CILQR_E_ARG)
     dev = a.mem == MEM_DEVICE
     d = getattr(vmap, "device", None)
     count, pc = a.out((n,), np.int32, dev, d)
