@@ -12,6 +12,7 @@
 #include "cilqr_device.cuh"
 #include <cfloat>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 
@@ -229,6 +230,140 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, 4) solve_kernel(const Sol
     }
 }
 
+// ------------------------------------------------------------------------------------------------- fused solve, v2 (reference semantics)
+// solve_kernel<false> runs the sequential phases (Riccati sweep, rollout) redundantly on all 32 lanes of the scenario's warp:
+// ncu showed the FP64 pipe 59 % busy with mostly replicated work (profiles/r01a_full.txt).  Here a CTA owns kSlots scenario
+// slots.  Phase D (derivatives, lane = timestep) still gives every slot a whole warp; phases B and F of ALL slots are then run by
+// warp 0 with lane = slot — one instruction stream for kSlots scenarios, each lane keeping its slot's V_x / V_xx in registers — while
+// the other warps wait at the CTA barrier without using issue slots.  Slots refill independently from the global queue, so a
+// scenario that stops early never idles its warp.  Same device functions, same arithmetic, same results as solve_kernel<false>.
+constexpr int kSlots = 8;
+
+struct SlotHdr {
+    double lamb;
+    int need_bf, finite;
+};
+
+__device__ __forceinline__ void finalize_slot(const SolveArgs &A, const WarpSmem &W, Polyline pl, int b, int iters, int status, int lane)
+{
+    const DevParams &P = A.P;
+    const int N = P.N;
+    store_controls(W, A.U + (size_t)b * 2 * N, N, lane);
+    if (A.X)
+        store_states(W, A.X + (size_t)b * 4 * (N + 1), N, lane);
+    if (A.J) { // J = get_J(X_result, U_result)
+        phase_derivs<false>(P, W, pl, nullptr, 0, false, lane);
+        const double J = sum_sequential(W.Jt, N);
+        if (lane == 0)
+            A.J[b] = J;
+    }
+    if (lane == 0) {
+        if (A.iters) A.iters[b] = iters;
+        if (A.status) A.status[b] = status;
+    }
+    __syncwarp();
+}
+
+__global__ void __launch_bounds__(kSlots * 32, 2) solve_kernel_v2(const SolveArgs A)
+{
+    extern __shared__ double smem[];
+    const DevParams &P = A.P;
+    const int N = P.N;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int stride = slot_stride_doubles(N, P.S);
+    const WarpSmem W = carve(smem + (size_t)warp * stride, N, P.S);
+    SlotHdr *hdr = reinterpret_cast<SlotHdr *>(smem + (size_t)kSlots * stride);
+
+    int b = -1, iters = 0, status = CILQR_ST_MAX_ITER;
+    bool queue_empty = false;
+    double lamb = 1.0, J_old = DBL_MAX;
+    Polyline pl{0.0, 0.0};
+    const double *obs = nullptr;
+
+    for (;;) {
+        // refill an empty slot from the global queue
+        if (b < 0 && !queue_empty) {
+            int nb = 0;
+            if (lane == 0)
+                nb = atomicAdd(A.counter, 1);
+            nb = __shfl_sync(0xffffffffu, nb, 0);
+            if (nb >= A.B) {
+                queue_empty = true;
+            } else {
+                b = nb;
+                pl.x_first = A.xlp[2 * b];
+                pl.dxs = (A.xlp[2 * b + 1] - A.xlp[2 * b]) / P.S; // Constraints.cpp:32
+                build_polyline(P, A.poly + (size_t)b * P.npoly, pl, W.Y, lane);
+                load_controls(W, A.U + (size_t)b * 2 * N, N, lane);
+                if (lane < 4)
+                    W.X[lane * (N + 1)] = A.x0[4 * (size_t)b + lane];
+                __syncwarp();
+                phase_rollout(P, W, lane); // X = get_nominal_trajectory(x_0, U)   (iLQR.cpp:203)
+                obs = A.obs + (size_t)b * A.n_obs * OB_FIELDS * N;
+                lamb = 1.0;
+                J_old = DBL_MAX;
+                iters = 0;
+                status = CILQR_ST_MAX_ITER;
+            }
+        }
+        // phase D and the (one-iteration-lagged) accept test of iLQR.cpp:217-219
+        bool need_bf = false, converged = false;
+        double J_new = 0.0;
+        if (b >= 0) {
+            ++iters;
+            phase_derivs<true>(P, W, pl, obs, A.n_obs, false, lane);
+            J_new = sum_sequential(W.Jt, N);
+            if (!(J_new < J_old)) { // rejected: the nominal never changes again, only lamb and the counter advance (see solve_kernel)
+                lamb = lamb * P.lamb_factor;
+                for (;;) {
+                    if (lamb > P.lamb_max) { status = CILQR_ST_LAMB_MAX; break; }
+                    if (iters >= P.max_iter) { status = CILQR_ST_MAX_ITER; break; }
+                    ++iters;
+                    lamb = lamb * P.lamb_factor;
+                }
+                finalize_slot(A, W, pl, b, iters, status, lane);
+                b = -1;
+            } else {
+                converged = fabs(J_new - J_old) < P.tol;
+                need_bf = true;
+            }
+        }
+        if (lane == 0) {
+            hdr[warp].need_bf = need_bf ? 1 : 0;
+            hdr[warp].lamb = lamb;
+        }
+        if (!__syncthreads_or((b >= 0 || !queue_empty) ? 1 : 0))
+            break;
+        // phases B and F of every slot that accepted: warp 0, lane = slot
+        if (warp == 0 && lane < kSlots && hdr[lane].need_bf) {
+            const WarpSmem Ws = carve(smem + (size_t)lane * stride, N, P.S);
+            const bool fin = phase_backward<true>(P, Ws, hdr[lane].lamb, 0);
+            if (fin)
+                phase_forward_inplace<true>(P, Ws, 0);
+            hdr[lane].finite = fin ? 1 : 0;
+        }
+        __syncthreads();
+        if (need_bf) {
+            if (!hdr[warp].finite) {
+                finalize_slot(A, W, pl, b, iters, CILQR_ST_NONFINITE, lane);
+                b = -1;
+            } else {
+                lamb = lamb / P.lamb_factor;
+                if (converged) {
+                    finalize_slot(A, W, pl, b, iters, CILQR_ST_TOLERANCE, lane);
+                    b = -1;
+                } else {
+                    J_old = J_new;
+                    if (iters >= P.max_iter) {
+                        finalize_slot(A, W, pl, b, iters, CILQR_ST_MAX_ITER, lane);
+                        b = -1;
+                    }
+                }
+            }
+        }
+    }
+}
+
 // ------------------------------------------------------------------------------------------------- stage kernel
 enum { STAGE_ROLLOUT = 0, STAGE_STATE_COST, STAGE_CONTROL_COST, STAGE_COST, STAGE_BACKWARD, STAGE_FORWARD };
 
@@ -354,6 +489,7 @@ struct cilqr_solver {
     int max_batch, max_obs;
     int cur_B = 0, cur_nobs = 0; // obstacle set currently resident
     int num_sms = 0;
+    bool v2_ok = false;          // solve_kernel_v2 fits in shared memory for this horizon
     DevBuf obs;                  // prepared obstacle records
     DevBuf counter, scratch;
     DevBuf stage[12];            // staging for CILQR_MEM_HOST callers / stage outputs
@@ -527,6 +663,12 @@ int cilqr_create(const cilqr_params *p, int max_batch, int max_obs, cilqr_handle
     CILQR_CUDA(cudaFuncSetAttribute(solve_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     CILQR_CUDA(cudaFuncSetAttribute(solve_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     CILQR_CUDA(cudaFuncSetAttribute(stage_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const size_t smem2 = (size_t)kSlots * slot_stride_doubles(h->dp.N, h->dp.S) * sizeof(double) + kSlots * sizeof(SlotHdr);
+    h->v2_ok = smem2 <= 227 * 1024;
+    if (h->v2_ok)
+        CILQR_CUDA(cudaFuncSetAttribute(solve_kernel_v2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
+    if (const char *e = getenv("CILQR_SOLVER_V1"))
+        if (atoi(e) != 0) h->v2_ok = false; // A/B switch for measurements: force the one-warp-per-scenario kernel
     if (int rc = h->counter.reserve(sizeof(int))) { delete h; return rc; }
     *out = h;
     return 0;
@@ -624,6 +766,24 @@ int cilqr_solve_batch(cilqr_handle h, int B, const double *x0, double *U, const 
     if (int rc = stage_out(h, 10, status, (size_t)B, mem, &A.status)) return rc;
     A.counter = h->counter.as<int>();
 
+    if (n_alphas == 1 && h->v2_ok) {
+        const size_t smem2 = (size_t)kSlots * slot_stride_doubles(N, h->dp.S) * sizeof(double) + kSlots * sizeof(SlotHdr);
+        int per_sm2 = 0;
+        CILQR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm2, solve_kernel_v2, kSlots * 32, smem2));
+        if (per_sm2 < 1) return fail(CILQR_E_CUDA, "solve kernel does not fit on an SM (smem %zu B)", smem2);
+        const int grid2 = std::min((B + kSlots - 1) / kSlots, h->num_sms * per_sm2);
+        A.scratch = nullptr;
+        CILQR_CUDA(cudaMemsetAsync(A.counter, 0, sizeof(int), st));
+        solve_kernel_v2<<<grid2, kSlots * 32, smem2, st>>>(A);
+        CILQR_LAUNCH_CHECK();
+        if (int rc = fetch_out(U, A.U, (size_t)B * 2 * N, mem, st)) return rc;
+        if (int rc = fetch_out(X, A.X, (size_t)B * 4 * (N + 1), mem, st)) return rc;
+        if (int rc = fetch_out(J, A.J, (size_t)B, mem, st)) return rc;
+        if (int rc = fetch_out(iters, A.iters, (size_t)B, mem, st)) return rc;
+        if (int rc = fetch_out(status, A.status, (size_t)B, mem, st)) return rc;
+        if (mem == CILQR_MEM_HOST) CILQR_CUDA(cudaStreamSynchronize(st));
+        return 0;
+    }
     const size_t smem = (size_t)kWarpsPerBlock * warp_smem_doubles(N, h->dp.S) * sizeof(double);
     int per_sm = 0;
     if (n_alphas > 1)
