@@ -241,7 +241,7 @@ constexpr int kSlots = 8;
 
 struct SlotHdr {
     double lamb;
-    int need_bf, finite;
+    int need_bf, finite, open_loop, pad;
 };
 
 __device__ __forceinline__ void finalize_slot(const SolveArgs &A, const WarpSmem &W, Polyline pl, int b, int iters, int status, int lane)
@@ -275,41 +275,52 @@ __global__ void __launch_bounds__(kSlots * 32, 2) solve_kernel_v2(const SolveArg
     SlotHdr *hdr = reinterpret_cast<SlotHdr *>(smem + (size_t)kSlots * stride);
 
     int b = -1, iters = 0, status = CILQR_ST_MAX_ITER;
-    bool queue_empty = false;
+    bool queue_empty = false, fresh = false;
     double lamb = 1.0, J_old = DBL_MAX;
     Polyline pl{0.0, 0.0};
     const double *obs = nullptr;
 
-    for (;;) {
-        // refill an empty slot from the global queue
-        if (b < 0 && !queue_empty) {
-            int nb = 0;
-            if (lane == 0)
-                nb = atomicAdd(A.counter, 1);
-            nb = __shfl_sync(0xffffffffu, nb, 0);
-            if (nb >= A.B) {
-                queue_empty = true;
-            } else {
-                b = nb;
-                pl.x_first = A.xlp[2 * b];
-                pl.dxs = (A.xlp[2 * b + 1] - A.xlp[2 * b]) / P.S; // Constraints.cpp:32
-                build_polyline(P, A.poly + (size_t)b * P.npoly, pl, W.Y, lane);
-                load_controls(W, A.U + (size_t)b * 2 * N, N, lane);
-                if (lane < 4)
-                    W.X[lane * (N + 1)] = A.x0[4 * (size_t)b + lane];
-                __syncwarp();
-                phase_rollout(P, W, lane); // X = get_nominal_trajectory(x_0, U)   (iLQR.cpp:203)
-                obs = A.obs + (size_t)b * A.n_obs * OB_FIELDS * N;
-                lamb = 1.0;
-                J_old = DBL_MAX;
-                iters = 0;
-                status = CILQR_ST_MAX_ITER;
-            }
+    // Takes the next scenario from the global queue into this warp's slot.  Its nominal rollout (iLQR.cpp:203) is left to the next
+    // lane-per-slot pass of warp 0 (open-loop form of the forward pass), so it costs one lane instead of a replicated warp.
+    auto refill = [&]() {
+        if (b >= 0 || queue_empty)
+            return;
+        int nb = 0;
+        if (lane == 0)
+            nb = atomicAdd(A.counter, 1);
+        nb = __shfl_sync(0xffffffffu, nb, 0);
+        if (nb >= A.B) {
+            queue_empty = true;
+            return;
         }
+        b = nb;
+        pl.x_first = A.xlp[2 * b];
+        pl.dxs = (A.xlp[2 * b + 1] - A.xlp[2 * b]) / P.S; // Constraints.cpp:32
+        build_polyline(P, A.poly + (size_t)b * P.npoly, pl, W.Y, lane);
+        load_controls(W, A.U + (size_t)b * 2 * N, N, lane);
+        if (lane < 4)
+            W.X[lane * (N + 1)] = A.x0[4 * (size_t)b + lane];
+        __syncwarp();
+        obs = A.obs + (size_t)b * A.n_obs * OB_FIELDS * N;
+        lamb = 1.0;
+        J_old = DBL_MAX;
+        iters = 0;
+        status = CILQR_ST_MAX_ITER;
+        fresh = true;
+    };
+
+#ifdef CILQR_PHASE_CLOCKS
+    long long c_d = 0, c_w1 = 0, c_bf = 0, c_post = 0, n_tick = 0, n_bf = 0, t0 = clock64(), t1;
+#define CK(acc) do { t1 = clock64(); acc += t1 - t0; t0 = t1; } while (0)
+#else
+#define CK(acc) do { } while (0)
+#endif
+    for (;;) {
+        refill();
         // phase D and the (one-iteration-lagged) accept test of iLQR.cpp:217-219
         bool need_bf = false, converged = false;
         double J_new = 0.0;
-        if (b >= 0) {
+        if (b >= 0 && !fresh) {
             ++iters;
             phase_derivs<true>(P, W, pl, obs, A.n_obs, false, lane);
             J_new = sum_sequential(W.Jt, N);
@@ -323,27 +334,41 @@ __global__ void __launch_bounds__(kSlots * 32, 2) solve_kernel_v2(const SolveArg
                 }
                 finalize_slot(A, W, pl, b, iters, status, lane);
                 b = -1;
+                refill(); // the successor's rollout joins this tick's lane-per-slot pass
             } else {
                 converged = fabs(J_new - J_old) < P.tol;
                 need_bf = true;
             }
         }
         if (lane == 0) {
-            hdr[warp].need_bf = need_bf ? 1 : 0;
+            hdr[warp].need_bf = (need_bf || (b >= 0 && fresh)) ? 1 : 0;
+            hdr[warp].open_loop = (b >= 0 && fresh) ? 1 : 0;
             hdr[warp].lamb = lamb;
         }
+        CK(c_d);
         if (!__syncthreads_or((b >= 0 || !queue_empty) ? 1 : 0))
             break;
-        // phases B and F of every slot that accepted: warp 0, lane = slot
+        CK(c_w1);
+        // phases B and F of every slot that accepted (and the nominal rollout of fresh slots): warp 0, lane = slot
         if (warp == 0 && lane < kSlots && hdr[lane].need_bf) {
             const WarpSmem Ws = carve(smem + (size_t)lane * stride, N, P.S);
-            const bool fin = phase_backward<true>(P, Ws, hdr[lane].lamb, 0);
+            const bool open_loop = hdr[lane].open_loop != 0;
+            bool fin = true;
+            if (!open_loop)
+                fin = phase_backward<true>(P, Ws, hdr[lane].lamb, 0);
             if (fin)
-                phase_forward_inplace<true>(P, Ws, 0);
+                phase_forward_inplace<true>(P, Ws, 0, open_loop);
             hdr[lane].finite = fin ? 1 : 0;
         }
+#ifdef CILQR_PHASE_CLOCKS
+        n_tick++;
+        n_bf += __popc(__ballot_sync(0xffffffffu, warp == 0 && lane < kSlots && hdr[lane < kSlots ? lane : 0].need_bf));
+#endif
         __syncthreads();
-        if (need_bf) {
+        CK(c_bf);
+        if (b >= 0 && fresh) {
+            fresh = false;
+        } else if (need_bf) {
             if (!hdr[warp].finite) {
                 finalize_slot(A, W, pl, b, iters, CILQR_ST_NONFINITE, lane);
                 b = -1;
@@ -361,7 +386,14 @@ __global__ void __launch_bounds__(kSlots * 32, 2) solve_kernel_v2(const SolveArg
                 }
             }
         }
+        CK(c_post);
     }
+#ifdef CILQR_PHASE_CLOCKS
+    if (blockIdx.x < 2 && lane == 0 && (warp == 0 || warp == 3))
+        printf("cta %d warp %d: ticks %lld  D %lld  wait1 %lld  BF+wait2 %lld  post %lld  (cycles per tick: %lld %lld %lld %lld)  slots in BF per tick %.2f\n",
+               blockIdx.x, warp, n_tick, c_d, c_w1, c_bf, c_post, c_d / n_tick, c_w1 / n_tick, c_bf / n_tick, c_post / n_tick, (double)n_bf / n_tick);
+#endif
+#undef CK
 }
 
 // ------------------------------------------------------------------------------------------------- stage kernel
