@@ -10,6 +10,7 @@
 //       _cost / _backward / _forward (same device functions as the fused kernel; used by the parity tests).
 #include "common.cuh"
 #include "cilqr_device.cuh"
+#include "cilqr_batch.cuh"
 #include <cfloat>
 #include <cmath>
 #include <cstdlib>
@@ -20,53 +21,6 @@ namespace cilqr
 {
 thread_local char g_err[512] = "";
 std::atomic<long long> g_launches{0};
-
-// ------------------------------------------------------------------------------------------------- obstacle prep
-__device__ __forceinline__ void write_obstacle_record(const DevParams &P, double *__restrict__ out, size_t bj, int t, double xo, double yo,
-                                                      double vo, double tho, double dim0, double dim1)
-{
-    double so, co;
-    sincos(tho, &so, &co);
-    const double a = dim0 / 2.0 + fabs(vo * co) * P.t_safe + P.s_safe_a + P.ego_rad;       // Obstacle.cpp:42
-    const double b = dim1 / 2.0 + fabs(vo * so) * P.t_safe + P.s_safe_b + P.ego_rad + 1.0; // Obstacle.cpp:43 (hard-coded +1)
-    double *o = out + bj * OB_FIELDS * P.N + t;
-    o[OB_X * P.N] = xo;
-    o[OB_Y * P.N] = yo;
-    o[OB_C * P.N] = co;
-    o[OB_S * P.N] = so;
-    o[OB_IA2 * P.N] = 1.0 / a / a; // Obstacle.cpp:45
-    o[OB_IB2 * P.N] = 1.0 / b / b; // Obstacle.cpp:46
-}
-
-__global__ void prep_obstacles_dense_kernel(DevParams P, size_t n_bj, const double *__restrict__ dim, const double *__restrict__ pos,
-                                            double *__restrict__ out)
-{
-    const size_t total = n_bj * P.N;
-    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
-        const size_t bj = i / P.N;
-        const int t = (int)(i - bj * P.N);
-        const double *d = dim + 2 * i, *q = pos + 4 * i; // Obstacle's dimension (2xN) / relative_pos_array (4xN) columns
-        write_obstacle_record(P, out, bj, t, q[0], q[1], q[2], q[3], d[0], d[1]);
-    }
-}
-
-__global__ void prep_obstacles_cv_kernel(DevParams P, size_t n_bj, const double *__restrict__ state0, const double *__restrict__ LW,
-                                         const double *__restrict__ sigma, double kappa, double *__restrict__ out)
-{
-    const size_t total = n_bj * P.N;
-    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
-        const size_t bj = i / P.N;
-        const int t = (int)(i - bj * P.N);
-        const double x0 = state0[4 * bj], y0 = state0[4 * bj + 1], v = state0[4 * bj + 2], th = state0[4 * bj + 3];
-        const double sx = sigma[3 * bj], sy = sigma[3 * bj + 1], sth = sigma[3 * bj + 2];
-        double s, c;
-        sincos(th, &s, &c);
-        const double tt = t * P.dt, arm = v * tt;
-        const double dim0 = LW[2 * bj] + 2.0 * kappa * sx;
-        const double dim1 = LW[2 * bj + 1] + 2.0 * kappa * sqrt(sy * sy + sth * sth * arm * arm);
-        write_obstacle_record(P, out, bj, t, x0 + v * c * tt, y0 + v * s * tt, v, th, dim0, dim1);
-    }
-}
 
 // ------------------------------------------------------------------------------------------------- FP64 roofline probe
 // 8 independent DFMA chains per thread: the denominator of the solver's FP64-pipe fraction, measured on the GPU the
@@ -522,7 +476,14 @@ struct cilqr_solver {
     int cur_B = 0, cur_nobs = 0; // obstacle set currently resident
     int num_sms = 0;
     bool v2_ok = false;          // solve_kernel_v2 fits in shared memory for this horizon
-    DevBuf obs;                  // prepared obstacle records
+    int occ_item = 1, occ_sweep = 1; // resident CTAs per SM of the (chunk, t) kernels / the sweep kernel
+    int variant = 3;             // 3 = batch-synchronous rounds (default), 2 = slot kernel, 1 = one warp per scenario (A/B switch CILQR_SOLVER)
+    DevBuf obs;                  // obstacle records [scenario][obstacle][field][t] of the fused kernels, built on demand from obs_b
+    bool obs_ready = false;
+    DevBuf obs_b;                // obstacle records, scenario fastest (cilqr_batch.cuh)
+    int obs_cv = 0;              // obs_b holds the compact constant-velocity form
+    size_t obs_pitch = 0;
+    DevBuf bws;                  // state of the batch-synchronous solve
     DevBuf counter, scratch;
     DevBuf stage[12];            // staging for CILQR_MEM_HOST callers / stage outputs
 };
@@ -699,8 +660,18 @@ int cilqr_create(const cilqr_params *p, int max_batch, int max_obs, cilqr_handle
     h->v2_ok = smem2 <= 227 * 1024;
     if (h->v2_ok)
         CILQR_CUDA(cudaFuncSetAttribute(solve_kernel_v2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
-    if (const char *e = getenv("CILQR_SOLVER_V1"))
-        if (atoi(e) != 0) h->v2_ok = false; // A/B switch for measurements: force the one-warp-per-scenario kernel
+    {
+        int o1 = 0, o2 = 0, o3 = 0;
+        CILQR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o1, batch_derivs_kernel<true>, kItemWarps * 32, 0));
+        CILQR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o2, batch_derivs_kernel<false>, kItemWarps * 32, 0));
+        CILQR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o3, batch_sweep_kernel, kSweepThreads, 0));
+        h->occ_item = std::max(1, std::min(o1, o2));
+        h->occ_sweep = std::max(1, o3);
+    }
+    if (const char *e = getenv("CILQR_SOLVER")) { // A/B switch for measurements
+        const int v = atoi(e);
+        if (v >= 1 && v <= 3) h->variant = v;
+    }
     if (int rc = h->counter.reserve(sizeof(int))) { delete h; return rc; }
     *out = h;
     return 0;
@@ -710,6 +681,8 @@ int cilqr_destroy(cilqr_handle h)
 {
     if (!h) return 0;
     h->obs.release();
+    h->obs_b.release();
+    h->bws.release();
     h->counter.release();
     h->scratch.release();
     for (auto &s : h->stage) s.release();
@@ -718,6 +691,22 @@ int cilqr_destroy(cilqr_handle h)
 }
 
 static int prep_grid(size_t total, int num_sms) { return (int)std::min<size_t>((total + 255) / 256, (size_t)num_sms * 8); }
+static size_t batch_pitch(int B) { return ((size_t)B + 31) / 32 * 32; }
+
+// The fused kernels and the stage entry points read [scenario][obstacle][field][t] records: built from obs_b when first needed.
+static int ensure_records(cilqr_handle h, cudaStream_t st)
+{
+    if (h->obs_ready || h->cur_nobs == 0 || h->cur_B == 0) return 0;
+    const int N = h->dp.N, B = h->cur_B, n_obs = h->cur_nobs;
+    if (int rc = h->obs.reserve((size_t)B * n_obs * OB_FIELDS * N * sizeof(double))) return rc;
+    const size_t pitch = h->obs_pitch;
+    const double *base = h->obs_b.as<double>();
+    relayout_records_kernel<<<prep_grid((size_t)B * n_obs * N, h->num_sms), 256, 0, st>>>(
+        h->dp, B, n_obs, pitch, h->obs_cv, base, base + (size_t)n_obs * CV_FIELDS * pitch, base, h->obs.as<double>());
+    CILQR_LAUNCH_CHECK();
+    h->obs_ready = true;
+    return 0;
+}
 
 int cilqr_set_obstacles(cilqr_handle h, int B, int n_obs, const double *dim, const double *pos, int mem, void *stream)
 {
@@ -732,9 +721,13 @@ int cilqr_set_obstacles(cilqr_handle h, int B, int n_obs, const double *dim, con
     const double *d_dim, *d_pos;
     if (int rc = stage_in(h, 0, dim, n_bj * 2 * N, mem, st, &d_dim)) return rc;
     if (int rc = stage_in(h, 1, pos, n_bj * 4 * N, mem, st, &d_pos)) return rc;
-    if (int rc = h->obs.reserve(n_bj * OB_FIELDS * N * sizeof(double))) return rc;
-    prep_obstacles_dense_kernel<<<prep_grid(n_bj * N, h->num_sms), 256, 0, st>>>(h->dp, n_bj, d_dim, d_pos, h->obs.as<double>());
+    const size_t pitch = batch_pitch(B);
+    if (int rc = h->obs_b.reserve((size_t)n_obs * N * OB_FIELDS * pitch * sizeof(double))) return rc;
+    prep_dense_b_kernel<<<prep_grid((size_t)n_obs * N * pitch, h->num_sms), 256, 0, st>>>(h->dp, B, n_obs, pitch, d_dim, d_pos, h->obs_b.as<double>());
     CILQR_LAUNCH_CHECK();
+    h->obs_cv = 0;
+    h->obs_pitch = pitch;
+    h->obs_ready = false;
     if (mem == CILQR_MEM_HOST) CILQR_CUDA(cudaStreamSynchronize(st));
     return 0;
 }
@@ -754,9 +747,14 @@ int cilqr_set_obstacles_cv(cilqr_handle h, int B, int n_obs, const double *state
     if (int rc = stage_in(h, 0, state0, n_bj * 4, mem, st, &d_s)) return rc;
     if (int rc = stage_in(h, 1, LW, n_bj * 2, mem, st, &d_lw)) return rc;
     if (int rc = stage_in(h, 2, sigma, n_bj * 3, mem, st, &d_sg)) return rc;
-    if (int rc = h->obs.reserve(n_bj * OB_FIELDS * N * sizeof(double))) return rc;
-    prep_obstacles_cv_kernel<<<prep_grid(n_bj * N, h->num_sms), 256, 0, st>>>(h->dp, n_bj, d_s, d_lw, d_sg, kappa, h->obs.as<double>());
+    const size_t pitch = batch_pitch(B);
+    if (int rc = h->obs_b.reserve((size_t)n_obs * (CV_FIELDS + N) * pitch * sizeof(double))) return rc;
+    double *ocv = h->obs_b.as<double>(), *oib2 = ocv + (size_t)n_obs * CV_FIELDS * pitch;
+    prep_cv_b_kernel<<<prep_grid((size_t)n_obs * pitch, h->num_sms), 256, 0, st>>>(h->dp, B, n_obs, pitch, d_s, d_lw, d_sg, kappa, ocv, oib2);
     CILQR_LAUNCH_CHECK();
+    h->obs_cv = 1;
+    h->obs_pitch = pitch;
+    h->obs_ready = false;
     if (mem == CILQR_MEM_HOST) CILQR_CUDA(cudaStreamSynchronize(st));
     return 0;
 }
@@ -765,6 +763,85 @@ static int need_obstacles(cilqr_handle h, int B)
 {
     if (h->cur_nobs > 0 && h->cur_B != B)
         return fail(CILQR_E_STATE, "obstacles were set for a batch of %d, this call has %d scenarios", h->cur_B, B);
+    return 0;
+}
+
+// Batch-synchronous solve (cilqr_batch.cuh): a fixed sequence of launches, work lists and termination handled on the device.
+static int solve_rounds(cilqr_handle h, const SolveArgs &A, cudaStream_t st)
+{
+    const DevParams &P = h->dp;
+    const int N = P.N, B = A.B;
+    const size_t Bp = batch_pitch(B);
+    const int rows = 4 * (N + 1) + 2 * N + 2 * (N + 1) + kRec * N + N + P.npoly + 6;
+    const int chunks = (int)(Bp / 32), n_cnt = P.max_iter + 3;
+    const size_t n_int = 6 * Bp + n_cnt + chunks;
+    if (int rc = h->bws.reserve(((size_t)rows * Bp) * sizeof(double) + n_int * sizeof(int))) return rc;
+    BatchView V;
+    V.Bp = Bp;
+    double *d = h->bws.as<double>();
+    V.X = d; d += (size_t)4 * (N + 1) * Bp;
+    V.U = d; d += (size_t)2 * N * Bp;
+    V.CS = d; d += (size_t)2 * (N + 1) * Bp;
+    V.R = d; d += (size_t)kRec * N * Bp;
+    V.Jt = d; d += (size_t)N * Bp;
+    V.poly = d; d += (size_t)P.npoly * Bp;
+    V.xf = d; d += Bp;
+    V.dxs = d; d += Bp;
+    V.lamb = d; d += Bp;
+    V.Jold = d; d += Bp;
+    V.Jnew = d; d += Bp;
+    V.Jres = d; d += Bp;
+    int *q = reinterpret_cast<int *>(d);
+    V.iters = q; q += Bp;
+    V.mode = q; q += Bp;
+    V.conv = q; q += Bp;
+    V.status = q; q += Bp;
+    V.list0 = q; q += Bp;
+    V.list1 = q; q += Bp;
+    V.cnt = q; q += n_cnt;
+    V.done = q;
+    V.n_obs = h->cur_nobs;
+    V.cv = h->obs_cv;
+    const double *ob = h->obs_b.as<double>();
+    V.ocv = ob;
+    V.oib2 = ob ? ob + (size_t)h->cur_nobs * CV_FIELDS * h->obs_pitch : nullptr;
+    V.orec = ob;
+    if (V.n_obs > 0 && h->obs_pitch != Bp) return fail(CILQR_E_STATE, "obstacle records were laid out for another batch size");
+
+    CILQR_CUDA(cudaMemsetAsync(V.cnt, 0, (size_t)(n_cnt + chunks) * sizeof(int), st));
+    const dim3 tb(32, 8);
+    transpose_in_kernel<<<dim3((2 * N + 31) / 32, chunks), tb, 0, st>>>(A.U, V.U, B, 2 * N, Bp);
+    CILQR_LAUNCH_CHECK();
+    transpose_in_kernel<<<dim3((P.npoly + 31) / 32, chunks), tb, 0, st>>>(A.poly, V.poly, B, P.npoly, Bp);
+    CILQR_LAUNCH_CHECK();
+    batch_init_kernel<<<(B + 127) / 128, 128, 0, st>>>(P, V, B, A.x0, A.xlp);
+    CILQR_LAUNCH_CHECK();
+
+    // persistent grids sized once for the full batch; later rounds find shorter lists and leave early
+    const long long items = (long long)chunks * N;
+    const int item_grid = (int)std::min<long long>((items + kItemWarps - 1) / kItemWarps, (long long)h->num_sms * h->occ_item);
+    const int sweep_grid = std::min(chunks, h->num_sms * h->occ_sweep);
+    for (int r = 0; r <= P.max_iter; ++r) {
+        batch_cost_kernel<<<item_grid, kItemWarps * 32, 0, st>>>(P, V, r);
+        CILQR_LAUNCH_CHECK();
+        if (r == P.max_iter) break; // the last round only evaluates J of the scenarios that ran out of iterations
+        if (V.cv)
+            batch_derivs_kernel<true><<<item_grid, kItemWarps * 32, 0, st>>>(P, V, r);
+        else
+            batch_derivs_kernel<false><<<item_grid, kItemWarps * 32, 0, st>>>(P, V, r);
+        CILQR_LAUNCH_CHECK();
+        batch_sweep_kernel<<<sweep_grid, kSweepThreads, 0, st>>>(P, V, r);
+        CILQR_LAUNCH_CHECK();
+    }
+    transpose_out_kernel<<<dim3((2 * N + 31) / 32, chunks), tb, 0, st>>>(V.U, A.U, B, 2 * N, Bp);
+    CILQR_LAUNCH_CHECK();
+    if (A.X) {
+        transpose_out_kernel<<<dim3((4 * (N + 1) + 31) / 32, chunks), tb, 0, st>>>(V.X, A.X, B, 4 * (N + 1), Bp);
+        CILQR_LAUNCH_CHECK();
+    }
+    if (A.J) CILQR_CUDA(cudaMemcpyAsync(A.J, V.Jres, (size_t)B * sizeof(double), cudaMemcpyDeviceToDevice, st));
+    if (A.iters) CILQR_CUDA(cudaMemcpyAsync(A.iters, V.iters, (size_t)B * sizeof(int), cudaMemcpyDeviceToDevice, st));
+    if (A.status) CILQR_CUDA(cudaMemcpyAsync(A.status, V.status, (size_t)B * sizeof(int), cudaMemcpyDeviceToDevice, st));
     return 0;
 }
 
@@ -785,7 +862,7 @@ int cilqr_solve_batch(cilqr_handle h, int B, const double *x0, double *U, const 
     A.n_obs = h->cur_nobs;
     A.n_alphas = n_alphas;
     A.merit = merit;
-    A.obs = h->obs.as<double>();
+    A.obs = nullptr;
     const double *dU_in;
     if (int rc = stage_in(h, 3, x0, (size_t)B * 4, mem, st, &A.x0)) return rc;
     if (int rc = stage_in(h, 4, (const double *)U, (size_t)B * 2 * N, mem, st, &dU_in)) return rc;
@@ -798,7 +875,21 @@ int cilqr_solve_batch(cilqr_handle h, int B, const double *x0, double *U, const 
     if (int rc = stage_out(h, 10, status, (size_t)B, mem, &A.status)) return rc;
     A.counter = h->counter.as<int>();
 
-    if (n_alphas == 1 && h->v2_ok) {
+    if (n_alphas == 1 && h->variant == 3) {
+        if (int rc = solve_rounds(h, A, st)) return rc;
+        if (int rc = fetch_out(U, A.U, (size_t)B * 2 * N, mem, st)) return rc;
+        if (int rc = fetch_out(X, A.X, (size_t)B * 4 * (N + 1), mem, st)) return rc;
+        if (int rc = fetch_out(J, A.J, (size_t)B, mem, st)) return rc;
+        if (int rc = fetch_out(iters, A.iters, (size_t)B, mem, st)) return rc;
+        if (int rc = fetch_out(status, A.status, (size_t)B, mem, st)) return rc;
+        if (mem == CILQR_MEM_HOST) CILQR_CUDA(cudaStreamSynchronize(st));
+        return 0;
+    }
+    if (h->cur_nobs > 0) {
+        if (int rc = ensure_records(h, st)) return rc;
+        A.obs = h->obs.as<double>();
+    }
+    if (n_alphas == 1 && h->v2_ok && h->variant == 2) {
         const size_t smem2 = (size_t)kSlots * slot_stride_doubles(N, h->dp.S) * sizeof(double) + kSlots * sizeof(SlotHdr);
         int per_sm2 = 0;
         CILQR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm2, solve_kernel_v2, kSlots * 32, smem2));
@@ -849,6 +940,10 @@ static int run_stage(cilqr_handle h, StageArgs &A, cudaStream_t st)
 {
     const size_t smem = (size_t)kWarpsPerBlock * warp_smem_doubles(h->dp.N, h->dp.S) * sizeof(double);
     const int grid = std::min((A.B + kWarpsPerBlock - 1) / kWarpsPerBlock, h->num_sms * 4);
+    if ((A.stage == STAGE_STATE_COST || A.stage == STAGE_BACKWARD) && h->cur_nobs > 0) {
+        if (int rc = ensure_records(h, st)) return rc;
+        A.obs = h->obs.as<double>();
+    }
     stage_kernel<<<grid, kWarpsPerBlock * 32, smem, st>>>(A);
     CILQR_LAUNCH_CHECK();
     return 0;
@@ -861,7 +956,7 @@ static StageArgs stage_args(cilqr_handle h, int B, int stage)
     A.B = B;
     A.stage = stage;
     A.n_obs = h->cur_nobs;
-    A.obs = h->cur_nobs > 0 ? h->obs.as<double>() : nullptr;
+    A.obs = nullptr; // set by run_stage for the stages that read obstacle records
     return A;
 }
 
