@@ -476,13 +476,12 @@ struct cilqr_solver {
     int cur_B = 0, cur_nobs = 0; // obstacle set currently resident
     int num_sms = 0;
     bool v2_ok = false;          // solve_kernel_v2 fits in shared memory for this horizon
-    int occ_item = 1, occ_sweep = 1; // resident CTAs per SM of the (chunk, t) kernels / the sweep kernel
+    int occ_cost = 1, occ_deriv = 1, occ_sweep = 1; // resident CTAs per SM of the round kernels
     int variant = 3;             // 3 = batch-synchronous rounds (default), 2 = slot kernel, 1 = one warp per scenario (A/B switch CILQR_SOLVER)
-    DevBuf obs;                  // obstacle records [scenario][obstacle][field][t] of the fused kernels, built on demand from obs_b
+    DevBuf obs;                  // obstacle records [scenario][obstacle][field][t]; expanded on demand when obs_cv
     bool obs_ready = false;
-    DevBuf obs_b;                // obstacle records, scenario fastest (cilqr_batch.cuh)
+    DevBuf obs_b;                // compact constant-velocity obstacles (cilqr_batch.cuh)
     int obs_cv = 0;              // obs_b holds the compact constant-velocity form
-    size_t obs_pitch = 0;
     DevBuf bws;                  // state of the batch-synchronous solve
     DevBuf counter, scratch;
     DevBuf stage[12];            // staging for CILQR_MEM_HOST callers / stage outputs
@@ -661,11 +660,16 @@ int cilqr_create(const cilqr_params *p, int max_batch, int max_obs, cilqr_handle
     if (h->v2_ok)
         CILQR_CUDA(cudaFuncSetAttribute(solve_kernel_v2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
     {
-        int o1 = 0, o2 = 0, o3 = 0;
-        CILQR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o1, batch_derivs_kernel<true>, kItemWarps * 32, 0));
-        CILQR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o2, batch_derivs_kernel<false>, kItemWarps * 32, 0));
+        const size_t cost_smem = (size_t)cost_entries_per_cta(h->dp.N) * h->dp.N * sizeof(double);
+        if (cost_smem > 48 * 1024)
+            CILQR_CUDA(cudaFuncSetAttribute(batch_cost_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cost_smem));
+        int o0 = 0, o1 = 0, o2 = 0, o3 = 0;
+        CILQR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o0, batch_cost_kernel, kCostThreads, cost_smem));
+        CILQR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o1, batch_derivs_kernel<true>, kDerivThreads, 0));
+        CILQR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o2, batch_derivs_kernel<false>, kDerivThreads, 0));
         CILQR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o3, batch_sweep_kernel, kSweepThreads, 0));
-        h->occ_item = std::max(1, std::min(o1, o2));
+        h->occ_cost = std::max(1, o0);
+        h->occ_deriv = std::max(1, std::min(o1, o2));
         h->occ_sweep = std::max(1, o3);
     }
     if (const char *e = getenv("CILQR_SOLVER")) { // A/B switch for measurements
@@ -691,18 +695,15 @@ int cilqr_destroy(cilqr_handle h)
 }
 
 static int prep_grid(size_t total, int num_sms) { return (int)std::min<size_t>((total + 255) / 256, (size_t)num_sms * 8); }
-static size_t batch_pitch(int B) { return ((size_t)B + 31) / 32 * 32; }
-
-// The fused kernels and the stage entry points read [scenario][obstacle][field][t] records: built from obs_b when first needed.
+// The fused kernels and the stage entry points read [scenario][obstacle][field][t] records: expanded from the compact
+// constant-velocity form when first needed.
 static int ensure_records(cilqr_handle h, cudaStream_t st)
 {
     if (h->obs_ready || h->cur_nobs == 0 || h->cur_B == 0) return 0;
-    const int N = h->dp.N, B = h->cur_B, n_obs = h->cur_nobs;
-    if (int rc = h->obs.reserve((size_t)B * n_obs * OB_FIELDS * N * sizeof(double))) return rc;
-    const size_t pitch = h->obs_pitch;
-    const double *base = h->obs_b.as<double>();
-    relayout_records_kernel<<<prep_grid((size_t)B * n_obs * N, h->num_sms), 256, 0, st>>>(
-        h->dp, B, n_obs, pitch, h->obs_cv, base, base + (size_t)n_obs * CV_FIELDS * pitch, base, h->obs.as<double>());
+    const size_t n_bj = (size_t)h->cur_B * h->cur_nobs, N = h->dp.N;
+    if (int rc = h->obs.reserve(n_bj * OB_FIELDS * N * sizeof(double))) return rc;
+    const double *ocv = h->obs_b.as<double>();
+    expand_cv_records_kernel<<<prep_grid(n_bj * N, h->num_sms), 256, 0, st>>>(h->dp, n_bj, ocv, ocv + n_bj * CV_FIELDS, h->obs.as<double>());
     CILQR_LAUNCH_CHECK();
     h->obs_ready = true;
     return 0;
@@ -721,13 +722,11 @@ int cilqr_set_obstacles(cilqr_handle h, int B, int n_obs, const double *dim, con
     const double *d_dim, *d_pos;
     if (int rc = stage_in(h, 0, dim, n_bj * 2 * N, mem, st, &d_dim)) return rc;
     if (int rc = stage_in(h, 1, pos, n_bj * 4 * N, mem, st, &d_pos)) return rc;
-    const size_t pitch = batch_pitch(B);
-    if (int rc = h->obs_b.reserve((size_t)n_obs * N * OB_FIELDS * pitch * sizeof(double))) return rc;
-    prep_dense_b_kernel<<<prep_grid((size_t)n_obs * N * pitch, h->num_sms), 256, 0, st>>>(h->dp, B, n_obs, pitch, d_dim, d_pos, h->obs_b.as<double>());
+    if (int rc = h->obs.reserve(n_bj * OB_FIELDS * N * sizeof(double))) return rc;
+    prep_obstacles_dense_kernel<<<prep_grid(n_bj * N, h->num_sms), 256, 0, st>>>(h->dp, n_bj, d_dim, d_pos, h->obs.as<double>());
     CILQR_LAUNCH_CHECK();
     h->obs_cv = 0;
-    h->obs_pitch = pitch;
-    h->obs_ready = false;
+    h->obs_ready = true;
     if (mem == CILQR_MEM_HOST) CILQR_CUDA(cudaStreamSynchronize(st));
     return 0;
 }
@@ -747,13 +746,11 @@ int cilqr_set_obstacles_cv(cilqr_handle h, int B, int n_obs, const double *state
     if (int rc = stage_in(h, 0, state0, n_bj * 4, mem, st, &d_s)) return rc;
     if (int rc = stage_in(h, 1, LW, n_bj * 2, mem, st, &d_lw)) return rc;
     if (int rc = stage_in(h, 2, sigma, n_bj * 3, mem, st, &d_sg)) return rc;
-    const size_t pitch = batch_pitch(B);
-    if (int rc = h->obs_b.reserve((size_t)n_obs * (CV_FIELDS + N) * pitch * sizeof(double))) return rc;
-    double *ocv = h->obs_b.as<double>(), *oib2 = ocv + (size_t)n_obs * CV_FIELDS * pitch;
-    prep_cv_b_kernel<<<prep_grid((size_t)n_obs * pitch, h->num_sms), 256, 0, st>>>(h->dp, B, n_obs, pitch, d_s, d_lw, d_sg, kappa, ocv, oib2);
+    if (int rc = h->obs_b.reserve(n_bj * (CV_FIELDS + N) * sizeof(double))) return rc;
+    double *ocv = h->obs_b.as<double>(), *oib2 = ocv + n_bj * CV_FIELDS;
+    prep_obstacles_cv_kernel<<<prep_grid(n_bj * N, h->num_sms), 256, 0, st>>>(h->dp, n_bj, d_s, d_lw, d_sg, kappa, ocv, oib2);
     CILQR_LAUNCH_CHECK();
     h->obs_cv = 1;
-    h->obs_pitch = pitch;
     h->obs_ready = false;
     if (mem == CILQR_MEM_HOST) CILQR_CUDA(cudaStreamSynchronize(st));
     return 0;
@@ -771,77 +768,48 @@ static int solve_rounds(cilqr_handle h, const SolveArgs &A, cudaStream_t st)
 {
     const DevParams &P = h->dp;
     const int N = P.N, B = A.B;
-    const size_t Bp = batch_pitch(B);
-    const int rows = 4 * (N + 1) + 2 * N + 2 * (N + 1) + kRec * N + N + P.npoly + 6;
-    const int chunks = (int)(Bp / 32), n_cnt = P.max_iter + 3;
-    const size_t n_int = 6 * Bp + n_cnt + chunks;
-    if (int rc = h->bws.reserve(((size_t)rows * Bp) * sizeof(double) + n_int * sizeof(int))) return rc;
+    const int n_cnt = P.max_iter + 3;
+    const size_t n_dbl = (size_t)B * kHdrD + (size_t)B * (N + 1) * kStepD;
+    if (int rc = h->bws.reserve(n_dbl * sizeof(double) + ((size_t)2 * B + n_cnt) * sizeof(int))) return rc;
     BatchView V;
-    V.Bp = Bp;
-    double *d = h->bws.as<double>();
-    V.X = d; d += (size_t)4 * (N + 1) * Bp;
-    V.U = d; d += (size_t)2 * N * Bp;
-    V.CS = d; d += (size_t)2 * (N + 1) * Bp;
-    V.R = d; d += (size_t)kRec * N * Bp;
-    V.Jt = d; d += (size_t)N * Bp;
-    V.poly = d; d += (size_t)P.npoly * Bp;
-    V.xf = d; d += Bp;
-    V.dxs = d; d += Bp;
-    V.lamb = d; d += Bp;
-    V.Jold = d; d += Bp;
-    V.Jnew = d; d += Bp;
-    V.Jres = d; d += Bp;
-    int *q = reinterpret_cast<int *>(d);
-    V.iters = q; q += Bp;
-    V.mode = q; q += Bp;
-    V.conv = q; q += Bp;
-    V.status = q; q += Bp;
-    V.list0 = q; q += Bp;
-    V.list1 = q; q += Bp;
-    V.cnt = q; q += n_cnt;
-    V.done = q;
+    V.N = N;
+    V.hdr = h->bws.as<double>();
+    V.rec = V.hdr + (size_t)B * kHdrD;
+    V.list0 = reinterpret_cast<int *>(V.rec + (size_t)B * (N + 1) * kStepD);
+    V.list1 = V.list0 + B;
+    V.cnt = V.list1 + B;
     V.n_obs = h->cur_nobs;
     V.cv = h->obs_cv;
-    const double *ob = h->obs_b.as<double>();
-    V.ocv = ob;
-    V.oib2 = ob ? ob + (size_t)h->cur_nobs * CV_FIELDS * h->obs_pitch : nullptr;
-    V.orec = ob;
-    if (V.n_obs > 0 && h->obs_pitch != Bp) return fail(CILQR_E_STATE, "obstacle records were laid out for another batch size");
+    V.ocv = h->obs_b.as<double>();
+    V.oib2 = V.ocv ? V.ocv + (size_t)B * h->cur_nobs * CV_FIELDS : nullptr;
+    V.orec = h->obs.as<double>();
 
-    CILQR_CUDA(cudaMemsetAsync(V.cnt, 0, (size_t)(n_cnt + chunks) * sizeof(int), st));
-    const dim3 tb(32, 8);
-    transpose_in_kernel<<<dim3((2 * N + 31) / 32, chunks), tb, 0, st>>>(A.U, V.U, B, 2 * N, Bp);
-    CILQR_LAUNCH_CHECK();
-    transpose_in_kernel<<<dim3((P.npoly + 31) / 32, chunks), tb, 0, st>>>(A.poly, V.poly, B, P.npoly, Bp);
-    CILQR_LAUNCH_CHECK();
-    batch_init_kernel<<<(B + 127) / 128, 128, 0, st>>>(P, V, B, A.x0, A.xlp);
+    CILQR_CUDA(cudaMemsetAsync(V.cnt, 0, (size_t)n_cnt * sizeof(int), st));
+    batch_init_kernel<<<(B + 127) / 128, 128, 0, st>>>(P, V, B, A.x0, A.U, A.poly, A.xlp);
     CILQR_LAUNCH_CHECK();
 
     // persistent grids sized once for the full batch; later rounds find shorter lists and leave early
-    const long long items = (long long)chunks * N;
-    const int item_grid = (int)std::min<long long>((items + kItemWarps - 1) / kItemWarps, (long long)h->num_sms * h->occ_item);
-    const int sweep_grid = std::min(chunks, h->num_sms * h->occ_sweep);
+    const int E = cost_entries_per_cta(N);
+    const size_t cost_smem = (size_t)E * N * sizeof(double);
+    const int cost_grid = std::min((B + E - 1) / E, h->num_sms * h->occ_cost);
+    const long long items = (long long)B * N;
+    const int deriv_grid = (int)std::min<long long>((items + kDerivThreads - 1) / kDerivThreads, (long long)h->num_sms * h->occ_deriv);
+    const int sweep_grid = std::min((B + kSweepThreads - 1) / kSweepThreads, h->num_sms * h->occ_sweep);
     for (int r = 0; r <= P.max_iter; ++r) {
-        batch_cost_kernel<<<item_grid, kItemWarps * 32, 0, st>>>(P, V, r);
+        batch_cost_kernel<<<cost_grid, kCostThreads, cost_smem, st>>>(P, V, r);
         CILQR_LAUNCH_CHECK();
         if (r == P.max_iter) break; // the last round only evaluates J of the scenarios that ran out of iterations
         if (V.cv)
-            batch_derivs_kernel<true><<<item_grid, kItemWarps * 32, 0, st>>>(P, V, r);
+            batch_derivs_kernel<true><<<deriv_grid, kDerivThreads, 0, st>>>(P, V, r);
         else
-            batch_derivs_kernel<false><<<item_grid, kItemWarps * 32, 0, st>>>(P, V, r);
+            batch_derivs_kernel<false><<<deriv_grid, kDerivThreads, 0, st>>>(P, V, r);
         CILQR_LAUNCH_CHECK();
         batch_sweep_kernel<<<sweep_grid, kSweepThreads, 0, st>>>(P, V, r);
         CILQR_LAUNCH_CHECK();
     }
-    transpose_out_kernel<<<dim3((2 * N + 31) / 32, chunks), tb, 0, st>>>(V.U, A.U, B, 2 * N, Bp);
+    const size_t out_items = (size_t)B * (N + 1);
+    batch_output_kernel<<<(int)std::min<size_t>((out_items + 255) / 256, (size_t)h->num_sms * 8), 256, 0, st>>>(P, V, B, A.U, A.X, A.J, A.iters, A.status);
     CILQR_LAUNCH_CHECK();
-    if (A.X) {
-        transpose_out_kernel<<<dim3((4 * (N + 1) + 31) / 32, chunks), tb, 0, st>>>(V.X, A.X, B, 4 * (N + 1), Bp);
-        CILQR_LAUNCH_CHECK();
-    }
-    if (A.J) CILQR_CUDA(cudaMemcpyAsync(A.J, V.Jres, (size_t)B * sizeof(double), cudaMemcpyDeviceToDevice, st));
-    if (A.iters) CILQR_CUDA(cudaMemcpyAsync(A.iters, V.iters, (size_t)B * sizeof(int), cudaMemcpyDeviceToDevice, st));
-    if (A.status) CILQR_CUDA(cudaMemcpyAsync(A.status, V.status, (size_t)B * sizeof(int), cudaMemcpyDeviceToDevice, st));
     return 0;
 }
 
