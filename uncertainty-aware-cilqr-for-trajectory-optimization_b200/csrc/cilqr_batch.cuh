@@ -13,7 +13,7 @@
 //                                                   (only for accepted scenarios: a rejected nominal never needs derivatives)
 //     batch_sweep_kernel   thread = scenario        Riccati sweep with V_x / V_xx in registers, then the closed-loop rollout
 //
-// State lives in HBM scenario-major: one 128-byte header and N+1 step records of 144 bytes per scenario.  The (scenario, t)
+// State lives in HBM scenario-major: one 144-byte header and N+1 step records of 144 bytes per scenario.  The (scenario, t)
 // kernels index the work list flat, g = entry * N + t, so a warp's lanes walk consecutive timesteps of one or two scenarios
 // (coalesced, obstacle constants warp-uniform); the sweep kernel's lanes each stream through their own scenario's records.
 // Either way every sector that is fetched is used, however sparse the set of still-active scenarios has become.
@@ -32,11 +32,11 @@ enum { MODE_ITERATE = 0, MODE_FINAL = 1, MODE_DONE = 2 };
 // record of step t (overwritten by the gains in the sweep).  16-byte aligned pairs -> 128-bit loads.
 enum { S_X = 0, S_Y, S_V, S_TH, S_C, S_S, S_U0, S_U1, S_R, kStepD = S_R + kRec };
 // Scenario header.
-enum { H_XF = 0, H_DXS, H_POLY, H_LAMB = H_POLY + kMaxPoly, H_JOLD, H_JNEW, H_JRES, H_ITERS_MODE, H_CONV_STATUS, kHdrD };
+enum { H_XF = 0, H_DXS, H_POLY, H_LAMB = H_POLY + kMaxPoly, H_JOLD, H_JNEW, H_JRES, H_ITERS_MODE, H_CONV_STATUS, H_LIP, H_PAD, kHdrD };
 static_assert(kStepD % 2 == 0 && kHdrD % 2 == 0, "records are accessed with 128-bit loads");
 
 // Compact constant-velocity obstacle: [scenario][obstacle][8] constants + [scenario][obstacle][t] 1/b^2.
-enum { CV_X0 = 0, CV_Y0, CV_VC, CV_VS, CV_C, CV_S, CV_IA2, CV_PAD, CV_FIELDS };
+enum { CV_X0 = 0, CV_Y0, CV_VC, CV_VS, CV_C, CV_S, CV_IA2, CV_V, CV_FIELDS };
 
 struct BatchView {
     int N;
@@ -88,35 +88,43 @@ __global__ void __launch_bounds__(256) prep_obstacles_dense_kernel(DevParams P, 
 }
 // Constant-velocity obstacles with covariance-inflated size (ARBIT.cuh:58-68, :87): per obstacle the
 // constants of the prediction, per timestep only 1/b^2 (the lateral sigma grows with the lever arm v t).
+// Two passes so that sincos runs once per obstacle, not once per (obstacle, t).
 __global__ void __launch_bounds__(256) prep_obstacles_cv_kernel(DevParams P, size_t n_bj, const double *__restrict__ state0,
                                                                 const double *__restrict__ LW, const double *__restrict__ sigma, double kappa,
-                                                                double *__restrict__ ocv, double *__restrict__ oib2)
+                                                                double *__restrict__ ocv)
+{
+    for (size_t bj = blockIdx.x * (size_t)blockDim.x + threadIdx.x; bj < n_bj; bj += (size_t)gridDim.x * blockDim.x) {
+        const double v = state0[4 * bj + 2], th = state0[4 * bj + 3];
+        double s, c;
+        sincos(th, &s, &c);
+        const double dim0 = LW[2 * bj] + 2.0 * kappa * sigma[3 * bj];
+        const double a = dim0 / 2.0 + fabs(v * c) * P.t_safe + P.s_safe_a + P.ego_rad; // Obstacle.cpp:42
+        double *o = ocv + bj * CV_FIELDS;
+        o[CV_X0] = state0[4 * bj];
+        o[CV_Y0] = state0[4 * bj + 1];
+        o[CV_VC] = v * c;
+        o[CV_VS] = v * s;
+        o[CV_C] = c;
+        o[CV_S] = s;
+        o[CV_IA2] = 1.0 / a / a; // Obstacle.cpp:45
+        o[CV_V] = v;
+    }
+}
+__global__ void __launch_bounds__(256) prep_obstacles_cv_ib2_kernel(DevParams P, size_t n_bj, const double *__restrict__ LW,
+                                                                    const double *__restrict__ sigma, double kappa, const double *__restrict__ ocv,
+                                                                    double *__restrict__ oib2)
 {
     const int N = P.N;
     const size_t total = n_bj * N;
     for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
         const size_t bj = i / N;
         const int t = (int)(i - bj * N);
-        const double v = state0[4 * bj + 2], th = state0[4 * bj + 3];
-        const double sx = sigma[3 * bj], sy = sigma[3 * bj + 1], sth = sigma[3 * bj + 2];
-        double s, c, ia2, ib2;
-        sincos(th, &s, &c);
-        const double arm = v * (t * P.dt);
-        const double dim0 = LW[2 * bj] + 2.0 * kappa * sx;
+        const double *o = ocv + bj * CV_FIELDS;
+        const double sy = sigma[3 * bj + 1], sth = sigma[3 * bj + 2];
+        const double arm = o[CV_V] * (t * P.dt);
         const double dim1 = LW[2 * bj + 1] + 2.0 * kappa * sqrt(sy * sy + sth * sth * arm * arm);
-        ellipse_axes(P, v, c, s, dim0, dim1, ia2, ib2);
-        oib2[i] = ib2;
-        if (t == 0) {
-            double *o = ocv + bj * CV_FIELDS;
-            o[CV_X0] = state0[4 * bj];
-            o[CV_Y0] = state0[4 * bj + 1];
-            o[CV_VC] = v * c;
-            o[CV_VS] = v * s;
-            o[CV_C] = c;
-            o[CV_S] = s;
-            o[CV_IA2] = ia2;
-            o[CV_PAD] = 0.0;
-        }
+        const double b = dim1 / 2.0 + fabs(o[CV_VS]) * P.t_safe + P.s_safe_b + P.ego_rad + 1.0; // Obstacle.cpp:43 (hard-coded +1)
+        oib2[i] = 1.0 / b / b;                                                                  // Obstacle.cpp:46
     }
 }
 // Position of a constant-velocity obstacle at step t; one expression shared by every consumer of the compact form.
@@ -165,6 +173,17 @@ __global__ void __launch_bounds__(128) batch_init_kernel(DevParams P, BatchView 
 #pragma unroll
     for (int k = 0; k < kMaxPoly; ++k)
         h[H_POLY + k] = k < P.npoly ? poly[(size_t)b * P.npoly + k] : 0.0;
+    {
+        PolyY yf;
+        yf.pl.x_first = xf;
+        yf.pl.dxs = h[H_DXS];
+        yf.npoly = P.npoly;
+#pragma unroll
+        for (int k = 0; k < kMaxPoly; ++k)
+            yf.c[k] = h[H_POLY + k];
+        h[H_LIP] = polyline_lipschitz(P, yf);
+        h[H_PAD] = 0.0;
+    }
     h[H_LAMB] = 1.0;
     h[H_JOLD] = DBL_MAX;
     h[H_JNEW] = 0.0;
@@ -258,7 +277,7 @@ __global__ void __launch_bounds__(kCostThreads) batch_cost_kernel(DevParams P, B
             const double2 xy = ld2(r + S_X), u = ld2(r + S_U0);
             const double v = r[S_V];
             double cx, cy;
-            closest_point_f(P, yf.pl, yf, xy.x, xy.y, cx, cy);
+            closest_point_lip(P, yf.pl, yf, h[H_LIP], xy.x, xy.y, cx, cy);
             const double ex = xy.x - cx, ey = xy.y - cy, ev = v - P.v_des;
             sJ[idx] = tracking_cost(P, ex, ey, ev, u.x, u.y);
             st2(r + S_R, 2.0 * P.w_pos * ex, 2.0 * P.w_pos * ey);
@@ -350,16 +369,20 @@ __global__ void __launch_bounds__(kDerivThreads, 2) batch_derivs_kernel(DevParam
                 const double tt = t * P.dt;
                 const double *oc = V.ocv + (size_t)b * n_obs * CV_FIELDS, *ob = V.oib2 + (size_t)b * n_obs * N + t;
                 double2 n0 = ld2(oc), n1 = ld2(oc + 2), n2 = ld2(oc + 4), n3 = ld2(oc + 6);
-                double nib = ob[0];
+                double nib = ob[0], nib2 = n_obs > 1 ? ob[N] : 0.0;
 #pragma unroll 1
                 for (int j = 0; j < n_obs; ++j) {
                     const double xo = n0.x + n1.x * tt, yo = n0.y + n1.y * tt; // cv_position
                     const double co = n2.x, so = n2.y, ia2 = n3.x, ib2 = nib;
-                    if (j + 1 < n_obs) { // the next obstacle's record travels while this one is evaluated
+                    // the next obstacle's constants (warp-uniform, cached) and the 1/b^2 stream two obstacles ahead (HBM) travel
+                    // while this one is evaluated
+                    nib = nib2;
+                    if (j + 1 < n_obs) {
                         const double *o2 = oc + (size_t)(j + 1) * CV_FIELDS;
                         n0 = ld2(o2); n1 = ld2(o2 + 2); n2 = ld2(o2 + 4); n3 = ld2(o2 + 6);
-                        nib = ob[(size_t)(j + 1) * N];
                     }
+                    if (j + 2 < n_obs)
+                        nib2 = ob[(size_t)(j + 2) * N];
                     obstacle_terms<true>(P, x, y, ce, se, xo, yo, co, so, ia2, ib2, g0, g1, h00, h01, h11, bo);
                 }
             } else {
@@ -388,6 +411,13 @@ __global__ void __launch_bounds__(kDerivThreads, 2) batch_derivs_kernel(DevParam
 
 // ------------------------------------------------------------------------------------------------- Riccati sweep + rollout
 __device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+// A prefetch brings one 32-byte sector: a step record (144 bytes, 16-byte aligned) lies in the five sectors touched here.
+__device__ __forceinline__ void prefetch_step(const double *r)
+{
+#pragma unroll
+    for (int k = 0; k < 5; ++k)
+        prefetch_l2(r + 4 * k);
+}
 
 // What one backward step reads from step record j: (v, cos, sin) feed step j-1 (A, B are linearised about column j+1), the
 // rest feeds step j.
@@ -436,6 +466,10 @@ __global__ void __launch_bounds__(kSweepThreads, 12) batch_sweep_kernel(DevParam
         double *h = V.header(b);
         double *rec = V.step(b, 0);
         const double lamb = h[H_LAMB];
+#ifdef CILQR_SWEEP_CLOCKS
+        unsigned long long g0, g1, g2;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g0));
+#endif
         // ---- iLQR::backward_pass (iLQR.cpp:91-195): gains overwrite the derivative records
         RiccatiState S;
         RiccatiIn I;
@@ -452,10 +486,8 @@ __global__ void __launch_bounds__(kSweepThreads, 12) batch_sweep_kernel(DevParam
             double *rj = rec + (size_t)j * kStepD;
             if (j > 0)
                 load_sweep_rec(rj - kStepD, nxt);
-            if (j >= kSweepAhead) { // record j - kSweepAhead on its way to L2 (144 bytes: two lines at most)
-                prefetch_l2(rj - kSweepAhead * kStepD);
-                prefetch_l2(rj - kSweepAhead * kStepD + kStepD - 1);
-            }
+            if (j >= kSweepAhead) // record j - kSweepAhead on its way to L2
+                prefetch_step(rj - kSweepAhead * kStepD);
             I.acc = cur.u0;
 #pragma unroll
             for (int f = 0; f < kRec; ++f)
@@ -474,6 +506,9 @@ __global__ void __launch_bounds__(kSweepThreads, 12) batch_sweep_kernel(DevParam
             hdr_ints(h, H_ITERS_MODE).y = MODE_DONE;
             continue;
         }
+#ifdef CILQR_SWEEP_CLOCKS
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g1));
+#endif
         // ---- iLQR::forward_pass (iLQR.cpp:68-86), full step, in place: the candidate is accepted by construction (lagged test)
         {
             const double2 a = ld2(rec + S_X), c2 = ld2(rec + S_V), cs = ld2(rec + S_C);
@@ -486,10 +521,8 @@ __global__ void __launch_bounds__(kSweepThreads, 12) batch_sweep_kernel(DevParam
                 double *rt = rec + (size_t)t * kStepD;
                 if (t + 1 < N)
                     load_forward_in(rt + kStepD, G);
-                if (t + kSweepAhead <= N) {
-                    prefetch_l2(rt + kSweepAhead * kStepD);
-                    prefetch_l2(rt + kSweepAhead * kStepD + kStepD - 1);
-                }
+                if (t + kSweepAhead <= N)
+                    prefetch_step(rt + kSweepAhead * kStepD);
                 double u0 = F.u0, u1 = F.u1;
                 apply_gains(F.g, n0 - o0, n1 - o1, n2 - o2, n3 - o3, u0, u1);
                 double m0, m1, m2, m3;
@@ -504,6 +537,11 @@ __global__ void __launch_bounds__(kSweepThreads, 12) batch_sweep_kernel(DevParam
                 F = G;
             }
         }
+#ifdef CILQR_SWEEP_CLOCKS
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g2));
+        if (threadIdx.x == 0 && (round == 12 || round == 0) && (blockIdx.x % 37) == 0)
+            printf("round %d block %d cnt %d: start %llu ns  backward %llu ns  forward %llu ns\n", round, blockIdx.x, cnt, g0 % 100000000ull, g1 - g0, g2 - g1);
+#endif
         // ---- iLQR.cpp:219-228
         h[H_LAMB] = lamb / P.lamb_factor;
         const int2 cst = hdr_ints(h, H_CONV_STATUS);

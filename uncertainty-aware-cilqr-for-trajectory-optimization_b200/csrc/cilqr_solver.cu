@@ -748,7 +748,9 @@ int cilqr_set_obstacles_cv(cilqr_handle h, int B, int n_obs, const double *state
     if (int rc = stage_in(h, 2, sigma, n_bj * 3, mem, st, &d_sg)) return rc;
     if (int rc = h->obs_b.reserve(n_bj * (CV_FIELDS + N) * sizeof(double))) return rc;
     double *ocv = h->obs_b.as<double>(), *oib2 = ocv + n_bj * CV_FIELDS;
-    prep_obstacles_cv_kernel<<<prep_grid(n_bj * N, h->num_sms), 256, 0, st>>>(h->dp, n_bj, d_s, d_lw, d_sg, kappa, ocv, oib2);
+    prep_obstacles_cv_kernel<<<prep_grid(n_bj, h->num_sms), 256, 0, st>>>(h->dp, n_bj, d_s, d_lw, d_sg, kappa, ocv);
+    CILQR_LAUNCH_CHECK();
+    prep_obstacles_cv_ib2_kernel<<<prep_grid(n_bj * N, h->num_sms), 256, 0, st>>>(h->dp, n_bj, d_lw, d_sg, kappa, ocv, oib2);
     CILQR_LAUNCH_CHECK();
     h->obs_cv = 1;
     h->obs_ready = false;
