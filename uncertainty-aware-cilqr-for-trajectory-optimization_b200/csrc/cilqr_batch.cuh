@@ -52,6 +52,7 @@ struct BatchView {
     __device__ __forceinline__ double *header(int b) const { return hdr + (size_t)b * kHdrD; }
     __device__ __forceinline__ double *step(int b, int t) const { return rec + ((size_t)b * (N + 1) + t) * kStepD; }
 };
+__device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 __device__ __forceinline__ int2 &hdr_ints(double *h, int which) { return *reinterpret_cast<int2 *>(h + which); }
 __device__ __forceinline__ double2 ld2(const double *p) { return *reinterpret_cast<const double2 *>(p); }
 __device__ __forceinline__ void st2(double *p, double a, double b) { *reinterpret_cast<double2 *>(p) = make_double2(a, b); }
@@ -356,13 +357,45 @@ __global__ void __launch_bounds__(kDerivThreads, 2) batch_derivs_kernel(DevParam
     const int *list = V.list(round + 1);
     const int n_obs = V.n_obs;
     const long long total = (long long)cnt * N;
-    for (long long g = (long long)blockIdx.x * kDerivThreads + threadIdx.x; g < total; g += (long long)gridDim.x * kDerivThreads) {
-        const int e = (int)(g / N), t = (int)(g - (long long)e * N);
-        const int b = list[e];
+    // Software pipeline over the thread's items: an item starts with a chain of dependent loads (list entry -> step record),
+    // a few microseconds that 16 resident warps per SM do not hide.  So the list entry is fetched two items ahead and the step
+    // record one item ahead, while the obstacle loop of the current item runs.
+    const long long stride = (long long)gridDim.x * kDerivThreads;
+    long long g = (long long)blockIdx.x * kDerivThreads + threadIdx.x;
+    int b = 0, t = 0, b_next = 0;
+    double2 xy = make_double2(0, 0), cs = xy, u = xy;
+    double v = 0;
+    if (g < total) {
+        const int e = (int)(g / N);
+        t = (int)(g - (long long)e * N);
+        b = list[e];
+        const double *r = V.step(b, t);
+        xy = ld2(r + S_X); cs = ld2(r + S_C); u = ld2(r + S_U0); v = r[S_V];
+        if (g + stride < total)
+            b_next = list[(int)((g + stride) / N)];
+    }
+    for (; g < total; g += stride) {
         double *r = V.step(b, t);
-        const double2 xy = ld2(r + S_X), cs = ld2(r + S_C), u = ld2(r + S_U0);
-        const double v = r[S_V];
-        const double x = xy.x, y = xy.y, ce = cs.x, se = cs.y;
+        const double x = xy.x, y = xy.y, ce = cs.x, se = cs.y, vv = v;
+        const double2 uu = u;
+        const int bn = b_next, tn = (int)((g + stride) % N);
+        if (g + stride < total) {
+            const double *rn = V.step(bn, tn);
+            xy = ld2(rn + S_X); cs = ld2(rn + S_C); u = ld2(rn + S_U0); v = rn[S_V];
+            if (g + 2 * stride < total)
+                b_next = list[(int)((g + 2 * stride) / N)];
+            if (CV && n_obs > 0) {
+                // the next item's obstacle constants (64 B per obstacle; the N threads of a scenario share the block and each
+                // asks for the sectors tn, tn + N, ...) and the head of its 1/b^2 stream on their way to L2
+                const char *oc_n = reinterpret_cast<const char *>(V.ocv + (size_t)bn * n_obs * CV_FIELDS);
+                for (int sct = tn; sct < 2 * n_obs; sct += N)
+                    prefetch_l2(oc_n + 32 * sct);
+                const double *ob_n = V.oib2 + (size_t)bn * n_obs * N + tn;
+                prefetch_l2(ob_n);
+                if (n_obs > 1)
+                    prefetch_l2(ob_n + N);
+            }
+        }
         double g0 = 0, g1 = 0, h00 = 0, h01 = 0, h11 = 0, bo = 0;
         if (n_obs > 0) {
             if (CV) {
@@ -399,18 +432,19 @@ __global__ void __launch_bounds__(kDerivThreads, 2) batch_derivs_kernel(DevParam
             }
         }
         double lu0, lu1, luu0, luu1, bc;
-        control_terms<true>(P, v, u.x, u.y, lu0, lu1, luu0, luu1, bc);
+        control_terms<true>(P, vv, uu.x, uu.y, lu0, lu1, luu0, luu1, bc);
         const double2 tr = ld2(r + S_R); // tracking part written by batch_cost_kernel
         st2(r + S_R, tr.x + P.w_obs * g0, tr.y + P.w_obs * g1);
         r[S_R + 3] = 2.0 * P.w_pos + P.w_obs * h00;
         st2(r + S_R + 4, P.w_obs * h01, 2.0 * P.w_pos + P.w_obs * h11);
         st2(r + S_R + 6, lu0, lu1);
         st2(r + S_R + 8, luu0, luu1);
+        b = bn;
+        t = tn;
     }
 }
 
 // ------------------------------------------------------------------------------------------------- Riccati sweep + rollout
-__device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 // A prefetch brings one 32-byte sector: a step record (144 bytes, 16-byte aligned) lies in the five sectors touched here.
 __device__ __forceinline__ void prefetch_step(const double *r)
 {
