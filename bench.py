@@ -7,14 +7,14 @@
 A "step" is one pass of the hot path over one batch of synthetic scenarios of BASELINE.json config 4 (the
 configuration the target is quoted on): 65 536 independent scenarios per GPU, horizon N = 50, 20 Gaussian-uncertain
 constant-velocity obstacles each with covariance propagation over the horizon on the device
-(cilqr_set_obstacles_cv), then the fused batched solve (cilqr_solve_batch, reference semantics n_alphas = 1), then
+(cilqr_set_obstacles_cv), then the batched solve (cilqr_solve_batch, reference semantics n_alphas = 1), then
 — for N > 1 — the single NCCL all-gather of the optimal control sequences.  Scenarios shard by batch index with no
 data-path collective, so per-GPU work is fixed as N grows ("scaling": "weak").
 
 `value`   whole-job solves/s with the inputs resident in HBM (CUDA events, max over ranks).
 `e2e`     the same metric through the C ABI with HOST (pinned) buffers: host->device copies of every input and
           device->host copies of U*, X*, J, iterations, status are inside the timed region.
-`roofline` the dominant kernel (solve_kernel): mandatory HBM bytes per launch / its CUDA-event duration against the
+`roofline` the solve (its round kernels together): mandatory HBM bytes per solve of the batch / its CUDA-event duration against the
           measured copy bandwidth of MEASURED_PEAKS.json; the solver is FP64-issue bound, so `fp64` reports the
           algorithmic FP64 flop rate against an FMA micro-benchmark run on the same GPU.
 `costmap_warp` the second half of BASELINE.json's metric: HBM GB/s of costmap_warp_batch (config 5, one grid size).
@@ -71,6 +71,17 @@ def measured_peaks():
         return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def recorded_traffic(key):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu capture of this same command
+    (profiles/traffic.json, written by tools/ncu_summary.py traffic); None when no capture is recorded."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            v = json.load(f).get(key)
+        return float(v) if v is not None else None
+    except Exception:
+        return None
+
+
 # ------------------------------------------------------------------------------------------------ algorithmic counts (DESIGN.md §5)
 def solver_bytes_per_solve(N, n_obs):
     """Mandatory HBM traffic of one solve with the compact obstacle form:
@@ -79,15 +90,21 @@ def solver_bytes_per_solve(N, n_obs):
     return 32 + 16 * N + 48 + 16 + 72 * n_obs + 32 * (N + 1) + 16 * N + 16
 
 
-def solver_flops_per_iteration(N, n_obs, S=200):
-    """Algorithmic FP64 flops of one iLQR iteration of one scenario, each operation counted once (the warp-replicated
-    Riccati / rollout arithmetic is NOT multiplied by 32); exp / sincos counted as 20 flops:
-      closest point   N * S * 6        (2 sub, 2 mul, 1 add, 1 compare per polyline sample; get_J shares the pass)
-      obstacles       N * n_obs * 2 * (46 + 20)   (two ellipses per obstacle, one exp each)
-      control cost    N * (4 * 22 + 16)
-      Riccati sweep   N * 330          (sparse A, B; symmetric V_xx; closed-form 2x2 inverse)
-      rollout         N * (40 + 20)    (gain application, bicycle step, one sincos)"""
-    return N * S * 6 + N * n_obs * 2 * 66 + N * 104 + N * 330 + N * 60
+def solver_flops(N, n_obs, cost_passes, deriv_passes):
+    """Algorithmic FP64 flops of the work the solver actually ran (cilqr_solve_stats), each operation counted once;
+    exp / sincos counted as 20 flops:
+      cost pass (Constraints::get_J), per scenario:            N * (5 polyline samples * 22 + 14)
+          (the bounded closest-point walk visits ~5 samples: 12 flops for the polynomial, 10 for offsets and bound)
+      derivative + backward + forward pass, per scenario:
+          obstacles       N * n_obs * 2 * (46 + 20)   (two ellipses per obstacle, one exp each)
+          control cost    N * (4 * 22 + 16)
+          Riccati sweep   N * 330          (sparse A, B; symmetric V_xx; closed-form 2x2 inverse)
+          rollout         N * (40 + 20)    (gain application, bicycle step, one sincos)
+    The reference's `iters` counter is NOT used: it also counts iterations in which a rejected nominal only waits for lamb
+    to pass lamb_max, which cost nothing here."""
+    per_cost = N * (5 * 22 + 14)
+    per_deriv = N * n_obs * 2 * 66 + N * 104 + N * 330 + N * 60
+    return cost_passes * per_cost + deriv_passes * per_deriv, per_cost, per_deriv
 
 
 # ------------------------------------------------------------------------------------------------ clocks during the timed region
@@ -101,7 +118,7 @@ class ClockSampler:
         self.proc = None
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(gpu_index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
-                                          "-lms", "100"], stdout=self.tmp, stderr=subprocess.DEVNULL)
+                                          "-lms", "20"], stdout=self.tmp, stderr=subprocess.DEVNULL)
         except Exception:
             self.proc = None
 
@@ -269,7 +286,7 @@ def bench_warp(args, device, hbm_peak, peak_kind):
                                    % (T, T, S, S, WARP_POSES, chunk), "l2": "working set per chunk larger than L2"},
             "value_only_gbs": res["value_only"]["gbs"],
             "roofline": {"bound": "hbm", "achieved": best["gbs"], "peak": hbm_peak, "unit": "GB/s", "frac": best["gbs"] / hbm_peak,
-                         "traffic": None, "peak_source": peak_kind,
+                         "traffic": recorded_traffic("warp_dram_bytes_per_launch") if T == WARP_T else None, "peak_source": peak_kind,
                          "algorithmic_bytes_per_cell": "4 B source read + 4 B value write + 4 B index write"},
             "launches": 2 * 2 * ((WARP_POSES + chunk - 1) // chunk)}
 
@@ -337,6 +354,7 @@ def run_b200_arm(args):
     kernel_ms = float(np.mean([a.elapsed_time(b) for a, b in kern_ev]))
     iters = solver.iterations.cpu().numpy()
     status = solver.status.cpu().numpy()
+    stats = solver.solve_stats() if args.n_alphas == 1 else (int(iters.sum()), int(iters.sum()), int(iters.max()))
     value = world * B * args.steps / (total_ms * 1e-3)
 
     # ---- end to end through the C ABI with pinned HOST buffers (copies inside the timed region)
@@ -382,14 +400,15 @@ def run_b200_arm(args):
     mean_iters = float(iters.mean())
     bytes_launch = B * solver_bytes_per_solve(N, n_obs)
     achieved = bytes_launch / (kernel_ms * 1e-3) / 1e9
-    flops_launch = B * mean_iters * solver_flops_per_iteration(N, n_obs)
+    flops_launch, per_cost, per_deriv = solver_flops(N, n_obs, stats[0], stats[1])
     fp64_peak = C.c_double(0.0)
     fp64 = None
     if hasattr(lib, "cilqr_measure_fp64_peak") and lib.cilqr_measure_fp64_peak(C.byref(fp64_peak)) == 0:
         tf = flops_launch / (kernel_ms * 1e-3) / 1e12
         fp64 = {"achieved": tf, "peak": fp64_peak.value, "unit": "TFLOP/s", "frac": tf / fp64_peak.value,
                 "peak_source": "DFMA micro-benchmark on this GPU (cilqr_measure_fp64_peak)",
-                "flops_per_iteration": solver_flops_per_iteration(N, n_obs), "mean_iterations": mean_iters}
+                "flops_per_cost_pass": per_cost, "flops_per_derivative_pass": per_deriv,
+                "cost_passes_per_solve": stats[0] / B, "derivative_passes_per_solve": stats[1] / B, "rounds": stats[2]}
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
@@ -397,12 +416,16 @@ def run_b200_arm(args):
         "config": {"workload": "config4: 65536 scenarios x 20 Gaussian-uncertain obstacles (covariance propagated on device), N=50, "
                                "n_alphas=%d, per GPU" % args.n_alphas,
                    "batch_per_gpu": B, "horizon": N, "n_obs": n_obs, "n_alphas": args.n_alphas, "parallelism": "scenario shards x%d" % world,
-                   "l2": "inputs larger than L2 (%.1f GB of obstacle records re-generated and re-read every step)" % (B * n_obs * 48 * N / 1e9),
+                   "l2": "working set larger than L2 (%.2f GB of obstacle data re-generated every step + %.2f GB of solver state)"
+                         % (B * n_obs * 8 * (8 + N) / 1e9, B * (18 + 18 * (N + 1)) * 8 / 1e9),
                    "collective": "all_gather U* (NCCL)" if world > 1 else "none"},
         "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches),
-        "roofline": {"kernel": "solve_kernel<false>" if args.n_alphas == 1 else "solve_kernel<true>", "bound": "hbm", "achieved": achieved,
-                     "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": None, "peak_source": peak_kind,
-                     "kernel_ms": kernel_ms, "algorithmic_bytes_per_solve": solver_bytes_per_solve(N, n_obs),
+        "roofline": {"kernel": ("cilqr_solve_batch = batch_init + <= %d rounds of batch_cost / batch_derivs / batch_sweep + batch_output "
+                                "(one 'launch' = one solve of the batch; batch_derivs_kernel dominates, see profiles/)" % (p.max_iterations + 1))
+                               if args.n_alphas == 1 else "solve_kernel<true>",
+                     "bound": "hbm", "achieved": achieved,
+                     "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": recorded_traffic("solver_dram_bytes_per_step"),
+                     "peak_source": peak_kind, "kernel_ms": kernel_ms, "algorithmic_bytes_per_solve": solver_bytes_per_solve(N, n_obs),
                      "note": "the solver is FP64-issue/latency bound, not HBM bound: see fp64"},
         "fp64": fp64,
         "solver": {"mean_iterations": mean_iters, "status_hist": {"tolerance": int((status == 0).sum()), "max_iter": int((status == 1).sum()),

@@ -159,6 +159,13 @@ int cilqr_solve_batch(cilqr_handle h, int B, const double *x0, double *U, const 
                       const double *xlp, int n_alphas, int merit, double *X, double *J,
                       int32_t *iters, int32_t *status, int mem, void *stream);
 
+/* Work done by the last cilqr_solve_batch call with n_alphas == 1 (measurement helper, no reference counterpart): how many
+ * times the cost (Constraints::get_J) and the derivative pass + backward/forward pass ran, summed over the scenarios, and
+ * the number of solver rounds that had work.  The reference's own iteration counter (`iters`) also counts the iterations in
+ * which a rejected nominal only waits for lamb to exceed lamb_max; those cost nothing here.  Synchronises `stream`. */
+int cilqr_solve_stats(cilqr_handle h, int64_t *cost_passes, int64_t *deriv_passes, int32_t *rounds,
+                      void *stream);
+
 /* ---- stage entry points (used by the parity tests; same device code as the fused solve) ---- */
 
 /* iLQR::get_nominal_trajectory (iLQR.cpp:51-62) over Model::forward_simulate (Model.cpp:17-30). */

@@ -38,7 +38,10 @@ def launches(path):
     h = rows[0]
     ki, vi, gi, bi = h.index("Kernel Name"), h.index("Metric Value"), h.index("Grid Size"), h.index("Block Size")
     agg = collections.OrderedDict()
+    mi = h.index("Metric Name")
     for r in rows[1:]:
+        if r[mi] != "gpu__time_duration.sum":
+            continue
         k = r[ki].split("(")[0]
         a = agg.setdefault(k, [0, 0.0, r[gi], r[bi]])
         a[0] += 1
@@ -72,7 +75,42 @@ def full(path):
         print()
 
 
+def traffic(path):
+    """DRAM bytes (dram__bytes_read.sum + dram__bytes_write.sum) per launch from a launch-list csv that carries those two
+    metrics: the solver's kernels summed over the LAST complete bench step, the costmap warp kernel averaged per launch.
+    Prints the JSON that bench.py reads from profiles/traffic.json."""
+    import json
+    rows = read_csv_lines(open(path).read())
+    h = rows[0]
+    ii, ki, mi, vi, ui = h.index("ID"), h.index("Kernel Name"), h.index("Metric Name"), h.index("Metric Value"), h.index("Metric Unit")
+    scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    per = collections.OrderedDict()
+    for r in rows[1:]:
+        if not r[mi].startswith("dram__bytes"):
+            continue
+        k = per.setdefault(r[ii], [r[ki].split("(")[0].replace("void ", ""), 0.0])
+        k[1] += float(r[vi].replace(",", "")) * scale.get(r[ui], 1.0)
+    seq = list(per.values())
+    starts = [i for i, (k, _) in enumerate(seq) if k.startswith("prep_obstacles_cv_kernel")]
+    out = {}
+    if starts:
+        step = []
+        for k, v in seq[starts[-1]:]:
+            if not (k.startswith("prep_") or k.startswith("batch_")):
+                break
+            step.append((k, v))
+        out["solver_dram_bytes_per_step"] = sum(v for _, v in step)
+        out["solver_dram_bytes_by_kernel"] = {}
+        for k, v in step:
+            out["solver_dram_bytes_by_kernel"][k] = out["solver_dram_bytes_by_kernel"].get(k, 0.0) + v
+    warp = [v for k, v in seq if k.startswith("warp_")]
+    if warp:
+        out["warp_dram_bytes_per_launch"] = sum(warp) / len(warp)
+        out["warp_launches"] = len(warp)
+    print(json.dumps(out, indent=1))
+
+
 if __name__ == "__main__":
     mode = sys.argv[1]
     for p in sys.argv[2:]:
-        (launches if mode == "launches" else full)(p)
+        {"launches": launches, "traffic": traffic}.get(mode, full)(p)

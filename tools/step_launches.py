@@ -10,11 +10,12 @@ import sys
 
 def main():
     path = sys.argv[1]
-    first = sys.argv[2] if len(sys.argv) > 2 else "prep_cv"
+    first = sys.argv[2] if len(sys.argv) > 2 else "prep_obstacles_cv_kernel"
     rows = list(csv.reader(io.StringIO("".join(l for l in open(path) if l.startswith('"')))))
     h = rows[0]
     ki, vi, gi = h.index("Kernel Name"), h.index("Metric Value"), h.index("Grid Size")
-    seq = [(r[ki].split("(")[0].replace("void ", ""), float(r[vi]) / 1e3, r[gi]) for r in rows[1:]]
+    mi = h.index("Metric Name")
+    seq = [(r[ki].split("(")[0].replace("void ", ""), float(r[vi]) / 1e3, r[gi]) for r in rows[1:] if r[mi] == "gpu__time_duration.sum"]
     idx = [i for i, (k, _, _) in enumerate(seq) if k.startswith(first)]
     start = idx[-1] if idx else 0
     tot, agg = 0.0, {}

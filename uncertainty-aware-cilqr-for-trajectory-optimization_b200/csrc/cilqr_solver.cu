@@ -16,6 +16,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <new>
+#include <vector>
 
 namespace cilqr
 {
@@ -184,172 +185,6 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, 4) solve_kernel(const Sol
     }
 }
 
-// ------------------------------------------------------------------------------------------------- fused solve, v2 (reference semantics)
-// solve_kernel<false> runs the sequential phases (Riccati sweep, rollout) redundantly on all 32 lanes of the scenario's warp:
-// ncu showed the FP64 pipe 59 % busy with mostly replicated work (profiles/r01a_full.txt).  Here a CTA owns kSlots scenario
-// slots.  Phase D (derivatives, lane = timestep) still gives every slot a whole warp; phases B and F of ALL slots are then run by
-// warp 0 with lane = slot — one instruction stream for kSlots scenarios, each lane keeping its slot's V_x / V_xx in registers — while
-// the other warps wait at the CTA barrier without using issue slots.  Slots refill independently from the global queue, so a
-// scenario that stops early never idles its warp.  Same device functions, same arithmetic, same results as solve_kernel<false>.
-constexpr int kSlots = 8;
-
-struct SlotHdr {
-    double lamb;
-    int need_bf, finite, open_loop, pad;
-};
-
-__device__ __forceinline__ void finalize_slot(const SolveArgs &A, const WarpSmem &W, Polyline pl, int b, int iters, int status, int lane)
-{
-    const DevParams &P = A.P;
-    const int N = P.N;
-    store_controls(W, A.U + (size_t)b * 2 * N, N, lane);
-    if (A.X)
-        store_states(W, A.X + (size_t)b * 4 * (N + 1), N, lane);
-    if (A.J) { // J = get_J(X_result, U_result)
-        phase_derivs<false>(P, W, pl, nullptr, 0, false, lane);
-        const double J = sum_sequential(W.Jt, N);
-        if (lane == 0)
-            A.J[b] = J;
-    }
-    if (lane == 0) {
-        if (A.iters) A.iters[b] = iters;
-        if (A.status) A.status[b] = status;
-    }
-    __syncwarp();
-}
-
-__global__ void __launch_bounds__(kSlots * 32, 2) solve_kernel_v2(const SolveArgs A)
-{
-    extern __shared__ double smem[];
-    const DevParams &P = A.P;
-    const int N = P.N;
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int stride = slot_stride_doubles(N, P.S);
-    const WarpSmem W = carve(smem + (size_t)warp * stride, N, P.S);
-    SlotHdr *hdr = reinterpret_cast<SlotHdr *>(smem + (size_t)kSlots * stride);
-
-    int b = -1, iters = 0, status = CILQR_ST_MAX_ITER;
-    bool queue_empty = false, fresh = false;
-    double lamb = 1.0, J_old = DBL_MAX;
-    Polyline pl{0.0, 0.0};
-    const double *obs = nullptr;
-
-    // Takes the next scenario from the global queue into this warp's slot.  Its nominal rollout (iLQR.cpp:203) is left to the next
-    // lane-per-slot pass of warp 0 (open-loop form of the forward pass), so it costs one lane instead of a replicated warp.
-    auto refill = [&]() {
-        if (b >= 0 || queue_empty)
-            return;
-        int nb = 0;
-        if (lane == 0)
-            nb = atomicAdd(A.counter, 1);
-        nb = __shfl_sync(0xffffffffu, nb, 0);
-        if (nb >= A.B) {
-            queue_empty = true;
-            return;
-        }
-        b = nb;
-        pl.x_first = A.xlp[2 * b];
-        pl.dxs = (A.xlp[2 * b + 1] - A.xlp[2 * b]) / P.S; // Constraints.cpp:32
-        build_polyline(P, A.poly + (size_t)b * P.npoly, pl, W.Y, lane);
-        load_controls(W, A.U + (size_t)b * 2 * N, N, lane);
-        if (lane < 4)
-            W.X[lane * (N + 1)] = A.x0[4 * (size_t)b + lane];
-        __syncwarp();
-        obs = A.obs + (size_t)b * A.n_obs * OB_FIELDS * N;
-        lamb = 1.0;
-        J_old = DBL_MAX;
-        iters = 0;
-        status = CILQR_ST_MAX_ITER;
-        fresh = true;
-    };
-
-#ifdef CILQR_PHASE_CLOCKS
-    long long c_d = 0, c_w1 = 0, c_bf = 0, c_post = 0, n_tick = 0, n_bf = 0, t0 = clock64(), t1;
-#define CK(acc) do { t1 = clock64(); acc += t1 - t0; t0 = t1; } while (0)
-#else
-#define CK(acc) do { } while (0)
-#endif
-    for (;;) {
-        refill();
-        // phase D and the (one-iteration-lagged) accept test of iLQR.cpp:217-219
-        bool need_bf = false, converged = false;
-        double J_new = 0.0;
-        if (b >= 0 && !fresh) {
-            ++iters;
-            phase_derivs<true>(P, W, pl, obs, A.n_obs, false, lane);
-            J_new = sum_sequential(W.Jt, N);
-            if (!(J_new < J_old)) { // rejected: the nominal never changes again, only lamb and the counter advance (see solve_kernel)
-                lamb = lamb * P.lamb_factor;
-                for (;;) {
-                    if (lamb > P.lamb_max) { status = CILQR_ST_LAMB_MAX; break; }
-                    if (iters >= P.max_iter) { status = CILQR_ST_MAX_ITER; break; }
-                    ++iters;
-                    lamb = lamb * P.lamb_factor;
-                }
-                finalize_slot(A, W, pl, b, iters, status, lane);
-                b = -1;
-                refill(); // the successor's rollout joins this tick's lane-per-slot pass
-            } else {
-                converged = fabs(J_new - J_old) < P.tol;
-                need_bf = true;
-            }
-        }
-        if (lane == 0) {
-            hdr[warp].need_bf = (need_bf || (b >= 0 && fresh)) ? 1 : 0;
-            hdr[warp].open_loop = (b >= 0 && fresh) ? 1 : 0;
-            hdr[warp].lamb = lamb;
-        }
-        CK(c_d);
-        if (!__syncthreads_or((b >= 0 || !queue_empty) ? 1 : 0))
-            break;
-        CK(c_w1);
-        // phases B and F of every slot that accepted (and the nominal rollout of fresh slots): warp 0, lane = slot
-        if (warp == 0 && lane < kSlots && hdr[lane].need_bf) {
-            const WarpSmem Ws = carve(smem + (size_t)lane * stride, N, P.S);
-            const bool open_loop = hdr[lane].open_loop != 0;
-            bool fin = true;
-            if (!open_loop)
-                fin = phase_backward<true>(P, Ws, hdr[lane].lamb, 0);
-            if (fin)
-                phase_forward_inplace<true>(P, Ws, 0, open_loop);
-            hdr[lane].finite = fin ? 1 : 0;
-        }
-#ifdef CILQR_PHASE_CLOCKS
-        n_tick++;
-        n_bf += __popc(__ballot_sync(0xffffffffu, warp == 0 && lane < kSlots && hdr[lane < kSlots ? lane : 0].need_bf));
-#endif
-        __syncthreads();
-        CK(c_bf);
-        if (b >= 0 && fresh) {
-            fresh = false;
-        } else if (need_bf) {
-            if (!hdr[warp].finite) {
-                finalize_slot(A, W, pl, b, iters, CILQR_ST_NONFINITE, lane);
-                b = -1;
-            } else {
-                lamb = lamb / P.lamb_factor;
-                if (converged) {
-                    finalize_slot(A, W, pl, b, iters, CILQR_ST_TOLERANCE, lane);
-                    b = -1;
-                } else {
-                    J_old = J_new;
-                    if (iters >= P.max_iter) {
-                        finalize_slot(A, W, pl, b, iters, CILQR_ST_MAX_ITER, lane);
-                        b = -1;
-                    }
-                }
-            }
-        }
-        CK(c_post);
-    }
-#ifdef CILQR_PHASE_CLOCKS
-    if (blockIdx.x < 2 && lane == 0 && (warp == 0 || warp == 3))
-        printf("cta %d warp %d: ticks %lld  D %lld  wait1 %lld  BF+wait2 %lld  post %lld  (cycles per tick: %lld %lld %lld %lld)  slots in BF per tick %.2f\n",
-               blockIdx.x, warp, n_tick, c_d, c_w1, c_bf, c_post, c_d / n_tick, c_w1 / n_tick, c_bf / n_tick, c_post / n_tick, (double)n_bf / n_tick);
-#endif
-#undef CK
-}
-
 // ------------------------------------------------------------------------------------------------- stage kernel
 enum { STAGE_ROLLOUT = 0, STAGE_STATE_COST, STAGE_CONTROL_COST, STAGE_COST, STAGE_BACKWARD, STAGE_FORWARD };
 
@@ -475,14 +310,14 @@ struct cilqr_solver {
     int max_batch, max_obs;
     int cur_B = 0, cur_nobs = 0; // obstacle set currently resident
     int num_sms = 0;
-    bool v2_ok = false;          // solve_kernel_v2 fits in shared memory for this horizon
     int occ_cost = 1, occ_deriv = 1, occ_sweep = 1; // resident CTAs per SM of the round kernels
-    int variant = 3;             // 3 = batch-synchronous rounds (default), 2 = slot kernel, 1 = one warp per scenario (A/B switch CILQR_SOLVER)
+    int variant = 3;             // 3 = batch-synchronous rounds (default), 1 = fused one-warp-per-scenario kernel (A/B switch CILQR_SOLVER)
     DevBuf obs;                  // obstacle records [scenario][obstacle][field][t]; expanded on demand when obs_cv
     bool obs_ready = false;
     DevBuf obs_b;                // compact constant-velocity obstacles (cilqr_batch.cuh)
     int obs_cv = 0;              // obs_b holds the compact constant-velocity form
     DevBuf bws;                  // state of the batch-synchronous solve
+    int *last_cnt = nullptr;     // work-list lengths of the last batch-synchronous solve (device)
     DevBuf counter, scratch;
     DevBuf stage[12];            // staging for CILQR_MEM_HOST callers / stage outputs
 };
@@ -655,10 +490,6 @@ int cilqr_create(const cilqr_params *p, int max_batch, int max_obs, cilqr_handle
     CILQR_CUDA(cudaFuncSetAttribute(solve_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     CILQR_CUDA(cudaFuncSetAttribute(solve_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     CILQR_CUDA(cudaFuncSetAttribute(stage_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    const size_t smem2 = (size_t)kSlots * slot_stride_doubles(h->dp.N, h->dp.S) * sizeof(double) + kSlots * sizeof(SlotHdr);
-    h->v2_ok = smem2 <= 227 * 1024;
-    if (h->v2_ok)
-        CILQR_CUDA(cudaFuncSetAttribute(solve_kernel_v2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
     {
         const size_t cost_smem = (size_t)cost_entries_per_cta(h->dp.N) * h->dp.N * sizeof(double);
         if (cost_smem > 48 * 1024)
@@ -674,7 +505,7 @@ int cilqr_create(const cilqr_params *p, int max_batch, int max_obs, cilqr_handle
     }
     if (const char *e = getenv("CILQR_SOLVER")) { // A/B switch for measurements
         const int v = atoi(e);
-        if (v >= 1 && v <= 3) h->variant = v;
+        if (v == 1 || v == 3) h->variant = v;
     }
     if (int rc = h->counter.reserve(sizeof(int))) { delete h; return rc; }
     *out = h;
@@ -787,6 +618,7 @@ static int solve_rounds(cilqr_handle h, const SolveArgs &A, cudaStream_t st)
     V.orec = h->obs.as<double>();
 
     CILQR_CUDA(cudaMemsetAsync(V.cnt, 0, (size_t)n_cnt * sizeof(int), st));
+    h->last_cnt = V.cnt;
     batch_init_kernel<<<(B + 127) / 128, 128, 0, st>>>(P, V, B, A.x0, A.U, A.poly, A.xlp);
     CILQR_LAUNCH_CHECK();
 
@@ -812,6 +644,27 @@ static int solve_rounds(cilqr_handle h, const SolveArgs &A, cudaStream_t st)
     const size_t out_items = (size_t)B * (N + 1);
     batch_output_kernel<<<(int)std::min<size_t>((out_items + 255) / 256, (size_t)h->num_sms * 8), 256, 0, st>>>(P, V, B, A.U, A.X, A.J, A.iters, A.status);
     CILQR_LAUNCH_CHECK();
+    return 0;
+}
+
+int cilqr_solve_stats(cilqr_handle h, int64_t *cost_passes, int64_t *deriv_passes, int32_t *rounds, void *stream)
+{
+    if (!h) return fail(CILQR_E_ARG, "null handle");
+    if (!h->last_cnt) return fail(CILQR_E_STATE, "no batch-synchronous solve has run on this handle");
+    const int n = h->dp.max_iter + 2;
+    std::vector<int> c(n);
+    CILQR_CUDA(cudaMemcpyAsync(c.data(), h->last_cnt, n * sizeof(int), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    CILQR_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+    int64_t cp = 0, dp = 0;
+    int r = 0;
+    for (int i = 0; i <= h->dp.max_iter; ++i) {
+        cp += c[i];
+        dp += c[i + 1];
+        if (c[i] > 0) r = i + 1;
+    }
+    if (cost_passes) *cost_passes = cp;
+    if (deriv_passes) *deriv_passes = dp;
+    if (rounds) *rounds = r;
     return 0;
 }
 
@@ -858,24 +711,6 @@ int cilqr_solve_batch(cilqr_handle h, int B, const double *x0, double *U, const 
     if (h->cur_nobs > 0) {
         if (int rc = ensure_records(h, st)) return rc;
         A.obs = h->obs.as<double>();
-    }
-    if (n_alphas == 1 && h->v2_ok && h->variant == 2) {
-        const size_t smem2 = (size_t)kSlots * slot_stride_doubles(N, h->dp.S) * sizeof(double) + kSlots * sizeof(SlotHdr);
-        int per_sm2 = 0;
-        CILQR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm2, solve_kernel_v2, kSlots * 32, smem2));
-        if (per_sm2 < 1) return fail(CILQR_E_CUDA, "solve kernel does not fit on an SM (smem %zu B)", smem2);
-        const int grid2 = std::min((B + kSlots - 1) / kSlots, h->num_sms * per_sm2);
-        A.scratch = nullptr;
-        CILQR_CUDA(cudaMemsetAsync(A.counter, 0, sizeof(int), st));
-        solve_kernel_v2<<<grid2, kSlots * 32, smem2, st>>>(A);
-        CILQR_LAUNCH_CHECK();
-        if (int rc = fetch_out(U, A.U, (size_t)B * 2 * N, mem, st)) return rc;
-        if (int rc = fetch_out(X, A.X, (size_t)B * 4 * (N + 1), mem, st)) return rc;
-        if (int rc = fetch_out(J, A.J, (size_t)B, mem, st)) return rc;
-        if (int rc = fetch_out(iters, A.iters, (size_t)B, mem, st)) return rc;
-        if (int rc = fetch_out(status, A.status, (size_t)B, mem, st)) return rc;
-        if (mem == CILQR_MEM_HOST) CILQR_CUDA(cudaStreamSynchronize(st));
-        return 0;
     }
     const size_t smem = (size_t)kWarpsPerBlock * warp_smem_doubles(N, h->dp.S) * sizeof(double);
     int per_sm = 0;

@@ -314,6 +314,20 @@ class iLQR:
         self.X_result, self.U_result, self.J_result, self.iterations, self.status = X, Uarr, J, it, stt
         return Uarr
 
+    def solve_stats(self):
+        """(cost passes, derivative + backward/forward passes, rounds with work) of the last n_alphas == 1 solve, summed
+        over the batch; synchronises the current stream."""
+        cp, dp, r = C.c_int64(0), C.c_int64(0), C.c_int32(0)
+        st = C.c_void_p(0)
+        try:
+            import torch
+            if torch.cuda.is_available():
+                st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+        except ImportError:
+            pass
+        _check(self.lib.cilqr_solve_stats(self._h, C.byref(cp), C.byref(dp), C.byref(r), st))
+        return int(cp.value), int(dp.value), int(r.value)
+
     # ------------------------------------------------------------------ run_step (iLQR.cpp:247-255)
     def set_global_plan(self, global_plan):
         """global_plan: [n, 2] waypoints (== the reference's column-major 2 x n matrix)."""
