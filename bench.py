@@ -443,6 +443,9 @@ def run_b200_arm(args):
 
 def main():
     args = parse_args()
+    # NCCL prints its version banner on stdout at NCCL_DEBUG=VERSION; stdout is reserved for the one JSON line
+    if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
+        os.environ["NCCL_DEBUG"] = "WARN"
     if args.impl == "reference":
         run_reference_arm(args)
     else:
