@@ -443,9 +443,12 @@ def run_b200_arm(args):
 
 def main():
     args = parse_args()
-    # NCCL prints its version banner on stdout at NCCL_DEBUG=VERSION; stdout is reserved for the one JSON line
-    if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
-        os.environ["NCCL_DEBUG"] = "WARN"
+    # stdout is reserved for the one JSON line: whatever native libraries write to file descriptor 1 (NCCL's version banner,
+    # for one) goes to stderr instead; Python's own sys.stdout keeps the real stdout
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(real_stdout, "w")
     if args.impl == "reference":
         run_reference_arm(args)
     else:

@@ -191,6 +191,19 @@ int cilqr_forward(cilqr_handle h, int B, const double *X, const double *U, const
                   const double *K, const double *alpha /*[B] or NULL*/, double *X_new, double *U_new,
                   int mem, void *stream);
 
+/*
+ * LocalPlanner (LocalPlanner.cpp:24-116) as iLQR::run_step uses it (iLQR.cpp:247-255), for B ego states on one shared
+ * global plan: closest_point_index (:24-41), get_local_wpts (:47-60: the next num_of_local_wpts waypoints),
+ * polyfit (:101-116: X.colPivHouseholderQr().solve(y), X(i,j) = pow(x_i, j)).
+ *   ego   [B][4]                 ego states (x, y, v, theta); only x, y are read
+ *   plan  [n_pts][2]             global plan waypoints (the reference's 2 x n matrix, column-major)
+ *   poly  [B][poly_order+1]  out get_local_plan_coeffs()
+ *   xlp   [B][2]             out first and last x of get_local_plan() (all of x_local_plan that Constraints.cpp:31-33 reads)
+ * The outputs are cilqr_solve_batch's `poly` and `xlp` arguments.
+ */
+int cilqr_local_plan_batch(const cilqr_params *p, int B, const double *ego, const double *plan, int n_pts,
+                           double *poly, double *xlp, int mem, void *stream);
+
 /* ---- costmap (map_engine) ---- */
 
 /* grid_map::GridMap geometry after setGeometry() (grid_map_core/src/GridMap.cpp:45-62):

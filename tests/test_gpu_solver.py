@@ -287,3 +287,35 @@ def test_full_size_properties_config4_shard(checker):
         assert int(ih[b]) == r["iters"], b
         assert rel(Uh[b], r["U"]) < TOL and abs(Jh[b] - r["J"]) <= TOL * abs(r["J"]), b
     s.close()
+
+
+# ------------------------------------------------------------------------------------------------ row N1: LocalPlanner on the device
+@pytest.mark.parametrize("curved", [False, True])
+def test_local_planner_on_device_matches_reference(checker, curved):
+    """cilqr_local_plan_batch against the compiled reference LocalPlanner (LocalPlanner.cpp:24-116): the first / last abscissa
+    of the local plan exactly, the fitted polynomial to 1e-9 on the plan's span (the coefficients themselves are conditioned by a
+    degree-5 Vandermonde matrix; the reference's own two builds differ there by more than they differ in the fitted values)."""
+    if not hasattr(checker, "local_plan"):
+        pytest.skip("needs the compiled reference (oracle/_ref)")
+    import torch
+    p = checker.params_default(horizon=50)
+    t = np.arange(200, dtype=np.float64) * 0.9
+    plan = np.stack([t, 0.002 * t ** 2 if curved else np.zeros_like(t)], axis=1)
+    rng = np.random.default_rng(7 + int(curved))
+    B = 96
+    s = rng.uniform(0.0, 175.0, B)
+    ego = np.stack([s + rng.uniform(-0.4, 0.4, B), (0.002 * s ** 2 if curved else 0.0) + rng.uniform(-2.0, 2.0, B),
+                    rng.uniform(2, 6, B), rng.uniform(-0.1, 0.1, B)], axis=1)
+    ego[-1, 0] = 178.0  # fewer than num_of_local_wpts waypoints left (LocalPlanner.cpp:51-54)
+    lp = cilqr_b200.LocalPlanner(p)
+    lp.set_global_planner(plan)
+    poly_h, xlp_h = lp.plan_batch_device(ego)  # host buffers
+    poly_d, xlp_d = lp.plan_batch_device(torch.from_numpy(ego).cuda())  # device buffers
+    assert np.array_equal(poly_d.cpu().numpy(), poly_h) and np.array_equal(xlp_d.cpu().numpy(), xlp_h)
+    for b in range(B):
+        pr, xr, _ = checker.local_plan(p, plan, ego[b])
+        assert np.array_equal(xlp_h[b], xr), b
+        xs = np.linspace(xr[0], xr[1], 40)
+        y_mine = sum(poly_h[b, j] * xs ** j for j in range(6))
+        y_ref = sum(pr[j] * xs ** j for j in range(6))
+        assert np.max(np.abs(y_mine - y_ref)) <= 1e-9 * max(1.0, np.max(np.abs(y_ref))), b

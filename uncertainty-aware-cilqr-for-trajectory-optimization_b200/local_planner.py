@@ -81,6 +81,27 @@ class LocalPlanner:
             y += c[j] * np.power(w[:, 0], j)
         return np.stack([w[:, 0], y], axis=1)
 
+    def plan_batch_device(self, ego_states):
+        """The same on the GPU (cilqr_local_plan_batch): [B,4] ego states (numpy or torch CUDA) -> poly [B, poly_order+1],
+        xlp [B,2].  The reference trajectory (only used for display by the reference) is not produced."""
+        import ctypes as C
+        from . import solver as S
+        lib = S.load_library()
+        a = S._Arg()
+        B = int(ego_states.shape[0])
+        pe = a.inp(ego_states)
+        plan = self.global_plan_points
+        if a.mem == S.MEM_DEVICE:
+            import torch
+            plan = torch.as_tensor(plan, device=ego_states.device)
+        pp = a.inp(plan)
+        dev = a.mem == S.MEM_DEVICE
+        poly, ppoly = a.out((B, self.param.poly_order + 1), np.float64, dev, getattr(ego_states, "device", None))
+        xlp, pxlp = a.out((B, 2), np.float64, dev, getattr(ego_states, "device", None))
+        S._check(lib.cilqr_local_plan_batch(C.byref(self.param), C.c_int(B), pe, pp, C.c_int(int(self.global_plan_points.shape[0])),
+                                            ppoly, pxlp, C.c_int(a.mem), a.stream_ptr()))
+        return poly, xlp
+
     def plan_batch(self, ego_states):
         """[B,4] ego states -> poly [B, poly_order+1], xlp [B,2] (first, last x of the local plan), ref trajectories."""
         B = ego_states.shape[0]

@@ -343,9 +343,9 @@ class iLQR:
             raise CilqrError("set_global_plan() first")
         ego = np.ascontiguousarray(ego_state, dtype=np.float64).reshape(-1, 4)
         B = ego.shape[0]
-        poly, xlp, ref = self.localplanner.plan_batch(ego)
+        poly, xlp = self.localplanner.plan_batch_device(ego)  # LocalPlanner on the GPU (cilqr_local_plan_batch)
         U = np.ascontiguousarray(self.control_seq[:B])
         self.get_optimal_control_seq(ego, U, poly, xlp)
         self.control_seq[:B] = U
-        self.ref_traj_result = ref
+        self.poly_result, self.xlp_result = poly, xlp
         return self.X_result, self.U_result
