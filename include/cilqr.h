@@ -248,6 +248,33 @@ int costmap_propagate_uncertainty(const float *map, const costmap_geom *geom, do
                                   double sigma_theta, int index, int32_t *count, double *value,
                                   int mem, void *stream);
 
+/*
+ * The nav_msgs/OccupancyGrid wire format either side of the warp (row N2):
+ * GridMapRosConverter::fromOccupancyGrid (CILQR/src/grid_map/grid_map_ros/src/GridMapRosConverter.cpp:225-269; call site
+ * local_costmap.cpp:169) and ::toOccupancyGrid (:271-307; call site local_costmap.cpp:298).
+ *   from: data[i] = occ[n-1-i] != -1 ? occ[n-1-i] : NaN                       (reverse order, -1 = unknown)
+ *   to:   occ[n-1-i] = isnan(v) ? -1 : (int8)(min(max(0, v), 1) * 100),  v = (data[i] - data_min) / (data_max - data_min)
+ * `data` is a grid_map layer in linear (column-major) order, n = rows * cols.
+ */
+int costmap_from_occupancy(const int8_t *occ, int64_t n, float *data, int mem, void *stream);
+int costmap_to_occupancy(const float *data, int64_t n, float data_min, float data_max, int8_t *occ,
+                         int mem, void *stream);
+
+/*
+ * LocalCostmap::bondingBoxHandle (CILQR/src/map_engine/src/local_costmap.cpp:860-922), the producer of the warp's
+ * "bounding_box_map" overlay (row N3), for P frames at once: every vehicle within 100 m of the ego becomes a rotated
+ * rectangle (size + 0.2 m) in the ego frame; cells whose centre Polygon::isInside (grid_map_core/src/Polygon.cpp:32-44)
+ * accepts are set to 100, all other cells of `layer` are left as they are.
+ *   own_poses [P][3]           HOST  (own_pos_x, own_pos_y, own_yaw) per frame
+ *   boxes     [P][n_boxes][5]  HOST  the VehicleInfo fields (pose.position.x, pose.position.y, pose.orientation.z,
+ *                                    size.x, size.y); the sign flips of :868 and :884 are applied here as there
+ *   layer     [P][rows*cols]   float, host or device according to `mem`, read-modify-write
+ * The poses and boxes are always host arrays: the rectangle corners are computed on the host with libm exactly as the
+ * reference does (a cell centre on an edge is decided by the last bit of a corner coordinate).
+ */
+int costmap_rasterize_boxes(const costmap_geom *geom, int P, const double *own_poses, int n_boxes,
+                            const double *boxes, float *layer, int mem, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -161,6 +161,27 @@ class _Base:
         return out, idx
 
 
+    # ---- rows N2 / N3 (compiled reference only)
+    def rasterize_boxes(self, g, own_pose, boxes, layer):
+        boxes = _c64(boxes).reshape(-1, 5)
+        layer = np.ascontiguousarray(layer, dtype=np.float32).copy()
+        self._fn("rasterize_boxes", C.c_int)(C.byref(g), C.c_double(own_pose[0]), C.c_double(own_pose[1]), C.c_double(own_pose[2]),
+                                             C.c_int(boxes.shape[0]), _d(boxes), _f(layer))
+        return layer
+
+    def from_occupancy(self, occ):
+        occ = np.ascontiguousarray(occ, dtype=np.int8)
+        out = np.zeros(occ.size, dtype=np.float32)
+        self._fn("from_occupancy", None)(occ.ctypes.data_as(C.c_void_p), C.c_longlong(occ.size), _f(out))
+        return out
+
+    def to_occupancy(self, data, data_min, data_max):
+        data = np.ascontiguousarray(data, dtype=np.float32)
+        out = np.zeros(data.size, dtype=np.int8)
+        self._fn("to_occupancy", None)(_f(data), C.c_longlong(data.size), C.c_float(data_min), C.c_float(data_max), out.ctypes.data_as(C.c_void_p))
+        return out
+
+
 def _ellipse_cells(self, g, cx, cy, lx, ly, rot, max_cells=4096):
     cells = np.zeros((max_cells, 2), dtype=np.int32)
     n = self._fn("ellipse_cells", C.c_int)(C.byref(g), C.c_double(cx), C.c_double(cy), C.c_double(lx), C.c_double(ly), C.c_double(rot),

@@ -49,6 +49,8 @@
 
 #include "grid_map_core/grid_map_core.hpp"
 #include "grid_map_core/iterators/EllipseIterator.hpp"
+#include "grid_map_core/iterators/PolygonIterator.hpp"
+#include "grid_map_core/Polygon.hpp"
 #include "grid_map_core/iterators/GridMapIterator.hpp"
 #include <Eigen/Eigenvalues>
 
@@ -481,6 +483,79 @@ extern "C"
         *x = p.x();
         *y = p.y();
         return ok ? 1 : 0;
+    }
+
+    // Row N3: LocalCostmap::bondingBoxHandle (local_costmap.cpp:860-922) on a real GridMap with the reference's
+    // grid_map::Polygon / PolygonIterator: every vehicle within 100 m of the ego becomes a rotated rectangle (size + 0.2 m) in
+    // the ego frame whose cells are set to 100 in the "bounding_box_map" layer.  boxes [n][5] = the message fields
+    // (pose.position.x, pose.position.y, pose.orientation.z, size.x, size.y); `layer` is read-modify-written.
+    int ref_rasterize_boxes(const costmap_geom *g, double own_pos_x, double own_pos_y, double own_yaw, int n_boxes, const double *boxes,
+                            float *layer)
+    {
+        grid_map::GridMap vehicle_map_({"bounding_box_map"});
+        vehicle_map_.setGeometry(grid_map::Length(g->length_x, g->length_y), g->resolution, grid_map::Position(g->pos_x, g->pos_y));
+        const int rows = vehicle_map_.getSize()(0), cols = vehicle_map_.getSize()(1);
+        vehicle_map_["bounding_box_map"] = Eigen::Map<const Eigen::MatrixXf>(layer, rows, cols);
+        for (int v = 0; v < n_boxes; ++v)
+        {
+            const double *bx = boxes + 5 * v;
+            double posX = bx[0];
+            double posY = -bx[1];
+            double distance = std::sqrt(std::pow(posX - own_pos_x, 2) + std::pow(posY - own_pos_y, 2));
+            if (distance <= 100.0)
+            {
+                grid_map::Polygon polygon;
+                polygon.setFrameId(vehicle_map_.getFrameId());
+                double sizeX = bx[3] + 0.2;
+                double sizeY = bx[4] + 0.2;
+                double yaw = -bx[2];
+                double half_sizeX = sizeX / 2.0;
+                double half_sizeY = sizeY / 2.0;
+                std::vector<grid_map::Position> corners = {
+                    {half_sizeX, half_sizeY}, {half_sizeX, -half_sizeY}, {-half_sizeX, -half_sizeY}, {-half_sizeX, half_sizeY}};
+                for (auto &corner : corners)
+                {
+                    double global_x = cos(yaw) * corner.x() - sin(yaw) * corner.y() + posX;
+                    double global_y = sin(yaw) * corner.x() + cos(yaw) * corner.y() + posY;
+                    double local_x = cos(own_yaw) * (global_x - own_pos_x) + sin(own_yaw) * (global_y - own_pos_y);
+                    double local_y = -sin(own_yaw) * (global_x - own_pos_x) + cos(own_yaw) * (global_y - own_pos_y);
+                    polygon.addVertex(grid_map::Position(local_x, local_y));
+                }
+                polygon.addVertex(polygon.getVertex(0));
+                for (grid_map::PolygonIterator iterator(vehicle_map_, polygon); !iterator.isPastEnd(); ++iterator)
+                    vehicle_map_.at("bounding_box_map", *iterator) = 100;
+            }
+        }
+        Eigen::Map<Eigen::MatrixXf>(layer, rows, cols) = vehicle_map_["bounding_box_map"];
+        return 0;
+    }
+
+    // Row N2: the occupancy-grid wire format either side of the warp.  grid_map_ros cannot be compiled here (ROS message
+    // headers), so these two loops restate GridMapRosConverter::fromOccupancyGrid (grid_map_ros/src/GridMapRosConverter.cpp:
+    // 259-266) and ::toOccupancyGrid (:291-306) on plain buffers; `n` = width * height cells, grid_map data in linear
+    // (column-major) order with startIndex 0.
+    void ref_from_occupancy(const int8_t *occ, long long n, float *data)
+    {
+        for (long long i = 0; i < n; ++i)
+        {
+            const int8_t v = occ[n - 1 - i]; // reverse iteration (:262-266)
+            data[i] = v != -1 ? (float)v : NAN;
+        }
+    }
+    void ref_to_occupancy(const float *data, long long n, float dataMin, float dataMax, int8_t *occ)
+    {
+        const float cellMin = 0;
+        const float cellMax = 100;
+        const float cellRange = cellMax - cellMin;
+        for (long long index = 0; index < n; ++index)
+        {
+            float value = (data[index] - dataMin) / (dataMax - dataMin);
+            if (std::isnan(value))
+                value = -1;
+            else
+                value = cellMin + std::min(std::max(0.0f, value), 1.0f) * cellRange;
+            occ[n - index - 1] = value; // reverse cell order (:303-305); float -> int8 conversion as in the reference's assignment
+        }
     }
 
     // The warp loop of LocalCostmap::odomCallback (local_costmap.cpp:242-264) on real GridMap objects,

@@ -69,3 +69,31 @@ def test_expand_obstacles_matches_numpy_generator(port):
     sc = scenarios.make_scenarios(p, 5, 3, 4)
     dim, pos = port.expand_obstacles_cv(p, sc["obs_state0"][1], sc["obs_LW"][1], sc["obs_sigma"][1], sc["kappa"])
     assert rel(dim, sc["dim"][1]) < 1e-15 and rel(pos, sc["pos"][1]) < 1e-15
+
+
+# ------------------------------------------------------------------------------------------------ rows N2 / N3: known answers
+def test_occupancy_wire_format_known_answers(ref):
+    """GridMapRosConverter.cpp:259-266 / :291-306 restated in oracle/ref_harness.cpp: reverse order, -1 <-> NaN, truncation."""
+    occ = np.array([0, 50, -1, 100, 59], dtype=np.int8)
+    data = ref.from_occupancy(occ)
+    assert np.array_equal(np.isnan(data), [False, False, True, False, False])
+    assert np.array_equal(data[[0, 1, 3, 4]], [59.0, 100.0, 50.0, 0.0])
+    back = ref.to_occupancy(data, 0.0, 100.0)
+    assert back.tolist() == [0, 50, -1, 100, 58]  # (59 / 100) * 100 = 58.99999 in float: the reference truncates
+    assert ref.to_occupancy(np.array([-7.0, 250.0, 12.5], np.float32), 0.0, 50.0).tolist() == [25, 100, 0]
+
+
+def test_bounding_box_rasterisation_known_answer(ref):
+    """bondingBoxHandle (local_costmap.cpp:860-922) on the reference's Polygon / PolygonIterator: an axis-aligned 4.0 x 2.0 m
+    vehicle (+0.2 m) right ahead of the ego covers 21 x 11 cell centres of a 0.2 m grid; a vehicle 150 m away is skipped."""
+    import cilqr_b200
+    g = cilqr_b200.CostmapGeom(40.0, 40.0, 0.2, 0.0, 0.0)
+    rows, cols = ref.geom_size(g)
+    boxes = np.array([[10.1, -0.1, 0.0, 4.0, 2.0], [150.0, 0.0, 0.3, 4.0, 2.0]])
+    layer = ref.rasterize_boxes(g, (0.0, 0.0, 0.0), boxes, np.zeros(rows * cols, np.float32))
+    filled = np.flatnonzero(layer == 100.0)
+    assert filled.size == 21 * 11 and set(np.unique(layer)) == {0.0, 100.0}
+    i, j = filled % rows, filled // rows  # column-major linear index
+    x = 0.0 + (0.5 * 40.0 - 0.5 * 0.2) - 0.2 * i
+    y = 0.0 + (0.5 * 40.0 - 0.5 * 0.2) - 0.2 * j
+    assert x.min() > 10.1 - 2.1 - 1e-9 and x.max() < 10.1 + 2.1 + 1e-9 and y.min() > 0.1 - 1.1 - 1e-9 and y.max() < 0.1 + 1.1 + 1e-9

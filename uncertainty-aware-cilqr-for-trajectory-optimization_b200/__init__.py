@@ -4,5 +4,5 @@ library; the first compute call dlopens libcilqr_b200.so and raises if it is mis
 from . import params, scenarios, solver, costmap, local_planner, dist  # noqa: F401
 from .params import Parameters, CostmapGeom, MEM_HOST, MEM_DEVICE, MERIT_TRACKING, MERIT_TOTAL  # noqa: F401
 from .solver import iLQR, Obstacle, load_library, LibraryMissing, CilqrError, launch_count  # noqa: F401
-from .costmap import warp_batch, propagate_uncertainty, geom_size  # noqa: F401
+from .costmap import warp_batch, propagate_uncertainty, geom_size, from_occupancy, to_occupancy, rasterize_boxes  # noqa: F401
 from .local_planner import LocalPlanner  # noqa: F401

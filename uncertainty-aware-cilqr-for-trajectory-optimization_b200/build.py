@@ -15,7 +15,7 @@ from concurrent.futures import ThreadPoolExecutor
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libcilqr_b200.so")
-SOURCES = ["cilqr_solver.cu", "costmap.cu", "propagate.cu", "local_planner.cu"]
+SOURCES = ["cilqr_solver.cu", "costmap.cu", "propagate.cu", "local_planner.cu", "costmap_io.cu"]
 # propagate.cu restates float/double expression chains of the reference operation by operation: no FMA contraction there
 EXTRA_FLAGS = {"propagate.cu": ["-fmad=false"]}
 HEADERS = ["common.cuh", "cilqr_device.cuh", "cilqr_batch.cuh", os.path.join("..", "..", "include", "cilqr.h")]

@@ -64,3 +64,61 @@ def propagate_uncertainty(vmap, geom, sin_theta, cos_theta, sigma_x, sigma_y, si
                                              C.c_double(sigma_y), C.c_double(sigma_theta), C.c_int(index), pc, pv, C.c_int(a.mem),
                                              a.stream_ptr()))
     return count, value
+
+
+def from_occupancy(occ):
+    """GridMapRosConverter::fromOccupancyGrid (GridMapRosConverter.cpp:225-269): int8 occupancy data -> float layer."""
+    lib = load_library()
+    a = _Arg()
+    if hasattr(occ, "is_cuda"):
+        import torch
+        if not (occ.is_cuda and occ.dtype == torch.int8 and occ.is_contiguous()):
+            raise ValueError("occ must be a contiguous int8 CUDA tensor")
+        a._set_mem(MEM_DEVICE)
+        a.keep.append(occ)
+        po, n = C.c_void_p(occ.data_ptr()), occ.numel()
+    else:
+        occ = np.ascontiguousarray(occ, dtype=np.int8)
+        a._set_mem(MEM_HOST)
+        a.keep.append(occ)
+        po, n = C.c_void_p(occ.ctypes.data), occ.size
+    out, pout = a.out((n,), np.float32, a.mem == MEM_DEVICE, getattr(occ, "device", None))
+    _check(lib.costmap_from_occupancy(po, C.c_int64(n), pout, C.c_int(a.mem), a.stream_ptr()))
+    return out
+
+
+def to_occupancy(data, data_min=0.0, data_max=100.0):
+    """GridMapRosConverter::toOccupancyGrid (GridMapRosConverter.cpp:271-307): float layer -> int8 occupancy data."""
+    lib = load_library()
+    a = _Arg()
+    pd = a.inp(data, np.float32)
+    n = int(data.numel()) if hasattr(data, "numel") else int(np.asarray(data).size)
+    if a.mem == MEM_DEVICE:
+        import torch
+        out = torch.empty(n, dtype=torch.int8, device=data.device)
+        pout = C.c_void_p(out.data_ptr())
+    else:
+        out = np.empty(n, dtype=np.int8)
+        pout = C.c_void_p(out.ctypes.data)
+    _check(lib.costmap_to_occupancy(pd, C.c_int64(n), C.c_float(data_min), C.c_float(data_max), pout, C.c_int(a.mem), a.stream_ptr()))
+    return out
+
+
+def rasterize_boxes(geom, own_poses, boxes, layer):
+    """LocalCostmap::bondingBoxHandle (local_costmap.cpp:860-922) for P frames: own_poses [P,3] (x, y, yaw), boxes
+    [P,n,5] (pose x, pose y, orientation z, size x, size y) — both host arrays; layer [P, rows*cols] float32 (numpy or torch
+    CUDA) is updated in place and returned."""
+    lib = load_library()
+    a = _Arg()
+    own = np.ascontiguousarray(own_poses, dtype=np.float64).reshape(-1, 3)
+    bx = np.ascontiguousarray(boxes, dtype=np.float64).reshape(own.shape[0], -1, 5)
+    if hasattr(layer, "is_cuda"):
+        pl = a.inp(layer, np.float32)
+    else:
+        if not (isinstance(layer, np.ndarray) and layer.dtype == np.float32 and layer.flags.c_contiguous):
+            raise ValueError("layer must be a C-contiguous float32 array (it is updated in place)")
+        a._set_mem(MEM_HOST)
+        pl = C.c_void_p(layer.ctypes.data)
+    _check(lib.costmap_rasterize_boxes(C.byref(geom), C.c_int(own.shape[0]), own.ctypes.data_as(C.c_void_p), C.c_int(bx.shape[1]),
+                                       bx.ctypes.data_as(C.c_void_p), pl, C.c_int(a.mem), a.stream_ptr()))
+    return layer
