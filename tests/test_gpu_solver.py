@@ -319,3 +319,38 @@ def test_local_planner_on_device_matches_reference(checker, curved):
         y_mine = sum(poly_h[b, j] * xs ** j for j in range(6))
         y_ref = sum(pr[j] * xs ** j for j in range(6))
         assert np.max(np.abs(y_mine - y_ref)) <= 1e-9 * max(1.0, np.max(np.abs(y_ref))), b
+
+
+# ------------------------------------------------------------------------------------------------ row N4: receding-horizon loop
+def test_receding_horizon_loop_matches_chained_reference_calls(checker, tmp_path):
+    """Four closed-loop ticks (no pose noise) of three vehicles against the same loop assembled from reference calls:
+    LocalPlanner -> get_optimal_control_seq warm-started from the previous tick, un-shifted -> Model::forward_simulate with
+    U_result(:, 0) (ilqr_uncertainty_node.cpp:111-128, iLQR.cpp:247-255)."""
+    if not hasattr(checker, "local_plan"):
+        pytest.skip("needs the compiled reference (oracle/_ref)")
+    from cilqr_b200 import receding_horizon as rh
+    p = checker.params_default(horizon=50)
+    B, n_obs, ticks = 3, 3, 4
+    sc = scenarios.make_scenarios(p, 500, B, n_obs)
+    plan = np.stack([np.arange(200, dtype=np.float64), np.zeros(200)], axis=1)
+    s = cilqr_b200.iLQR(p, max_batch=B, max_obs=n_obs)
+    s.set_obstacles_dense(sc["dim"], sc["pos"])
+    path = str(tmp_path / "loop.bin")
+    loop = rh.RecedingHorizon(s, plan, sc["x0"], log_path=path)
+    for _ in range(ticks):
+        loop.tick()
+    loop.close()
+    N, Bl, rec = rh.read_log(path)
+    assert (N, Bl, rec.size) == (50, B, ticks * B)
+    for b in range(B):
+        x = sc["x0"][b].copy()
+        U = sc["U0"][b].copy()  # the constructor's control sequence (iLQR.cpp:9-15)
+        for k in range(ticks):
+            poly, xlp, _ = checker.local_plan(p, plan, x)
+            r = checker.solve(p, sc["dim"][b], sc["pos"][b], x, U, poly, xlp)
+            got = rec[k * B + b]
+            assert rel(got["start_pos"], x) < 1e-9 or np.max(np.abs(got["start_pos"] - x)) < 1e-9
+            assert rel(got["U"], r["U"]) < 1e-6 and rel(got["X"], r["X"]) < 1e-6, (b, k)  # the fit feeds in at ~1e-12, k solves amplify it
+            U = r["U"]
+            x = checker.forward_simulate(p, x, r["U"][:2])
+    s.close()

@@ -94,3 +94,60 @@ def test_world_size_2_shard_and_gather_over_gloo(tmp_path, port):
                         "--master-port", "29611", str(script)], capture_output=True, text=True, env=env, timeout=600)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     assert "GLOO_OK" in r.stdout
+
+
+# ------------------------------------------------------------------------------------------------ row N4: receding-horizon wrapper (host side)
+class _FakeSolver:
+    """Stands in for cilqr_b200.iLQR: the wrapper's bookkeeping (noise, warm-start shift, log) needs no GPU."""
+
+    def __init__(self, p, B):
+        self.params, self.B = p, B
+        N = p.horizon
+        self.control_seq = np.tile(np.arange(2 * N, dtype=np.float64), (B, 1))
+        self.seen = []
+
+    def set_global_plan(self, plan):
+        self.plan = plan
+
+    def run_step(self, ego):
+        N = self.params.horizon
+        self.seen.append((ego.copy(), self.control_seq.copy()))
+        X = np.tile(ego, (1, N + 1)) + np.arange(4 * (N + 1))
+        return X, self.control_seq[:ego.shape[0]] + 1.0
+
+    def get_nominal_trajectory(self, x0, U):
+        N = self.params.horizon
+        X = np.tile(x0, (1, N + 1))
+        X[:, 4:8] = x0 + 0.1 * U[:, [0, 1, 0, 1]]
+        return X
+
+
+def test_receding_horizon_noise_log_and_shift(port, tmp_path):
+    from cilqr_b200 import receding_horizon as rh
+    p = port.params_default(horizon=50)
+    B = 3
+    x0 = np.array([[0.0, 0.1, 4.0, 0.0], [5.0, -0.2, 3.0, 0.01], [9.0, 0.0, 5.0, -0.02]])
+    path = str(tmp_path / "run.bin")
+    s = _FakeSolver(p, B)
+    loop = rh.RecedingHorizon(s, np.zeros((10, 2)), x0, sigma=(0.16, 0.16, 0.017), seed=11, shift=True, log_path=path)
+    for _ in range(3):
+        loop.tick()
+    loop.close()
+    # noise: x, y, theta perturbed, v untouched (ilqr_uncertainty_node.cpp:111); reproducible; roughly the right scale
+    ego0 = s.seen[0][0]
+    assert np.array_equal(ego0[:, 2], x0[:, 2]) and not np.array_equal(ego0[:, [0, 1, 3]], x0[:, [0, 1, 3]])
+    assert np.allclose(rh.pose_noise(11, 0, B, (0.16, 0.16, 0.017)), ego0[:, [0, 1, 3]] - x0[:, [0, 1, 3]], rtol=0, atol=1e-12)
+    big = rh.pose_noise(3, 7, 20000, (0.16, 0.16, 0.017))
+    assert np.allclose(big.std(axis=0), (0.16, 0.16, 0.017), rtol=0.05) and np.all(np.abs(big.mean(axis=0)) < 0.01)
+    # shift extension: tick k >= 1 starts from the previous controls advanced by one step, last control repeated
+    N = p.horizon
+    before = np.tile(np.arange(2 * N, dtype=np.float64), (B, 1)).reshape(B, N, 2)
+    assert np.array_equal(s.seen[0][1].reshape(B, N, 2), before)
+    assert np.array_equal(s.seen[1][1].reshape(B, N, 2)[:, :-1], before[:, 1:]) and np.array_equal(s.seen[1][1].reshape(B, N, 2)[:, -1], before[:, -1])
+    # log: one Experiment record per (tick, scenario), start_pos = the noise-free state, X / U as returned
+    Nr, Br, rec = rh.read_log(path)
+    assert (Nr, Br, rec.size) == (N, B, 3 * B)
+    assert np.array_equal(rec["tick"], np.repeat(np.arange(3), B)) and np.array_equal(rec["scenario"], np.tile(np.arange(B), 3))
+    assert np.array_equal(rec["start_pos"][:B], x0) and np.all(rec["planning_time"] >= 0.0)
+    assert np.array_equal(rec["X"][:B], np.tile(ego0, (1, N + 1)) + np.arange(4 * (N + 1)))
+    assert np.array_equal(rec["start_pos"][B:2 * B], x0 + 0.1 * loop.commands[0][:, [0, 1, 0, 1]])
