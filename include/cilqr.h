@@ -166,6 +166,13 @@ int cilqr_solve_batch(cilqr_handle h, int B, const double *x0, double *U, const 
 int cilqr_solve_stats(cilqr_handle h, int64_t *cost_passes, int64_t *deriv_passes, int32_t *rounds,
                       void *stream);
 
+/* Diagnostics: timeline of the last batch-synchronous solve on a handle created with CILQR_TRACE=1 in the environment.
+ * out[chunk][round][kind][2] (kind 0 cost, 1 derivatives, 2 sweep, 3 init (round 0) / output (round 1)): %globaltimer
+ * nanoseconds of the first CTA's start and the last CTA's end of that launch, 0 when it did not run.  *rounds receives the
+ * round dimension (max_iterations + 3).  No reference counterpart (the reference times run_step with std::chrono,
+ * ilqr_uncertainty_node.cpp:117-121). */
+int cilqr_solve_trace(cilqr_handle h, uint64_t *out, int capacity, int32_t *chunks, int32_t *rounds, void *stream);
+
 /* ---- stage entry points (used by the parity tests; same device code as the fused solve) ---- */
 
 /* iLQR::get_nominal_trajectory (iLQR.cpp:51-62) over Model::forward_simulate (Model.cpp:17-30). */

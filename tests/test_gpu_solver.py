@@ -208,6 +208,63 @@ def test_device_resident_and_host_buffers_give_identical_bits():
     s.close()
 
 
+@pytest.mark.parametrize("chunks", [2, 3, 8])
+def test_chunked_streams_give_the_bits_of_one_stream(monkeypatch, chunks):
+    """cilqr_solve_batch cuts the batch into chunks on internal streams (host->device copy, rounds, device->host copy per
+    chunk); ragged last chunk, host and device buffers, constant-velocity obstacles: same bits as the single-stream solve."""
+    import torch
+    p = cilqr_b200.Parameters()
+    cilqr_b200.load_library().cilqr_params_default(__import__("ctypes").byref(p))
+    p = p.replace(horizon=50)
+    B, n_obs = 203, 4  # chunks of 128/75, 96/96/11, 32 x 6 + 11
+    sc = scenarios.make_scenarios(p, 11, B, n_obs, curved=True, dense=False)
+    out = {}
+    for k in (1, chunks):
+        monkeypatch.setenv("CILQR_CHUNKS", str(k))  # read at cilqr_create
+        s = cilqr_b200.iLQR(p, max_batch=B, max_obs=n_obs)
+        s.set_obstacles_cv(sc["obs_state0"], sc["obs_LW"], sc["obs_sigma"], sc["kappa"])
+        U = sc["U0"].copy()
+        s.get_optimal_control_seq(sc["x0"], U, sc["poly"], sc["xlp"])
+        host = (U, s.X_result.copy(), s.J_result.copy(), s.iterations.copy(), s.status.copy())
+        stats = s.solve_stats()
+        dev = torch.device("cuda:0")
+        t = {n: torch.from_numpy(sc[n]).to(dev) for n in ("x0", "U0", "poly", "xlp", "obs_state0", "obs_LW", "obs_sigma")}
+        s.set_obstacles_cv(t["obs_state0"], t["obs_LW"], t["obs_sigma"], sc["kappa"])
+        Ud = t["U0"].clone()
+        N = p.horizon
+        od = {"X": torch.empty(B, 4 * (N + 1), dtype=torch.float64, device=dev), "J": torch.empty(B, dtype=torch.float64, device=dev),
+              "iters": torch.empty(B, dtype=torch.int32, device=dev), "status": torch.empty(B, dtype=torch.int32, device=dev)}
+        for rep in range(4):  # the second call with the same buffers records a CUDA graph, the later ones replay it
+            Ud.copy_(t["U0"])
+            for o in od.values():
+                o.zero_()
+            s.get_optimal_control_seq(t["x0"], Ud, t["poly"], t["xlp"], outputs=od)
+            torch.cuda.synchronize()
+            devr = (Ud.cpu().numpy(), od["X"].cpu().numpy(), od["J"].cpu().numpy(), od["iters"].cpu().numpy(), od["status"].cpu().numpy())
+            for a, b in zip(host, devr):
+                assert np.array_equal(a, b), rep
+        assert s.solve_stats() == stats
+        # pinned host buffers: recorded too, host<->device copies included
+        pin = {n: torch.from_numpy(sc[n]).pin_memory() for n in ("x0", "U0", "poly", "xlp")}
+        s.set_obstacles_cv(sc["obs_state0"], sc["obs_LW"], sc["obs_sigma"], sc["kappa"])
+        Up = pin["U0"].clone().pin_memory().numpy()
+        op = {n: torch.empty(o.shape, dtype=o.dtype).pin_memory().numpy() for n, o in od.items()}
+        for rep in range(4):
+            Up[...] = sc["U0"]
+            for o in op.values():
+                o[...] = 0
+            s.get_optimal_control_seq(pin["x0"].numpy(), Up, pin["poly"].numpy(), pin["xlp"].numpy(), outputs=op)
+            for a, b in zip(host, (Up, op["X"], op["J"], op["iters"], op["status"])):
+                assert np.array_equal(a, b), rep
+        for a, b in zip(host, devr):
+            assert np.array_equal(a, b)
+        out[k] = host + (stats,)
+        s.close()
+    for a, b in zip(out[1][:5], out[chunks][:5]):
+        assert np.array_equal(a, b)
+    assert out[1][5][:2] == out[chunks][5][:2]  # cost / derivative passes summed over the chunks
+
+
 def test_edge_cases_and_error_codes(checker):
     p = checker.params_default(horizon=50)
     sc = scenarios.make_scenarios(p, 0, 4, 2)

@@ -3,6 +3,10 @@
 //   A  LDG.128 x9 into registers one step ahead (what batch_sweep_kernel does)
 //   B  cp.async (LDGSTS) 16 B x9 per lane into a shared-memory ring, 4 steps ahead
 //   C  cp.async.bulk 144 B per lane into a shared-memory ring (TMA unit), 4 steps ahead, mbarrier completion
+//   D  dense structure-of-arrays (coalesced by construction), LDG one step ahead
+//   G  warp-cooperative cp.async ring: the 32 records of a step are fetched as 288 16-byte pieces, lane l takes pieces
+//      l, l+32, ... (consecutive lanes -> consecutive bytes of one record), results staged in shared memory and written back
+//      the same way: ~6 cache lines per warp instruction instead of 32
 //   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o build/stream_micro tools/stream_micro.cu
 #include <cstdio>
 #include <cstdint>
@@ -141,6 +145,143 @@ __global__ void __launch_bounds__(32) variant_c(double *rec, const int *list, lo
     if (lane == 0) cyc[blockIdx.x] = t1 - t0;
 }
 
+
+template <int DEPTH>
+__global__ void __launch_bounds__(32) variant_g(double *rec, const int *list, long long *cyc, double *sink)
+{
+    __shared__ __align__(16) double ring[DEPTH][32][kStepD];
+    __shared__ __align__(16) double outb[32][10];
+    __shared__ double *bases[32];
+    const int lane = threadIdx.x;
+    const int b = list[blockIdx.x * 32 + lane];
+    double *base = rec + (size_t)b * (N + 1) * kStepD;
+    bases[lane] = base;
+    __syncwarp();
+    auto issue = [&](int j) {
+        if (j >= 0) {
+#pragma unroll
+            for (int i = 0; i < 9; ++i) {
+                const int p = i * 32 + lane, src = p / 9, f = p - src * 9;
+                const double *g = bases[src] + (size_t)j * kStepD + 2 * f;
+                const uint32_t dst = (uint32_t)__cvta_generic_to_shared(&ring[j % DEPTH][src][2 * f]);
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(g));
+            }
+        }
+        asm volatile("cp.async.commit_group;");
+    };
+    for (int d = 0; d < DEPTH - 1; ++d) issue(N - 1 - d);
+    double a = lane;
+    long long t0 = clock64();
+    for (int j = N - 1; j >= 0; --j) {
+        issue(j - (DEPTH - 1));
+        asm volatile("cp.async.wait_group %0;" ::"n"(DEPTH - 1));
+        __syncwarp();
+        double cur[kStepD];
+#pragma unroll
+        for (int f = 0; f < kStepD; f += 2) {
+            double2 v = *reinterpret_cast<double2 *>(&ring[j % DEPTH][lane][f]);
+            cur[f] = v.x; cur[f + 1] = v.y;
+        }
+        a = chain(a, cur);
+#pragma unroll
+        for (int f = 0; f < 10; f += 2)
+            *reinterpret_cast<double2 *>(&outb[lane][f]) = make_double2(a, a + f);
+        __syncwarp();
+#pragma unroll
+        for (int i = 0; i < 5; ++i) {
+            const int p = i * 32 + lane, src = p / 5, f = p - src * 5;
+            const double2 v = *reinterpret_cast<double2 *>(&outb[src][2 * f]);
+            *reinterpret_cast<double2 *>(bases[src] + (size_t)j * kStepD + 8 + 2 * f) = v;
+        }
+        __syncwarp();
+    }
+    long long t1 = clock64();
+    if (a == 1234.5) sink[0] = a;
+    if (lane == 0) cyc[blockIdx.x] = t1 - t0;
+}
+
+// I/J/K: the structure batch_sweep_kernel uses — piece offsets precomputed per lane, results of step j staged in a double
+// buffer and written during step j - 1, one __syncwarp per step.  MODE 0: as the kernel; 1: own-record and staged reads first,
+// then cp.async, then global stores; 2: no write-back at all.
+template <int DEPTH, int MODE>
+__global__ void __launch_bounds__(32) variant_i(double *rec, const int *list, long long *cyc, double *sink)
+{
+    __shared__ __align__(16) double ring[DEPTH][32][kStepD];
+    __shared__ __align__(16) double outb[2][32][10];
+    const int lane = threadIdx.x;
+    const int b = list[blockIdx.x * 32 + lane];
+    const size_t stride16 = (size_t)(N + 1) * 9;
+    size_t ld_off[9], st_off[5];
+#pragma unroll
+    for (int k = 0; k < 9; ++k) {
+        const int p = k * 32 + lane, src = p / 9, f = p - src * 9;
+        ld_off[k] = (size_t)__shfl_sync(0xffffffffu, b, src) * stride16 + f;
+    }
+#pragma unroll
+    for (int k = 0; k < 5; ++k) {
+        const int p = k * 32 + lane, src = p / 5, f = p - src * 5;
+        st_off[k] = (size_t)__shfl_sync(0xffffffffu, b, src) * stride16 + 4 + f;
+    }
+    const double2 *rec16 = reinterpret_cast<const double2 *>(rec);
+    double2 *out16 = reinterpret_cast<double2 *>(rec);
+    const uint32_t ring0 = (uint32_t)__cvta_generic_to_shared(&ring[0][0][0]);
+    auto fetch = [&](int j, int slot) {
+#pragma unroll
+        for (int k = 0; k < 9; ++k)
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(ring0 + slot * 4608 + (k * 32 + lane) * 16), "l"(rec16 + ld_off[k] + (size_t)j * 9) : "memory");
+    };
+    for (int d = 0; d < DEPTH - 1; ++d) {
+        fetch(N - 1 - d, d);
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    }
+    double a = lane;
+    int slot = 0;
+    long long t0 = clock64();
+    for (int j = N - 1; j >= 0; --j) {
+        asm volatile("cp.async.wait_group %0;" ::"n"(DEPTH - 2) : "memory");
+        __syncwarp();
+        const int nslot = slot == 0 ? DEPTH - 1 : slot - 1;
+        double cur[kStepD];
+        double2 o[5];
+        if (MODE >= 1) {
+#pragma unroll
+            for (int f = 0; f < kStepD; f += 2) {
+                double2 v = *reinterpret_cast<double2 *>(&ring[slot][lane][f]);
+                cur[f] = v.x; cur[f + 1] = v.y;
+            }
+            if (MODE == 1 && j < N - 1) {
+#pragma unroll
+                for (int k = 0; k < 5; ++k) o[k] = reinterpret_cast<const double2 *>(&outb[(j + 1) & 1][0][0])[k * 32 + lane];
+            }
+        }
+        if (j - (DEPTH - 1) >= 0) fetch(j - (DEPTH - 1), nslot);
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        if (MODE == 0) {
+            if (j < N - 1) {
+#pragma unroll
+                for (int k = 0; k < 5; ++k)
+                    out16[st_off[k] + (size_t)(j + 1) * 9] = reinterpret_cast<const double2 *>(&outb[(j + 1) & 1][0][0])[k * 32 + lane];
+            }
+#pragma unroll
+            for (int f = 0; f < kStepD; f += 2) {
+                double2 v = *reinterpret_cast<double2 *>(&ring[slot][lane][f]);
+                cur[f] = v.x; cur[f + 1] = v.y;
+            }
+        } else if (MODE == 1 && j < N - 1) {
+#pragma unroll
+            for (int k = 0; k < 5; ++k) out16[st_off[k] + (size_t)(j + 1) * 9] = o[k];
+        }
+        a = chain(a, cur);
+#pragma unroll
+        for (int f = 0; f < 10; f += 2)
+            *reinterpret_cast<double2 *>(&outb[j & 1][lane][f]) = make_double2(a, a + f);
+        slot = slot == DEPTH - 1 ? 0 : slot + 1;
+    }
+    long long t1 = clock64();
+    if (a == 1234.5) sink[0] = a;
+    if (lane == 0) cyc[blockIdx.x] = t1 - t0;
+}
+
 // D: dense structure-of-arrays, [t][field][position]: every access of the warp is one 256-byte line.
 __global__ void __launch_bounds__(32) variant_d(double *rec, long long *cyc, double *sink, size_t pitch)
 {
@@ -173,15 +314,16 @@ int main()
     cudaMalloc(&rec, (size_t)S * (N + 1) * kStepD * 8);
     cudaMemset(rec, 0, (size_t)S * (N + 1) * kStepD * 8);
     cudaMalloc(&sink, 8);
-    const int maxb = 148 * 8;
+    const int maxb = 148 * 12;
     cudaMalloc(&list, maxb * 32 * 4);
     cudaMalloc(&cyc, maxb * 8);
     int *hl = new int[maxb * 32];
     for (int i = 0; i < maxb * 32; ++i) hl[i] = (i * active_stride + 3) % S;
     cudaMemcpy(list, hl, maxb * 32 * 4, cudaMemcpyHostToDevice);
     long long *hc = new long long[maxb];
-    for (int blocks : {148, 296, 1184}) {
-        for (int v = 0; v < 6; ++v) {
+    for (int blocks : {148, 296, 444, 1628}) {
+        for (int v = 0; v < 12; ++v) {
+            if (v == 2 || v == 4 || v == 7) continue;
             for (int rep = 0; rep < 2; ++rep) {
                 if (v == 0) variant_a<<<blocks, 32>>>(rec, list, cyc, sink);
                 if (v == 1) variant_b<4, true><<<blocks, 32>>>(rec, list, cyc, sink);
@@ -189,6 +331,12 @@ int main()
                 if (v == 4) variant_b<8, true><<<blocks, 32>>>(rec, list, cyc, sink);
                 if (v == 5) variant_b<4, false><<<blocks, 32>>>(rec, list, cyc, sink);
                 if (v == 2) variant_c<<<blocks, 32>>>(rec, list, cyc, sink);
+                if (v == 8) variant_i<3, 0><<<blocks, 32>>>(rec, list, cyc, sink);
+                if (v == 9) variant_i<3, 1><<<blocks, 32>>>(rec, list, cyc, sink);
+                if (v == 10) variant_i<3, 2><<<blocks, 32>>>(rec, list, cyc, sink);
+                if (v == 11) variant_i<4, 1><<<blocks, 32>>>(rec, list, cyc, sink);
+                if (v == 6) variant_g<4><<<blocks, 32>>>(rec, list, cyc, sink);
+                if (v == 7) variant_g<3><<<blocks, 32>>>(rec, list, cyc, sink);
                 cudaError_t e = cudaDeviceSynchronize();
                 if (e != cudaSuccess) { printf("variant %c: %s\n", 'A' + v, cudaGetErrorString(e)); return 1; }
             }

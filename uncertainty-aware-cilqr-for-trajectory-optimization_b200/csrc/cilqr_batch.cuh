@@ -48,10 +48,53 @@ struct BatchView {
     const double *ocv;  // [B][n_obs][CV_FIELDS]
     const double *oib2; // [B][n_obs][N]
     const double *orec; // [B][n_obs][OB_FIELDS][N]  (the fused kernels' records)
+    unsigned long long *trace; // diagnostics (cilqr_solve_trace): [max_iter + 3][kTraceKinds][2] first-start / last-end per launch, or null
     __device__ __forceinline__ int *list(int r) const { return (r & 1) ? list1 : list0; }
     __device__ __forceinline__ double *header(int b) const { return hdr + (size_t)b * kHdrD; }
     __device__ __forceinline__ double *step(int b, int t) const { return rec + ((size_t)b * (N + 1) + t) * kStepD; }
 };
+// Timeline of one solve without a profiler: every CTA's thread 0 folds %globaltimer into (min start, ~max end) of its launch.
+enum { TRACE_COST = 0, TRACE_DERIVS, TRACE_SWEEP, TRACE_IO, kTraceKinds };
+struct TraceScope {
+    unsigned long long *t;
+    __device__ __forceinline__ static unsigned long long now()
+    {
+        unsigned long long v;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(v));
+        return v;
+    }
+    __device__ __forceinline__ TraceScope(const BatchView &V, int kind, int round) : t(V.trace ? V.trace + 2 * ((size_t)round * kTraceKinds + kind) : nullptr)
+    {
+        if (t && threadIdx.x == 0) atomicMin(t, now());
+    }
+    __device__ __forceinline__ ~TraceScope()
+    {
+        if (t && threadIdx.x == 0) atomicMin(t + 1, ~now());
+    }
+};
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void *src) { asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory"); }
+// L2 policy for data that is read once per pass (the 1/b^2 stream): evicted before the step records, which every kernel of a
+// round touches again.
+__device__ __forceinline__ uint64_t l2_evict_first_policy()
+{
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+__device__ __forceinline__ double ld_stream(const double *p, uint64_t pol)
+{
+    double v;
+    asm volatile("ld.global.L1::no_allocate.L2::cache_hint.f64 %0, [%1], %2;" : "=d"(v) : "l"(p), "l"(pol));
+    return v;
+}
+__device__ __forceinline__ void cp_async8_stream(uint32_t dst, const void *src, uint64_t pol)
+{
+    asm volatile("cp.async.ca.shared.global.L2::cache_hint [%0], [%1], 8, %2;" ::"r"(dst), "l"(src), "l"(pol) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int KEEP>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(KEEP) : "memory"); }
+
 __device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 __device__ __forceinline__ int2 &hdr_ints(double *h, int which) { return *reinterpret_cast<int2 *>(h + which); }
 __device__ __forceinline__ double2 ld2(const double *p) { return *reinterpret_cast<const double2 *>(p); }
@@ -161,6 +204,7 @@ __global__ void __launch_bounds__(256) expand_cv_records_kernel(DevParams P, siz
 __global__ void __launch_bounds__(128) batch_init_kernel(DevParams P, BatchView V, int B, const double *__restrict__ x0, const double *__restrict__ U,
                                                          const double *__restrict__ poly, const double *__restrict__ xlp)
 {
+    TraceScope trace_scope(V, TRACE_IO, 0);
     const int N = P.N;
     const int b = blockIdx.x * blockDim.x + threadIdx.x;
     if (b == 0)
@@ -218,6 +262,7 @@ __global__ void __launch_bounds__(128) batch_init_kernel(DevParams P, BatchView 
 __global__ void __launch_bounds__(256) batch_output_kernel(DevParams P, BatchView V, int B, double *__restrict__ U, double *__restrict__ X,
                                                            double *__restrict__ J, int32_t *__restrict__ iters, int32_t *__restrict__ status)
 {
+    TraceScope trace_scope(V, TRACE_IO, 1);
     const int N = P.N;
     const size_t total = (size_t)B * (N + 1);
     for (size_t g = blockIdx.x * (size_t)blockDim.x + threadIdx.x; g < total; g += (size_t)gridDim.x * blockDim.x) {
@@ -247,6 +292,7 @@ __host__ __device__ inline int cost_entries_per_cta(int N) { return N >= kCostTh
 // Dynamic shared memory: entries_per_cta * N doubles (the per-step cost terms of the CTA's scenarios).
 __global__ void __launch_bounds__(kCostThreads) batch_cost_kernel(DevParams P, BatchView V, int round)
 {
+    TraceScope trace_scope(V, TRACE_COST, round);
     extern __shared__ double sJ[];
     const int N = P.N;
     const int E = cost_entries_per_cta(N);
@@ -347,11 +393,22 @@ __global__ void __launch_bounds__(kCostThreads) batch_cost_kernel(DevParams P, B
 // Constraints::get_state_cost (Constraints.cpp:145-227) obstacle part + get_control_cost (:86-137) for accepted scenarios.
 // Flat index g = entry * N + t: lanes walk consecutive timesteps, so a warp touches one or two scenarios — its obstacle
 // constants are (nearly) warp-uniform loads and the per-timestep arrays are read coalesced.
+//
+// STAGED (constant-velocity obstacles): the one per-(obstacle, timestep) input, 1/b^2, is the kernel's HBM stream — n_obs
+// doubles per item.  Read with plain loads two obstacles ahead it keeps ~24 bytes per thread in flight, which at 16 warps per SM
+// is ~2 TB/s worth of outstanding requests: the FP64 pipe sat at 57 % behind long-scoreboard stalls.  Staged, every thread
+// cp.asyncs the whole 1/b^2 column of its NEXT item into its own shared-memory column (dynamic, 2 x n_obs x 256 doubles) while
+// the current item is evaluated: n_obs x 8 bytes in flight per thread for the length of an item, no barrier needed (a thread
+// reads only what it copied itself).
 constexpr int kDerivThreads = 256;
+__host__ __device__ inline size_t deriv_stage_bytes(int n_obs) { return (size_t)2 * n_obs * kDerivThreads * sizeof(double); }
 
-template <bool CV>
+template <bool CV, bool STAGED = false>
 __global__ void __launch_bounds__(kDerivThreads, 2) batch_derivs_kernel(DevParams P, BatchView V, int round)
 {
+    static_assert(CV || !STAGED, "only the compact obstacle form has a separate 1/b^2 stream");
+    extern __shared__ __align__(16) double deriv_smem[];
+    TraceScope trace_scope(V, TRACE_DERIVS, round);
     const int N = P.N;
     const int cnt = V.cnt[round + 1];
     const int *list = V.list(round + 1);
@@ -365,6 +422,15 @@ __global__ void __launch_bounds__(kDerivThreads, 2) batch_derivs_kernel(DevParam
     int b = 0, t = 0, b_next = 0;
     double2 xy = make_double2(0, 0), cs = xy, u = xy;
     double v = 0;
+    int stage = 0;
+    const uint64_t stream_policy = l2_evict_first_policy();
+    const uint32_t col0 = (uint32_t)__cvta_generic_to_shared(deriv_smem + threadIdx.x);
+    auto stage_column = [&](int bb, int tt, int st) { // 1/b^2 of item (bb, tt), all obstacles -> this thread's column of stage st
+        const double *src = V.oib2 + (size_t)bb * n_obs * N + tt;
+        uint32_t dst = col0 + (uint32_t)st * n_obs * kDerivThreads * 8;
+        for (int j = 0; j < n_obs; ++j, src += N, dst += kDerivThreads * 8)
+            cp_async8_stream(dst, src, stream_policy);
+    };
     if (g < total) {
         const int e = (int)(g / N);
         t = (int)(g - (long long)e * N);
@@ -373,6 +439,10 @@ __global__ void __launch_bounds__(kDerivThreads, 2) batch_derivs_kernel(DevParam
         xy = ld2(r + S_X); cs = ld2(r + S_C); u = ld2(r + S_U0); v = r[S_V];
         if (g + stride < total)
             b_next = list[(int)((g + stride) / N)];
+        if (STAGED) {
+            stage_column(b, t, 0);
+            cp_async_commit();
+        }
     }
     for (; g < total; g += stride) {
         double *r = V.step(b, t);
@@ -390,11 +460,19 @@ __global__ void __launch_bounds__(kDerivThreads, 2) batch_derivs_kernel(DevParam
                 const char *oc_n = reinterpret_cast<const char *>(V.ocv + (size_t)bn * n_obs * CV_FIELDS);
                 for (int sct = tn; sct < 2 * n_obs; sct += N)
                     prefetch_l2(oc_n + 32 * sct);
-                const double *ob_n = V.oib2 + (size_t)bn * n_obs * N + tn;
-                prefetch_l2(ob_n);
-                if (n_obs > 1)
-                    prefetch_l2(ob_n + N);
+                if (STAGED) {
+                    stage_column(bn, tn, stage ^ 1);
+                } else {
+                    const double *ob_n = V.oib2 + (size_t)bn * n_obs * N + tn;
+                    prefetch_l2(ob_n);
+                    if (n_obs > 1)
+                        prefetch_l2(ob_n + N);
+                }
             }
+        }
+        if (STAGED) {
+            cp_async_commit();
+            cp_async_wait<1>(); // this item's column has landed; the next item's stays in flight
         }
         double g0 = 0, g1 = 0, h00 = 0, h01 = 0, h11 = 0, bo = 0;
         if (n_obs > 0) {
@@ -402,20 +480,26 @@ __global__ void __launch_bounds__(kDerivThreads, 2) batch_derivs_kernel(DevParam
                 const double tt = t * P.dt;
                 const double *oc = V.ocv + (size_t)b * n_obs * CV_FIELDS, *ob = V.oib2 + (size_t)b * n_obs * N + t;
                 double2 n0 = ld2(oc), n1 = ld2(oc + 2), n2 = ld2(oc + 4), n3 = ld2(oc + 6);
-                double nib = ob[0], nib2 = n_obs > 1 ? ob[N] : 0.0;
+                const double *col = deriv_smem + (size_t)stage * n_obs * kDerivThreads + threadIdx.x;
+                double nib = STAGED ? col[0] : ld_stream(ob, stream_policy), nib2 = STAGED || n_obs < 2 ? 0.0 : ld_stream(ob + N, stream_policy);
 #pragma unroll 1
                 for (int j = 0; j < n_obs; ++j) {
                     const double xo = n0.x + n1.x * tt, yo = n0.y + n1.y * tt; // cv_position
                     const double co = n2.x, so = n2.y, ia2 = n3.x, ib2 = nib;
-                    // the next obstacle's constants (warp-uniform, cached) and the 1/b^2 stream two obstacles ahead (HBM) travel
-                    // while this one is evaluated
-                    nib = nib2;
+                    // the next obstacle's constants (warp-uniform, cached) and the 1/b^2 stream (staged: the shared-memory column;
+                    // else two obstacles ahead from HBM) travel while this one is evaluated
+                    if (STAGED) {
+                        if (j + 1 < n_obs)
+                            nib = col[(size_t)(j + 1) * kDerivThreads];
+                    } else {
+                        nib = nib2;
+                    }
                     if (j + 1 < n_obs) {
                         const double *o2 = oc + (size_t)(j + 1) * CV_FIELDS;
                         n0 = ld2(o2); n1 = ld2(o2 + 2); n2 = ld2(o2 + 4); n3 = ld2(o2 + 6);
                     }
-                    if (j + 2 < n_obs)
-                        nib2 = ob[(size_t)(j + 2) * N];
+                    if (!STAGED && j + 2 < n_obs)
+                        nib2 = ld_stream(ob + (size_t)(j + 2) * N, stream_policy);
                     obstacle_terms<true>(P, x, y, ce, se, xo, yo, co, so, ia2, ib2, g0, g1, h00, h01, h11, bo);
                 }
             } else {
@@ -441,6 +525,7 @@ __global__ void __launch_bounds__(kDerivThreads, 2) batch_derivs_kernel(DevParam
         st2(r + S_R + 8, luu0, luu1);
         b = bn;
         t = tn;
+        stage ^= 1;
     }
 }
 
@@ -453,140 +538,227 @@ __device__ __forceinline__ void prefetch_step(const double *r)
         prefetch_l2(r + 4 * k);
 }
 
-// What one backward step reads from step record j: (v, cos, sin) feed step j-1 (A, B are linearised about column j+1), the
-// rest feeds step j.
-struct SweepRec {
-    double v, c, s, u0;
-    double d[kRec];
-};
-__device__ __forceinline__ void load_sweep_rec(const double *r, SweepRec &o)
-{
-    const double2 vt = ld2(r + S_V), cs = ld2(r + S_C), u = ld2(r + S_U0);
-    o.v = vt.x; o.c = cs.x; o.s = cs.y; o.u0 = u.x;
-#pragma unroll
-    for (int f = 0; f < kRec; f += 2) {
-        const double2 a = ld2(r + S_R + f);
-        o.d[f] = a.x;
-        o.d[f + 1] = a.y;
-    }
-}
-// What one forward step reads: control and gains of record t, the old state column of record t+1.
-struct ForwardIn {
-    double u0, u1, p0, p1, p2, p3, g[kRec];
-};
-__device__ __forceinline__ void load_forward_in(const double *r, ForwardIn &F)
-{
-    const double2 u = ld2(r + S_U0), a = ld2(r + kStepD + S_X), c = ld2(r + kStepD + S_V);
-    F.u0 = u.x; F.u1 = u.y;
-    F.p0 = a.x; F.p1 = a.y; F.p2 = c.x; F.p3 = c.y; // old column t+1, read before it is overwritten
-#pragma unroll
-    for (int f = 0; f < kRec; f += 2) {
-        const double2 q = ld2(r + S_R + f);
-        F.g[f] = q.x;
-        F.g[f + 1] = q.y;
-    }
-}
-
+// ---- Riccati sweep + rollout: one scenario per lane, one warp per CTA.
+//
+// The 32 scenarios of a warp sit anywhere in the batch (work-list order), so "lane l loads its own record" is 32 cache lines per
+// warp instruction: measured (tools/stream_micro.cu) that costs ~2.9 cycles per line in the load/store unit and bounds the sweep
+// at ~5600 cycles per step with 12 warps per SM.  Instead the warp moves the 32 records of a step together: 32 x 9 pieces of
+// 16 bytes, lane l taking pieces l, l + 32, ... — consecutive lanes read consecutive bytes of one record, ~6 lines per instruction.
+// The pieces go to a shared-memory ring with cp.async (kRing records deep, i.e. kRing - 1 steps ahead of the arithmetic), each
+// lane reads its own record back from the ring (144-byte rows: conflict-free 128-bit reads), and results return the same way:
+// staged in shared memory, written by the warp in 16-byte pieces.  Same probe: ~3300 cycles per step at 12 warps per SM, which
+// is the HBM rate for this traffic.
 constexpr int kSweepThreads = 32;
-constexpr int kSweepAhead = 6; // L2 prefetch distance in steps
+constexpr int kRing = 3;                       // records in flight per lane
+constexpr int kPieces = kStepD / 2;            // 16-byte pieces per step record
+constexpr int kOutD = 10;                      // doubles per staged result row (80-byte rows: conflict-free)
+static_assert(kOutD >= kRec && kOutD % 2 == 0, "a result row holds the gains of one step");
 
-__global__ void __launch_bounds__(kSweepThreads, 12) batch_sweep_kernel(DevParams P, BatchView V, int round)
+struct SweepSmem {
+    double ring[kRing][kSweepThreads][kStepD];
+    double out[2][kSweepThreads][kOutD];
+};
+
+__global__ void __launch_bounds__(kSweepThreads, 11) batch_sweep_kernel(DevParams P, BatchView V, int round)
 {
+    TraceScope trace_scope(V, TRACE_SWEEP, round);
+    __shared__ __align__(16) SweepSmem sm;
     const int N = P.N;
     const int cnt = V.cnt[round + 1];
     const int *list = V.list(round + 1);
-    for (int i = blockIdx.x * kSweepThreads + threadIdx.x; i < cnt; i += gridDim.x * kSweepThreads) {
-        const int b = list[i];
+    const int lane = threadIdx.x;
+    const uint32_t ring0 = (uint32_t)__cvta_generic_to_shared(&sm.ring[0][0][0]);
+    constexpr uint32_t kSlotBytes = kSweepThreads * kStepD * 8;
+    const size_t stride16 = (size_t)(N + 1) * kPieces; // 16-byte pieces per scenario
+
+    for (int i0 = blockIdx.x * kSweepThreads; i0 < cnt; i0 += gridDim.x * kSweepThreads) {
+        const int nact = min(kSweepThreads, cnt - i0);
+        const bool active = lane < nact;
+        const int b = list[i0 + (active ? lane : 0)];
         double *h = V.header(b);
-        double *rec = V.step(b, 0);
         const double lamb = h[H_LAMB];
-#ifdef CILQR_SWEEP_CLOCKS
-        unsigned long long g0, g1, g2;
-        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g0));
-#endif
+        const double2 *rec16 = reinterpret_cast<const double2 *>(V.rec);
+        // piece p = k * 32 + lane of a step belongs to the scenario of lane p / pieces-per-row
+        size_t ld_off[kPieces]; // load pieces: record (lane p / 9), piece p % 9
+        bool ld_on[kPieces];
+#pragma unroll
+        for (int k = 0; k < kPieces; ++k) {
+            const int p = k * kSweepThreads + lane, src = p / kPieces, f = p - src * kPieces;
+            ld_off[k] = (size_t)__shfl_sync(0xffffffffu, b, src) * stride16 + f;
+            ld_on[k] = src < nact;
+        }
+        auto fetch = [&](int t, int slot) { // record t of every active lane -> ring[slot]
+#pragma unroll
+            for (int k = 0; k < kPieces; ++k)
+                if (ld_on[k])
+                    cp_async16(ring0 + slot * kSlotBytes + (k * kSweepThreads + lane) * 16, rec16 + ld_off[k] + (size_t)t * kPieces);
+        };
+
         // ---- iLQR::backward_pass (iLQR.cpp:91-195): gains overwrite the derivative records
+        constexpr int kGainPieces = kRec / 2;
+        size_t st_off[kGainPieces];
+        bool st_on[kGainPieces];
+#pragma unroll
+        for (int k = 0; k < kGainPieces; ++k) {
+            const int p = k * kSweepThreads + lane, src = p / kGainPieces, f = p - src * kGainPieces;
+            st_off[k] = (size_t)__shfl_sync(0xffffffffu, b, src) * stride16 + S_R / 2 + f;
+            st_on[k] = src < nact;
+        }
+        auto flush_gains = [&](int j) { // staged gains of step j -> records j
+            const double2 *o = reinterpret_cast<const double2 *>(&sm.out[j & 1][0][0]);
+            double2 *g16 = reinterpret_cast<double2 *>(V.rec);
+#pragma unroll
+            for (int k = 0; k < kGainPieces; ++k)
+                if (st_on[k])
+                    g16[st_off[k] + (size_t)j * kPieces] = o[k * kSweepThreads + lane];
+        };
         RiccatiState S;
         RiccatiIn I;
-        SweepRec cur, nxt;
         {
-            const double *rN = rec + (size_t)N * kStepD;
+            const double *rN = V.step(b, N);
             const double2 vt = ld2(rN + S_V), cs = ld2(rN + S_C);
             I.v = vt.x; I.c = cs.x; I.s = cs.y;
         }
-        load_sweep_rec(rec + (size_t)(N - 1) * kStepD, cur);
-        riccati_seed(P, cur.d, S);
+        __syncwarp(); // the previous group's staged results have been read
+        int slot = 0;  // ring slot of the record the arithmetic is at
+#pragma unroll
+        for (int d = 0; d < kRing - 1; ++d) {
+            if (N - 1 - d >= 0)
+                fetch(N - 1 - d, d);
+            cp_async_commit();
+        }
         bool finite = true;
         for (int j = N - 1; j >= 0; --j) {
-            double *rj = rec + (size_t)j * kStepD;
-            if (j > 0)
-                load_sweep_rec(rj - kStepD, nxt);
-            if (j >= kSweepAhead) // record j - kSweepAhead on its way to L2
-                prefetch_step(rj - kSweepAhead * kStepD);
-            I.acc = cur.u0;
+            cp_async_wait<kRing - 2>(); // record j has landed (this lane's pieces) ...
+            __syncwarp();               // ... and every other lane's; the slot of record j + 1 is free; staged gains j + 1 are visible
+            {
+                const int nslot = slot == 0 ? kRing - 1 : slot - 1; // slot of record j - (kRing - 1) == slot of record j + 1
+                if (j - (kRing - 1) >= 0)
+                    fetch(j - (kRing - 1), nslot);
+                cp_async_commit();
+            }
+            if (j < N - 1)
+                flush_gains(j + 1);
+            const double *r = &sm.ring[slot][lane][0];
+            const double2 vt = *reinterpret_cast<const double2 *>(r + S_V), cs = *reinterpret_cast<const double2 *>(r + S_C),
+                          u = *reinterpret_cast<const double2 *>(r + S_U0);
+            I.acc = u.x;
 #pragma unroll
-            for (int f = 0; f < kRec; ++f)
-                I.d[f] = cur.d[f];
+            for (int f = 0; f < kRec; f += 2) {
+                const double2 q = *reinterpret_cast<const double2 *>(r + S_R + f);
+                I.d[f] = q.x;
+                I.d[f + 1] = q.y;
+            }
+            if (j == N - 1)
+                riccati_seed(P, I.d, S);
             double g[kRec];
             finite = riccati_step(P, I, lamb, S, g) && finite;
+            double *o = &sm.out[j & 1][lane][0];
 #pragma unroll
             for (int f = 0; f < kRec; f += 2)
-                st2(rj + S_R + f, g[f], g[f + 1]);
-            I.v = cur.v; I.c = cur.c; I.s = cur.s;
-            cur = nxt;
+                *reinterpret_cast<double2 *>(o + f) = make_double2(g[f], g[f + 1]);
+            I.v = vt.x; I.c = cs.x; I.s = cs.y;
+            slot = slot == kRing - 1 ? 0 : slot + 1; // record j - 1 sits in the next slot
         }
-        if (!finite) { // the reference's `return false` path: the loop stops, the current nominal is the result (iLQR.cpp:214-215)
+        cp_async_wait<0>();
+        __syncwarp();
+        flush_gains(0);
+        __threadfence();
+        __syncwarp(); // gains are in memory before the rollout's cp.async reads them (other lanes' writes included)
+
+        // the reference's `return false` path: the loop stops, the current nominal is the result (iLQR.cpp:214-215)
+        const bool roll = active && finite;
+        if (active && !finite) {
             hdr_ints(h, H_CONV_STATUS).y = CILQR_ST_NONFINITE;
             h[H_JRES] = h[H_JNEW];
             hdr_ints(h, H_ITERS_MODE).y = MODE_DONE;
-            continue;
         }
-#ifdef CILQR_SWEEP_CLOCKS
-        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g1));
-#endif
+        const unsigned roll_mask = __ballot_sync(0xffffffffu, roll);
+
         // ---- iLQR::forward_pass (iLQR.cpp:68-86), full step, in place: the candidate is accepted by construction (lagged test)
-        {
-            const double2 a = ld2(rec + S_X), c2 = ld2(rec + S_V), cs = ld2(rec + S_C);
-            double n0 = a.x, n1 = a.y, n2 = c2.x, n3 = c2.y;
-            double o0 = n0, o1 = n1, o2 = n2, o3 = n3;
-            double c = cs.x, s = cs.y;
-            ForwardIn F, G;
-            load_forward_in(rec, F);
-            for (int t = 0; t < N; ++t) {
-                double *rt = rec + (size_t)t * kStepD;
-                if (t + 1 < N)
-                    load_forward_in(rt + kStepD, G);
-                if (t + kSweepAhead <= N)
-                    prefetch_step(rt + kSweepAhead * kStepD);
-                double u0 = F.u0, u1 = F.u1;
-                apply_gains(F.g, n0 - o0, n1 - o1, n2 - o2, n3 - o3, u0, u1);
-                double m0, m1, m2, m3;
-                dyn_step(P, n0, n1, n2, n3, c, s, u0, u1, m0, m1, m2, m3);
-                sincos(m3, &s, &c);
-                st2(rt + S_U0, u0, u1); // unclamped, like U_new (iLQR.cpp:83)
-                st2(rt + kStepD + S_X, m0, m1);
-                st2(rt + kStepD + S_V, m2, m3);
-                st2(rt + kStepD + S_C, c, s);
-                o0 = F.p0; o1 = F.p1; o2 = F.p2; o3 = F.p3;
-                n0 = m0; n1 = m1; n2 = m2; n3 = m3;
-                F = G;
-            }
+        // Step t reads record t (old state column, control, gains) and produces U(:, t) and column t + 1; they are written one
+        // step later, when record t + 1 — whose old column is still needed — is known to be in the ring.
+        constexpr int kRollPieces = 4; // (u0, u1) -> record t; (x, y), (v, theta), (cos, sin) -> record t + 1
+        size_t ro_off[kRollPieces];
+        bool ro_on[kRollPieces];
+#pragma unroll
+        for (int k = 0; k < kRollPieces; ++k) {
+            const int p = k * kSweepThreads + lane, src = p / kRollPieces, f = p - src * kRollPieces;
+            ro_off[k] = (size_t)__shfl_sync(0xffffffffu, b, src) * stride16 + (f == 0 ? S_U0 / 2 : kPieces + f - 1);
+            ro_on[k] = (roll_mask >> src) & 1u;
         }
-#ifdef CILQR_SWEEP_CLOCKS
-        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g2));
-        if (threadIdx.x == 0 && (round == 12 || round == 0) && (blockIdx.x % 37) == 0)
-            printf("round %d block %d cnt %d: start %llu ns  backward %llu ns  forward %llu ns\n", round, blockIdx.x, cnt, g0 % 100000000ull, g1 - g0, g2 - g1);
-#endif
+        auto flush_roll = [&](int t) {
+            double2 *g16 = reinterpret_cast<double2 *>(V.rec);
+#pragma unroll
+            for (int k = 0; k < kRollPieces; ++k) {
+                const int p = k * kSweepThreads + lane, src = p / kRollPieces, f = p - src * kRollPieces;
+                if (ro_on[k])
+                    g16[ro_off[k] + (size_t)t * kPieces] = *reinterpret_cast<const double2 *>(&sm.out[t & 1][src][2 * f]);
+            }
+        };
+        slot = 0;
+#pragma unroll
+        for (int d = 0; d < kRing - 1; ++d) {
+            if (d < N)
+                fetch(d, d);
+            cp_async_commit();
+        }
+        double n0 = 0, n1 = 0, n2 = 0, n3 = 0, c = 0, s = 0;
+        for (int t = 0; t < N; ++t) {
+            cp_async_wait<kRing - 2>();
+            __syncwarp();
+            {
+                const int nslot = slot == 0 ? kRing - 1 : slot - 1;
+                if (t + (kRing - 1) < N)
+                    fetch(t + (kRing - 1), nslot);
+                cp_async_commit();
+            }
+            if (t > 0)
+                flush_roll(t - 1);
+            const double *r = &sm.ring[slot][lane][0];
+            const double2 xy = *reinterpret_cast<const double2 *>(r + S_X), vt = *reinterpret_cast<const double2 *>(r + S_V),
+                          u = *reinterpret_cast<const double2 *>(r + S_U0);
+            double g[kRec];
+#pragma unroll
+            for (int f = 0; f < kRec; f += 2) {
+                const double2 q = *reinterpret_cast<const double2 *>(r + S_R + f);
+                g[f] = q.x;
+                g[f + 1] = q.y;
+            }
+            if (t == 0) {
+                const double2 cs = *reinterpret_cast<const double2 *>(r + S_C);
+                n0 = xy.x; n1 = xy.y; n2 = vt.x; n3 = vt.y;
+                c = cs.x; s = cs.y;
+            }
+            double u0 = u.x, u1 = u.y;
+            apply_gains(g, n0 - xy.x, n1 - xy.y, n2 - vt.x, n3 - vt.y, u0, u1);
+            double m0, m1, m2, m3;
+            dyn_step(P, n0, n1, n2, n3, c, s, u0, u1, m0, m1, m2, m3);
+            sincos(m3, &s, &c);
+            double *o = &sm.out[t & 1][lane][0];
+            *reinterpret_cast<double2 *>(o + 0) = make_double2(u0, u1); // unclamped, like U_new (iLQR.cpp:83)
+            *reinterpret_cast<double2 *>(o + 2) = make_double2(m0, m1);
+            *reinterpret_cast<double2 *>(o + 4) = make_double2(m2, m3);
+            *reinterpret_cast<double2 *>(o + 6) = make_double2(c, s);
+            n0 = m0; n1 = m1; n2 = m2; n3 = m3;
+            slot = slot == kRing - 1 ? 0 : slot + 1;
+        }
+        cp_async_wait<0>();
+        __syncwarp();
+        flush_roll(N - 1);
         // ---- iLQR.cpp:219-228
-        h[H_LAMB] = lamb / P.lamb_factor;
-        const int2 cst = hdr_ints(h, H_CONV_STATUS);
-        if (cst.x) {
-            hdr_ints(h, H_CONV_STATUS).y = CILQR_ST_TOLERANCE;
-            hdr_ints(h, H_ITERS_MODE).y = MODE_FINAL;
-        } else if (hdr_ints(h, H_ITERS_MODE).x >= P.max_iter) {
-            hdr_ints(h, H_CONV_STATUS).y = CILQR_ST_MAX_ITER;
-            hdr_ints(h, H_ITERS_MODE).y = MODE_FINAL;
-        } else {
-            h[H_JOLD] = h[H_JNEW];
+        if (roll) {
+            h[H_LAMB] = lamb / P.lamb_factor;
+            const int2 cst = hdr_ints(h, H_CONV_STATUS);
+            if (cst.x) {
+                hdr_ints(h, H_CONV_STATUS).y = CILQR_ST_TOLERANCE;
+                hdr_ints(h, H_ITERS_MODE).y = MODE_FINAL;
+            } else if (hdr_ints(h, H_ITERS_MODE).x >= P.max_iter) {
+                hdr_ints(h, H_CONV_STATUS).y = CILQR_ST_MAX_ITER;
+                hdr_ints(h, H_ITERS_MODE).y = MODE_FINAL;
+            } else {
+                h[H_JOLD] = h[H_JNEW];
+            }
         }
     }
 }

@@ -304,6 +304,8 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) stage_kernel(const StageA
 // ================================================================================================= host side
 using namespace cilqr;
 
+constexpr int kMaxChunks = 8; // batch-synchronous solve: chunks of the batch, one stream each
+
 struct cilqr_solver {
     cilqr_params p;
     DevParams dp;
@@ -317,7 +319,20 @@ struct cilqr_solver {
     DevBuf obs_b;                // compact constant-velocity obstacles (cilqr_batch.cuh)
     int obs_cv = 0;              // obs_b holds the compact constant-velocity form
     DevBuf bws;                  // state of the batch-synchronous solve
-    int *last_cnt = nullptr;     // work-list lengths of the last batch-synchronous solve (device)
+    int *last_cnt = nullptr;     // work-list lengths of the last batch-synchronous solve (device), one block per chunk
+    int last_chunks = 1;
+    int force_chunks = 0;        // CILQR_CHUNKS: override the number of chunks (A/B switch)
+    bool deriv_staged = true;    // CILQR_DERIV_STAGED=0: plain loads for the 1/b^2 stream (A/B switch)
+    int smem_per_sm = 0;
+    bool trace_on = false;       // CILQR_TRACE=1: kernels record their start / end times (cilqr_solve_trace)
+    DevBuf trace;
+    cudaStream_t chunk_stream[kMaxChunks] = {};
+    cudaEvent_t ev_fork = nullptr, ev_join[kMaxChunks] = {}, ev_copied = nullptr;
+    cudaStream_t cap_stream = nullptr;       // origin stream of the recorded solve
+    cudaGraphExec_t graph_exec = nullptr;    // the last repeated solve, recorded (solve_rounds)
+    std::vector<uintptr_t> graph_key, seen_key;
+    long long graph_kernels = 0;
+    bool use_graph = true;                   // CILQR_GRAPH=0: always issue the launches directly
     DevBuf counter, scratch;
     DevBuf stage[12];            // staging for CILQR_MEM_HOST callers / stage outputs
 };
@@ -494,6 +509,12 @@ int cilqr_create(const cilqr_params *p, int max_batch, int max_obs, cilqr_handle
         const size_t cost_smem = (size_t)cost_entries_per_cta(h->dp.N) * h->dp.N * sizeof(double);
         if (cost_smem > 48 * 1024)
             CILQR_CUDA(cudaFuncSetAttribute(batch_cost_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cost_smem));
+        CILQR_CUDA(cudaDeviceGetAttribute(&h->smem_per_sm, cudaDevAttrMaxSharedMemoryPerMultiprocessor, dev));
+        int optin = 0;
+        CILQR_CUDA(cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
+        h->smem_per_sm = std::min(h->smem_per_sm, 2 * optin);
+        CILQR_CUDA(cudaFuncSetAttribute(batch_derivs_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, std::min(optin, h->smem_per_sm / 2 - 1024)));
+
         int o0 = 0, o1 = 0, o2 = 0, o3 = 0;
         CILQR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o0, batch_cost_kernel, kCostThreads, cost_smem));
         CILQR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o1, batch_derivs_kernel<true>, kDerivThreads, 0));
@@ -507,7 +528,24 @@ int cilqr_create(const cilqr_params *p, int max_batch, int max_obs, cilqr_handle
         const int v = atoi(e);
         if (v == 1 || v == 3) h->variant = v;
     }
+    if (const char *e = getenv("CILQR_CHUNKS")) h->force_chunks = std::max(0, atoi(e));
+    if (const char *e = getenv("CILQR_GRAPH")) h->use_graph = atoi(e) != 0;
+    if (const char *e = getenv("CILQR_DERIV_STAGED")) h->deriv_staged = atoi(e) != 0;
+    if (const char *e = getenv("CILQR_TRACE")) h->trace_on = atoi(e) != 0;
     if (int rc = h->counter.reserve(sizeof(int))) { delete h; return rc; }
+    bool ok = cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming) == cudaSuccess;
+    int prio_least = 0, prio_greatest = 0; // earlier chunks get the higher priority: they finish first (see solve_rounds)
+    cudaDeviceGetStreamPriorityRange(&prio_least, &prio_greatest);
+    for (int c = 0; c < kMaxChunks && ok; ++c)
+        ok = cudaStreamCreateWithPriority(&h->chunk_stream[c], cudaStreamNonBlocking, std::min(prio_greatest + c, prio_least)) == cudaSuccess &&
+             cudaEventCreateWithFlags(&h->ev_join[c], cudaEventDisableTiming) == cudaSuccess;
+    ok = ok && cudaStreamCreateWithFlags(&h->cap_stream, cudaStreamNonBlocking) == cudaSuccess;
+    ok = ok && cudaEventCreateWithFlags(&h->ev_copied, cudaEventDisableTiming | cudaEventBlockingSync) == cudaSuccess;
+    if (!ok) {
+        const cudaError_t e = cudaGetLastError();
+        cilqr_destroy(h);
+        return fail(CILQR_E_CUDA, "stream/event creation failed: %s", cudaGetErrorString(e));
+    }
     *out = h;
     return 0;
 }
@@ -518,9 +556,18 @@ int cilqr_destroy(cilqr_handle h)
     h->obs.release();
     h->obs_b.release();
     h->bws.release();
+    h->trace.release();
     h->counter.release();
     h->scratch.release();
     for (auto &s : h->stage) s.release();
+    for (int c = 0; c < kMaxChunks; ++c) {
+        if (h->chunk_stream[c]) cudaStreamDestroy(h->chunk_stream[c]);
+        if (h->ev_join[c]) cudaEventDestroy(h->ev_join[c]);
+    }
+    if (h->ev_fork) cudaEventDestroy(h->ev_fork);
+    if (h->ev_copied) cudaEventDestroy(h->ev_copied);
+    if (h->graph_exec) cudaGraphExecDestroy(h->graph_exec);
+    if (h->cap_stream) cudaStreamDestroy(h->cap_stream);
     delete h;
     return 0;
 }
@@ -577,6 +624,7 @@ int cilqr_set_obstacles_cv(cilqr_handle h, int B, int n_obs, const double *state
     if (int rc = stage_in(h, 0, state0, n_bj * 4, mem, st, &d_s)) return rc;
     if (int rc = stage_in(h, 1, LW, n_bj * 2, mem, st, &d_lw)) return rc;
     if (int rc = stage_in(h, 2, sigma, n_bj * 3, mem, st, &d_sg)) return rc;
+    if (mem == CILQR_MEM_HOST) CILQR_CUDA(cudaEventRecord(h->ev_copied, st));
     if (int rc = h->obs_b.reserve(n_bj * (CV_FIELDS + N) * sizeof(double))) return rc;
     double *ocv = h->obs_b.as<double>(), *oib2 = ocv + n_bj * CV_FIELDS;
     prep_obstacles_cv_kernel<<<prep_grid(n_bj, h->num_sms), 256, 0, st>>>(h->dp, n_bj, d_s, d_lw, d_sg, kappa, ocv);
@@ -585,7 +633,8 @@ int cilqr_set_obstacles_cv(cilqr_handle h, int B, int n_obs, const double *state
     CILQR_LAUNCH_CHECK();
     h->obs_cv = 1;
     h->obs_ready = false;
-    if (mem == CILQR_MEM_HOST) CILQR_CUDA(cudaStreamSynchronize(st));
+    // host arrays: the caller may reuse them once they have been copied; the two kernels stay in flight on `stream`
+    if (mem == CILQR_MEM_HOST) CILQR_CUDA(cudaEventSynchronize(h->ev_copied));
     return 0;
 }
 
@@ -597,53 +646,213 @@ static int need_obstacles(cilqr_handle h, int B)
 }
 
 // Batch-synchronous solve (cilqr_batch.cuh): a fixed sequence of launches, work lists and termination handled on the device.
-static int solve_rounds(cilqr_handle h, const SolveArgs &A, cudaStream_t st)
+//
+// The batch is cut into up to kMaxChunks contiguous chunks, each with its own work lists, on its own stream (forked from and
+// joined back into the caller's stream with events).  Two reasons: (1) after the first rounds a round's kernels are short and
+// latency-bound (a sweep over a few thousand scenarios takes as long as the dependent chain of one thread), so the chunks'
+// sweeps, cost and derivative kernels overlap each other; (2) with host buffers each chunk's host->device copies, rounds and
+// device->host copies form a pipeline, so PCIe transfers run under the other chunks' kernels.
+struct HostIO { // caller's host arrays (CILQR_MEM_HOST) — null members when the caller's buffers are device memory
+    const double *x0 = nullptr, *U_in = nullptr, *poly = nullptr, *xlp = nullptr;
+    double *U = nullptr, *X = nullptr, *J = nullptr;
+    int32_t *iters = nullptr, *status = nullptr;
+};
+
+// The launches of one solve, relative to stream `st` (the caller's stream, or the capture stream when a graph is recorded).
+static int issue_rounds(cilqr_handle h, const SolveArgs &A, const HostIO *io, cudaStream_t st, int K, int Bc)
+{
+    const DevParams &P = h->dp;
+    const int N = P.N, B = A.B, n_obs = h->cur_nobs;
+    const int n_cnt = P.max_iter + 3;
+    double *hdr = h->bws.as<double>(), *rec = hdr + (size_t)B * kHdrD;
+    int *list0 = reinterpret_cast<int *>(rec + (size_t)B * (N + 1) * kStepD), *list1 = list0 + B, *cnt = list1 + B;
+    const double *ocv = h->obs_b.as<double>(), *oib2 = ocv ? ocv + (size_t)B * n_obs * CV_FIELDS : nullptr, *orec = h->obs.as<double>();
+    const size_t trace_per_chunk = (size_t)n_cnt * kTraceKinds * 2;
+    if (h->trace_on) CILQR_CUDA(cudaMemsetAsync(h->trace.p, 0xff, (size_t)kMaxChunks * trace_per_chunk * sizeof(unsigned long long), st));
+    cudaStream_t cs[kMaxChunks];
+    if (K == 1) {
+        cs[0] = st;
+    } else {
+        CILQR_CUDA(cudaEventRecord(h->ev_fork, st));
+        for (int c = 0; c < K; ++c) {
+            cs[c] = h->chunk_stream[c];
+            CILQR_CUDA(cudaStreamWaitEvent(cs[c], h->ev_fork, 0));
+        }
+    }
+    // 1/b^2 staged through shared memory while two CTAs per SM still fit (n_obs <= 55), else read directly
+    const bool staged = h->obs_cv && n_obs > 0 && h->deriv_staged && 2 * (deriv_stage_bytes(n_obs) + 1024) <= (size_t)h->smem_per_sm;
+    // persistent grids sized once per chunk; later rounds find shorter lists and leave early
+    const int E = cost_entries_per_cta(N);
+    const size_t cost_smem = (size_t)E * N * sizeof(double);
+    // Chunk after chunk in issue order, earlier chunks on higher-priority streams: chunk c runs ahead of chunk c+1, so its
+    // short latency-bound late rounds run under the next chunk's full early rounds, and with host buffers its results travel
+    // back while the later chunks are still iterating.
+    for (int c = 0; c < K; ++c) {
+        const int o = c * Bc, b = std::min(Bc, B - o);
+        BatchView v;
+        v.N = N;
+        v.hdr = hdr + (size_t)o * kHdrD;
+        v.rec = rec + (size_t)o * (N + 1) * kStepD;
+        v.list0 = list0 + o;
+        v.list1 = list1 + o;
+        v.cnt = cnt + (size_t)c * n_cnt;
+        v.n_obs = n_obs;
+        v.cv = h->obs_cv;
+        v.ocv = ocv ? ocv + (size_t)o * n_obs * CV_FIELDS : nullptr;
+        v.oib2 = oib2 ? oib2 + (size_t)o * n_obs * N : nullptr;
+        v.orec = orec ? orec + (size_t)o * n_obs * OB_FIELDS * N : nullptr;
+        v.trace = h->trace_on ? h->trace.as<unsigned long long>() + (size_t)c * trace_per_chunk : nullptr;
+        const size_t so = (size_t)o, sb = (size_t)b;
+        if (io) { // this chunk's inputs: host -> staging
+            CILQR_CUDA(cudaMemcpyAsync(const_cast<double *>(A.x0) + 4 * so, io->x0 + 4 * so, sb * 4 * sizeof(double), cudaMemcpyHostToDevice, cs[c]));
+            CILQR_CUDA(cudaMemcpyAsync(A.U + 2 * N * so, io->U_in + 2 * N * so, sb * 2 * N * sizeof(double), cudaMemcpyHostToDevice, cs[c]));
+            CILQR_CUDA(cudaMemcpyAsync(const_cast<double *>(A.poly) + P.npoly * so, io->poly + P.npoly * so, sb * P.npoly * sizeof(double), cudaMemcpyHostToDevice, cs[c]));
+            CILQR_CUDA(cudaMemcpyAsync(const_cast<double *>(A.xlp) + 2 * so, io->xlp + 2 * so, sb * 2 * sizeof(double), cudaMemcpyHostToDevice, cs[c]));
+        }
+        CILQR_CUDA(cudaMemsetAsync(v.cnt, 0, (size_t)n_cnt * sizeof(int), cs[c]));
+        batch_init_kernel<<<(b + 127) / 128, 128, 0, cs[c]>>>(P, v, b, A.x0 + 4 * so, A.U + 2 * N * so, A.poly + P.npoly * so, A.xlp + 2 * so);
+        CILQR_LAUNCH_CHECK();
+        const int cost_grid = std::min((b + E - 1) / E, h->num_sms * h->occ_cost);
+        const long long items = (long long)b * N;
+        const int deriv_grid = (int)std::min<long long>((items + kDerivThreads - 1) / kDerivThreads, (long long)h->num_sms * h->occ_deriv);
+        const int sweep_grid = std::min((b + kSweepThreads - 1) / kSweepThreads, h->num_sms * h->occ_sweep);
+        for (int r = 0; r <= P.max_iter; ++r) {
+            batch_cost_kernel<<<cost_grid, kCostThreads, cost_smem, cs[c]>>>(P, v, r);
+            CILQR_LAUNCH_CHECK();
+            if (r == P.max_iter) break; // the last round only evaluates J of the scenarios that ran out of iterations
+            if (v.cv && staged)
+                batch_derivs_kernel<true, true><<<deriv_grid, kDerivThreads, deriv_stage_bytes(n_obs), cs[c]>>>(P, v, r);
+            else if (v.cv)
+                batch_derivs_kernel<true><<<deriv_grid, kDerivThreads, 0, cs[c]>>>(P, v, r);
+            else
+                batch_derivs_kernel<false><<<deriv_grid, kDerivThreads, 0, cs[c]>>>(P, v, r);
+            CILQR_LAUNCH_CHECK();
+            batch_sweep_kernel<<<sweep_grid, kSweepThreads, 0, cs[c]>>>(P, v, r);
+            CILQR_LAUNCH_CHECK();
+        }
+        const size_t out_items = sb * (N + 1);
+        batch_output_kernel<<<(int)std::min<size_t>((out_items + 255) / 256, (size_t)h->num_sms * 8), 256, 0, cs[c]>>>(
+            P, v, b, A.U + 2 * N * so, A.X ? A.X + 4 * (N + 1) * so : nullptr, A.J ? A.J + so : nullptr, A.iters ? A.iters + so : nullptr,
+            A.status ? A.status + so : nullptr);
+        CILQR_LAUNCH_CHECK();
+        if (io) { // this chunk's results: staging -> host
+            CILQR_CUDA(cudaMemcpyAsync(io->U + 2 * N * so, A.U + 2 * N * so, sb * 2 * N * sizeof(double), cudaMemcpyDeviceToHost, cs[c]));
+            if (io->X) CILQR_CUDA(cudaMemcpyAsync(io->X + 4 * (N + 1) * so, A.X + 4 * (N + 1) * so, sb * 4 * (N + 1) * sizeof(double), cudaMemcpyDeviceToHost, cs[c]));
+            if (io->J) CILQR_CUDA(cudaMemcpyAsync(io->J + so, A.J + so, sb * sizeof(double), cudaMemcpyDeviceToHost, cs[c]));
+            if (io->iters) CILQR_CUDA(cudaMemcpyAsync(io->iters + so, A.iters + so, sb * sizeof(int32_t), cudaMemcpyDeviceToHost, cs[c]));
+            if (io->status) CILQR_CUDA(cudaMemcpyAsync(io->status + so, A.status + so, sb * sizeof(int32_t), cudaMemcpyDeviceToHost, cs[c]));
+        }
+        if (K > 1) {
+            CILQR_CUDA(cudaEventRecord(h->ev_join[c], cs[c]));
+            CILQR_CUDA(cudaStreamWaitEvent(st, h->ev_join[c], 0));
+        }
+    }
+    return 0;
+}
+
+static bool pinned_or_null(const void *p)
+{
+    if (!p) return true;
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, p) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    return at.type == cudaMemoryTypeHost;
+}
+
+static void drop_graph(cilqr_handle h)
+{
+    if (h->graph_exec) cudaGraphExecDestroy(h->graph_exec);
+    h->graph_exec = nullptr;
+    h->graph_key.clear();
+}
+
+// One solve = ~60 launches per chunk, most of them a few microseconds long: issued one by one the host's launch rate
+// (~2.5 us per launch) would bound the step as soon as there is more than one chunk.  A call that repeats the previous call's
+// arguments (same buffers, sizes and obstacle form — the receding-horizon loop, the benchmark) records the whole multi-stream
+// sequence once as a CUDA graph and replays it with a single launch afterwards; anything else is issued directly.
+static int solve_rounds(cilqr_handle h, const SolveArgs &A, const HostIO *io, cudaStream_t st)
 {
     const DevParams &P = h->dp;
     const int N = P.N, B = A.B;
     const int n_cnt = P.max_iter + 3;
+    // chunks pay off when there are transfers to hide; on device buffers the rounds of one chunk already fill the GPU
+    int K = io ? (B >= 16384 ? 4 : (B >= 2048 ? 2 : 1)) : 1;
+    if (h->force_chunks > 0) K = std::min(h->force_chunks, kMaxChunks);
+    const int Bc = ((B + K - 1) / K + 31) / 32 * 32; // chunk size, a multiple of the warp size
+    K = (B + Bc - 1) / Bc;
     const size_t n_dbl = (size_t)B * kHdrD + (size_t)B * (N + 1) * kStepD;
-    if (int rc = h->bws.reserve(n_dbl * sizeof(double) + ((size_t)2 * B + n_cnt) * sizeof(int))) return rc;
-    BatchView V;
-    V.N = N;
-    V.hdr = h->bws.as<double>();
-    V.rec = V.hdr + (size_t)B * kHdrD;
-    V.list0 = reinterpret_cast<int *>(V.rec + (size_t)B * (N + 1) * kStepD);
-    V.list1 = V.list0 + B;
-    V.cnt = V.list1 + B;
-    V.n_obs = h->cur_nobs;
-    V.cv = h->obs_cv;
-    V.ocv = h->obs_b.as<double>();
-    V.oib2 = V.ocv ? V.ocv + (size_t)B * h->cur_nobs * CV_FIELDS : nullptr;
-    V.orec = h->obs.as<double>();
+    if (int rc = h->bws.reserve(n_dbl * sizeof(double) + ((size_t)2 * B + (size_t)kMaxChunks * n_cnt) * sizeof(int))) return rc;
+    if (h->trace_on)
+        if (int rc = h->trace.reserve((size_t)kMaxChunks * n_cnt * kTraceKinds * 2 * sizeof(unsigned long long))) return rc;
+    h->last_cnt = reinterpret_cast<int *>(h->bws.as<double>() + n_dbl) + 2 * (size_t)B;
+    h->last_chunks = K;
 
-    CILQR_CUDA(cudaMemsetAsync(V.cnt, 0, (size_t)n_cnt * sizeof(int), st));
-    h->last_cnt = V.cnt;
-    batch_init_kernel<<<(B + 127) / 128, 128, 0, st>>>(P, V, B, A.x0, A.U, A.poly, A.xlp);
-    CILQR_LAUNCH_CHECK();
-
-    // persistent grids sized once for the full batch; later rounds find shorter lists and leave early
-    const int E = cost_entries_per_cta(N);
-    const size_t cost_smem = (size_t)E * N * sizeof(double);
-    const int cost_grid = std::min((B + E - 1) / E, h->num_sms * h->occ_cost);
-    const long long items = (long long)B * N;
-    const int deriv_grid = (int)std::min<long long>((items + kDerivThreads - 1) / kDerivThreads, (long long)h->num_sms * h->occ_deriv);
-    const int sweep_grid = std::min((B + kSweepThreads - 1) / kSweepThreads, h->num_sms * h->occ_sweep);
-    for (int r = 0; r <= P.max_iter; ++r) {
-        batch_cost_kernel<<<cost_grid, kCostThreads, cost_smem, st>>>(P, V, r);
-        CILQR_LAUNCH_CHECK();
-        if (r == P.max_iter) break; // the last round only evaluates J of the scenarios that ran out of iterations
-        if (V.cv)
-            batch_derivs_kernel<true><<<deriv_grid, kDerivThreads, 0, st>>>(P, V, r);
-        else
-            batch_derivs_kernel<false><<<deriv_grid, kDerivThreads, 0, st>>>(P, V, r);
-        CILQR_LAUNCH_CHECK();
-        batch_sweep_kernel<<<sweep_grid, kSweepThreads, 0, st>>>(P, V, r);
-        CILQR_LAUNCH_CHECK();
+    std::vector<uintptr_t> key = {(uintptr_t)B, (uintptr_t)h->cur_nobs, (uintptr_t)h->obs_cv, (uintptr_t)K, (uintptr_t)h->bws.p, (uintptr_t)h->obs_b.p,
+                                  (uintptr_t)h->obs.p, (uintptr_t)h->trace.p, (uintptr_t)A.x0, (uintptr_t)A.U, (uintptr_t)A.poly, (uintptr_t)A.xlp, (uintptr_t)A.X,
+                                  (uintptr_t)A.J, (uintptr_t)A.iters, (uintptr_t)A.status};
+    if (io)
+        for (const void *q : {(const void *)io->x0, (const void *)io->U, (const void *)io->poly, (const void *)io->xlp, (const void *)io->X,
+                              (const void *)io->J, (const void *)io->iters, (const void *)io->status})
+            key.push_back((uintptr_t)q);
+    if (h->graph_exec && key == h->graph_key) {
+        CILQR_CUDA(cudaGraphLaunch(h->graph_exec, st));
+        g_launches.fetch_add(h->graph_kernels, std::memory_order_relaxed);
+        return 0;
     }
-    const size_t out_items = (size_t)B * (N + 1);
-    batch_output_kernel<<<(int)std::min<size_t>((out_items + 255) / 256, (size_t)h->num_sms * 8), 256, 0, st>>>(P, V, B, A.U, A.X, A.J, A.iters, A.status);
-    CILQR_LAUNCH_CHECK();
+    bool record = h->use_graph && key == h->seen_key; // second call in a row with these arguments
+    h->seen_key = key;
+    if (record && io)
+        record = pinned_or_null(io->x0) && pinned_or_null(io->U) && pinned_or_null(io->poly) && pinned_or_null(io->xlp) && pinned_or_null(io->X) &&
+                 pinned_or_null(io->J) && pinned_or_null(io->iters) && pinned_or_null(io->status); // pageable copies are not recorded
+    if (!record) return issue_rounds(h, A, io, st, K, Bc);
+
+    drop_graph(h);
+    const long long before = g_launches.load(std::memory_order_relaxed);
+    CILQR_CUDA(cudaStreamBeginCapture(h->cap_stream, cudaStreamCaptureModeRelaxed));
+    const int rc = issue_rounds(h, A, io, h->cap_stream, K, Bc);
+    cudaGraph_t g = nullptr;
+    const cudaError_t e = cudaStreamEndCapture(h->cap_stream, &g);
+    const long long recorded = g_launches.load(std::memory_order_relaxed) - before;
+    g_launches.fetch_sub(recorded, std::memory_order_relaxed); // nothing has run yet
+    if (rc != 0 || e != cudaSuccess || !g) {
+        if (g) cudaGraphDestroy(g);
+        cudaGetLastError();
+        h->use_graph = false; // do not try again on this handle
+        if (rc != 0) return rc;
+        return issue_rounds(h, A, io, st, K, Bc);
+    }
+    const cudaError_t ei = cudaGraphInstantiate(&h->graph_exec, g, 0);
+    cudaGraphDestroy(g);
+    if (ei != cudaSuccess) {
+        cudaGetLastError();
+        h->graph_exec = nullptr;
+        h->use_graph = false;
+        return issue_rounds(h, A, io, st, K, Bc);
+    }
+    h->graph_key = key;
+    h->graph_kernels = recorded;
+    CILQR_CUDA(cudaGraphLaunch(h->graph_exec, st));
+    g_launches.fetch_add(h->graph_kernels, std::memory_order_relaxed);
+    return 0;
+}
+
+int cilqr_solve_trace(cilqr_handle h, uint64_t *out, int capacity, int32_t *chunks, int32_t *rounds, void *stream)
+{
+    if (!h || !out) return fail(CILQR_E_ARG, "null argument");
+    if (!h->trace_on || !h->trace.p || !h->last_cnt) return fail(CILQR_E_STATE, "no traced solve on this handle (create it with CILQR_TRACE=1 in the environment)");
+    const int n_cnt = h->dp.max_iter + 3, K = h->last_chunks;
+    const size_t n = (size_t)K * n_cnt * kTraceKinds * 2;
+    if ((size_t)capacity < n) return fail(CILQR_E_ARG, "trace needs %zu entries, the buffer has %d", n, capacity);
+    CILQR_CUDA(cudaMemcpyAsync(out, h->trace.p, n * sizeof(uint64_t), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    CILQR_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+    for (size_t i = 0; i < n; i += 2) {
+        if (out[i] == ~0ull) out[i] = out[i + 1] = 0; // launch not recorded
+        else out[i + 1] = ~out[i + 1];
+    }
+    if (chunks) *chunks = K;
+    if (rounds) *rounds = n_cnt;
     return 0;
 }
 
@@ -651,17 +860,18 @@ int cilqr_solve_stats(cilqr_handle h, int64_t *cost_passes, int64_t *deriv_passe
 {
     if (!h) return fail(CILQR_E_ARG, "null handle");
     if (!h->last_cnt) return fail(CILQR_E_STATE, "no batch-synchronous solve has run on this handle");
-    const int n = h->dp.max_iter + 2;
-    std::vector<int> c(n);
-    CILQR_CUDA(cudaMemcpyAsync(c.data(), h->last_cnt, n * sizeof(int), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    const int n_cnt = h->dp.max_iter + 3, K = h->last_chunks;
+    std::vector<int> c((size_t)n_cnt * K);
+    CILQR_CUDA(cudaMemcpyAsync(c.data(), h->last_cnt, c.size() * sizeof(int), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
     CILQR_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
     int64_t cp = 0, dp = 0;
     int r = 0;
-    for (int i = 0; i <= h->dp.max_iter; ++i) {
-        cp += c[i];
-        dp += c[i + 1];
-        if (c[i] > 0) r = i + 1;
-    }
+    for (int k = 0; k < K; ++k)
+        for (int i = 0; i <= h->dp.max_iter; ++i) {
+            cp += c[(size_t)k * n_cnt + i];
+            dp += c[(size_t)k * n_cnt + i + 1];
+            if (c[(size_t)k * n_cnt + i] > 0) r = std::max(r, i + 1);
+        }
     if (cost_passes) *cost_passes = cp;
     if (deriv_passes) *deriv_passes = dp;
     if (rounds) *rounds = r;
@@ -686,6 +896,32 @@ int cilqr_solve_batch(cilqr_handle h, int B, const double *x0, double *U, const 
     A.n_alphas = n_alphas;
     A.merit = merit;
     A.obs = nullptr;
+    if (n_alphas == 1 && h->variant == 3) {
+        if (mem == CILQR_MEM_DEVICE) {
+            A.x0 = x0; A.U = U; A.poly = poly; A.xlp = xlp;
+            A.X = X; A.J = J; A.iters = iters; A.status = status;
+            return solve_rounds(h, A, nullptr, st);
+        }
+        // host buffers: staging only — solve_rounds moves each chunk's slice on the chunk's own stream
+        HostIO io;
+        io.x0 = x0; io.U_in = U; io.poly = poly; io.xlp = xlp;
+        io.U = U; io.X = X; io.J = J; io.iters = iters; io.status = status;
+        double *d;
+        if (int rc = stage_out(h, 3, const_cast<double *>(x0), (size_t)B * 4, mem, &d)) return rc;
+        A.x0 = d;
+        if (int rc = stage_out(h, 4, U, (size_t)B * 2 * N, mem, &A.U)) return rc;
+        if (int rc = stage_out(h, 5, const_cast<double *>(poly), (size_t)B * h->dp.npoly, mem, &d)) return rc;
+        A.poly = d;
+        if (int rc = stage_out(h, 6, const_cast<double *>(xlp), (size_t)B * 2, mem, &d)) return rc;
+        A.xlp = d;
+        if (int rc = stage_out(h, 7, X, (size_t)B * 4 * (N + 1), mem, &A.X)) return rc;
+        if (int rc = stage_out(h, 8, J, (size_t)B, mem, &A.J)) return rc;
+        if (int rc = stage_out(h, 9, iters, (size_t)B, mem, &A.iters)) return rc;
+        if (int rc = stage_out(h, 10, status, (size_t)B, mem, &A.status)) return rc;
+        if (int rc = solve_rounds(h, A, &io, st)) return rc;
+        CILQR_CUDA(cudaStreamSynchronize(st));
+        return 0;
+    }
     const double *dU_in;
     if (int rc = stage_in(h, 3, x0, (size_t)B * 4, mem, st, &A.x0)) return rc;
     if (int rc = stage_in(h, 4, (const double *)U, (size_t)B * 2 * N, mem, st, &dU_in)) return rc;
@@ -698,16 +934,6 @@ int cilqr_solve_batch(cilqr_handle h, int B, const double *x0, double *U, const 
     if (int rc = stage_out(h, 10, status, (size_t)B, mem, &A.status)) return rc;
     A.counter = h->counter.as<int>();
 
-    if (n_alphas == 1 && h->variant == 3) {
-        if (int rc = solve_rounds(h, A, st)) return rc;
-        if (int rc = fetch_out(U, A.U, (size_t)B * 2 * N, mem, st)) return rc;
-        if (int rc = fetch_out(X, A.X, (size_t)B * 4 * (N + 1), mem, st)) return rc;
-        if (int rc = fetch_out(J, A.J, (size_t)B, mem, st)) return rc;
-        if (int rc = fetch_out(iters, A.iters, (size_t)B, mem, st)) return rc;
-        if (int rc = fetch_out(status, A.status, (size_t)B, mem, st)) return rc;
-        if (mem == CILQR_MEM_HOST) CILQR_CUDA(cudaStreamSynchronize(st));
-        return 0;
-    }
     if (h->cur_nobs > 0) {
         if (int rc = ensure_records(h, st)) return rc;
         A.obs = h->obs.as<double>();

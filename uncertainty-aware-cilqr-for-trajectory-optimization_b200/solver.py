@@ -328,6 +328,26 @@ class iLQR:
         _check(self.lib.cilqr_solve_stats(self._h, C.byref(cp), C.byref(dp), C.byref(r), st))
         return int(cp.value), int(dp.value), int(r.value)
 
+    def solve_trace(self):
+        """Timeline of the last solve (handle created with CILQR_TRACE=1): list of (chunk, round, kind, start_ns, end_ns),
+        times relative to the first start, sorted by start; kind in ("cost", "derivs", "sweep", "init", "output")."""
+        n_cnt = self.params.max_iterations + 3
+        kinds = 4
+        buf = (C.c_uint64 * (8 * n_cnt * kinds * 2))()
+        k, r = C.c_int32(0), C.c_int32(0)
+        _check(self.lib.cilqr_solve_trace(self._h, buf, C.c_int(len(buf)), C.byref(k), C.byref(r), C.c_void_p(0)))
+        a = np.frombuffer(buf, dtype=np.uint64)[:k.value * r.value * kinds * 2].reshape(k.value, r.value, kinds, 2)
+        t0 = int(a[..., 0][a[..., 0] > 0].min())
+        names = ("cost", "derivs", "sweep", "io")
+        out = []
+        for c in range(k.value):
+            for rd in range(r.value):
+                for kind in range(kinds):
+                    if a[c, rd, kind, 0]:
+                        name = names[kind] if kind < 3 else ("init" if rd == 0 else "output")
+                        out.append((c, rd, name, int(a[c, rd, kind, 0]) - t0, int(a[c, rd, kind, 1]) - t0))
+        return sorted(out, key=lambda e: e[3])
+
     # ------------------------------------------------------------------ run_step (iLQR.cpp:247-255)
     def set_global_plan(self, global_plan):
         """global_plan: [n, 2] waypoints (== the reference's column-major 2 x n matrix)."""
