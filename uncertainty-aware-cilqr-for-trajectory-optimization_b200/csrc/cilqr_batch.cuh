@@ -30,7 +30,9 @@ enum { MODE_ITERATE = 0, MODE_FINAL = 1, MODE_DONE = 2 };
 
 // Step record of (scenario, t), t = 0..N: state column t, cos/sin of its heading, control column t, and the derivative
 // record of step t (overwritten by the gains in the sweep).  16-byte aligned pairs -> 128-bit loads.
-enum { S_X = 0, S_Y, S_V, S_TH, S_C, S_S, S_U0, S_U1, S_R, kStepD = S_R + kRec };
+// kStepD may be padded beyond kStepUsed: tried 160-byte records (every write group on whole 32-byte sectors) — the derivative
+// kernel lost 45 % to it (826 vs 562 us in round 0), so records stay packed at 144 bytes.
+enum { S_X = 0, S_Y, S_V, S_TH, S_C, S_S, S_U0, S_U1, S_R, kStepUsed = S_R + kRec, kStepD = kStepUsed };
 // Scenario header.
 enum { H_XF = 0, H_DXS, H_POLY, H_LAMB = H_POLY + kMaxPoly, H_JOLD, H_JNEW, H_JRES, H_ITERS_MODE, H_CONV_STATUS, H_LIP, H_PAD, kHdrD };
 static_assert(kStepD % 2 == 0 && kHdrD % 2 == 0, "records are accessed with 128-bit loads");
@@ -201,61 +203,123 @@ __global__ void __launch_bounds__(256) expand_cv_records_kernel(DevParams P, siz
 
 // ------------------------------------------------------------------------------------------------- round 0 set-up
 // X = get_nominal_trajectory(x_0, U) (iLQR.cpp:203, :51-62), J_old = DBL_MAX, lamb = 1 (iLQR.cpp:205-209), work list = all.
-__global__ void __launch_bounds__(128) batch_init_kernel(DevParams P, BatchView V, int B, const double *__restrict__ x0, const double *__restrict__ U,
-                                                         const double *__restrict__ poly, const double *__restrict__ xlp)
+//
+// One scenario per lane (the rollout is a sincos chain), but memory is moved by the warp: a lane writing its own 64 bytes of a
+// step record is 32 cache lines per store instruction, and the first version of this kernel spent 320 us on that.  Headers and
+// step records are staged in shared memory and written in 16-byte pieces, consecutive lanes -> consecutive bytes (the 32
+// headers of a warp are one contiguous 4.6 KB block); the controls are read as 128-byte row segments, kInitTile steps at a time.
+constexpr int kInitThreads = 128;
+constexpr int kInitTile = 8; // timesteps of U per shared-memory tile
+struct InitSmem {
+    double u[32][kHdrD];     // header rows first, then tiles of U: 2 * kInitTile controls per row (144-byte rows: conflict-free)
+    double out[2][32][10];   // (x, y, v, theta, cos, sin, u0, u1) of one step, double-buffered, 80-byte rows
+};
+static_assert(kHdrD >= 2 * kInitTile && kHdrD % 2 == 0, "the header rows double as U tiles");
+
+__global__ void __launch_bounds__(kInitThreads) batch_init_kernel(DevParams P, BatchView V, int B, const double *__restrict__ x0,
+                                                                  const double *__restrict__ U, const double *__restrict__ poly,
+                                                                  const double *__restrict__ xlp)
 {
     TraceScope trace_scope(V, TRACE_IO, 0);
-    const int N = P.N;
-    const int b = blockIdx.x * blockDim.x + threadIdx.x;
-    if (b == 0)
-        V.cnt[0] = B;
-    if (b >= B)
+    __shared__ __align__(16) InitSmem smw[kInitThreads / 32];
+    InitSmem &sm = smw[threadIdx.x >> 5];
+    const int N = P.N, lane = threadIdx.x & 31;
+    const int b0 = (blockIdx.x * (kInitThreads / 32) + (threadIdx.x >> 5)) * 32;
+    if (b0 >= B)
         return;
-    double *h = V.header(b);
-    const double xf = xlp[2 * (size_t)b];
-    h[H_XF] = xf;
-    h[H_DXS] = (xlp[2 * (size_t)b + 1] - xf) / P.S; // Constraints.cpp:32
-#pragma unroll
-    for (int k = 0; k < kMaxPoly; ++k)
-        h[H_POLY + k] = k < P.npoly ? poly[(size_t)b * P.npoly + k] : 0.0;
+    const int nact = min(32, B - b0);
+    const int b = b0 + (lane < nact ? lane : 0);
+    if (b0 == 0 && lane == 0)
+        V.cnt[0] = B;
+    // ---- header
     {
+        double *h = sm.u[lane];
+        const double xf = xlp[2 * (size_t)b];
+        h[H_XF] = xf;
+        h[H_DXS] = (xlp[2 * (size_t)b + 1] - xf) / P.S; // Constraints.cpp:32
         PolyY yf;
         yf.pl.x_first = xf;
         yf.pl.dxs = h[H_DXS];
         yf.npoly = P.npoly;
 #pragma unroll
-        for (int k = 0; k < kMaxPoly; ++k)
-            yf.c[k] = h[H_POLY + k];
+        for (int k = 0; k < kMaxPoly; ++k) {
+            yf.c[k] = k < P.npoly ? poly[(size_t)b * P.npoly + k] : 0.0;
+            h[H_POLY + k] = yf.c[k];
+        }
         h[H_LIP] = polyline_lipschitz(P, yf);
         h[H_PAD] = 0.0;
+        h[H_LAMB] = 1.0;
+        h[H_JOLD] = DBL_MAX;
+        h[H_JNEW] = 0.0;
+        h[H_JRES] = 0.0;
+        hdr_ints(h, H_ITERS_MODE) = make_int2(0, MODE_ITERATE);
+        hdr_ints(h, H_CONV_STATUS) = make_int2(0, CILQR_ST_MAX_ITER);
+        __syncwarp();
+        const double2 *src = reinterpret_cast<const double2 *>(&sm.u[0][0]);
+        double2 *dst = reinterpret_cast<double2 *>(V.hdr + (size_t)b0 * kHdrD);
+        for (int p = lane; p < nact * (kHdrD / 2); p += 32)
+            dst[p] = src[p];
     }
-    h[H_LAMB] = 1.0;
-    h[H_JOLD] = DBL_MAX;
-    h[H_JNEW] = 0.0;
-    h[H_JRES] = 0.0;
-    hdr_ints(h, H_ITERS_MODE) = make_int2(0, MODE_ITERATE);
-    hdr_ints(h, H_CONV_STATUS) = make_int2(0, CILQR_ST_MAX_ITER);
-    V.list0[b] = b;
+    if (lane < nact)
+        V.list0[b] = b;
+    // ---- rollout
     double n0 = x0[4 * (size_t)b], n1 = x0[4 * (size_t)b + 1], n2 = x0[4 * (size_t)b + 2], n3 = x0[4 * (size_t)b + 3];
     double c, s;
     sincos(n3, &s, &c);
-    const double *Ub = U + (size_t)b * 2 * N;
-    double *r = V.step(b, 0);
-    for (int t = 0; t < N; ++t, r += kStepD) {
-        const double2 u = make_double2(Ub[2 * t], Ub[2 * t + 1]); // caller memory: no alignment assumed
-        st2(r + S_X, n0, n1);
-        st2(r + S_V, n2, n3);
-        st2(r + S_C, c, s);
-        st2(r + S_U0, u.x, u.y);
-        double m0, m1, m2, m3;
-        dyn_step(P, n0, n1, n2, n3, c, s, u.x, u.y, m0, m1, m2, m3);
-        sincos(m3, &s, &c);
-        n0 = m0; n1 = m1; n2 = m2; n3 = m3;
+    double2 *rec16 = reinterpret_cast<double2 *>(V.rec);
+    const size_t stride16 = (size_t)(N + 1) * (kStepD / 2);
+    // Whole records are written, derivative fields zeroed: a record is 4.5 sectors, and sectors left partly written would make
+    // the memory system merge them with their old contents on eviction.  Piece p = k * 32 + lane of a step: scenario p / 9,
+    // piece p % 9 — (x, y), (v, theta), (cos, sin), (u0, u1) from the staging row, zeros for the rest.
+    constexpr int kPiecesPerRec = kStepD / 2;
+    size_t st_off[kPiecesPerRec];
+    int st_src[kPiecesPerRec]; // staging piece to copy, -1: zeros, -2: nothing (inactive lane)
+#pragma unroll
+    for (int k = 0; k < kPiecesPerRec; ++k) {
+        const int p = k * 32 + lane, src = p / kPiecesPerRec, f = p - src * kPiecesPerRec;
+        st_off[k] = (size_t)(b0 + src) * stride16 + f;
+        st_src[k] = src >= nact ? -2 : (f < 4 ? src * 5 + f : -1);
     }
-    st2(r + S_X, n0, n1);
-    st2(r + S_V, n2, n3);
-    st2(r + S_C, c, s);
-    st2(r + S_U0, 0.0, 0.0);
+    auto flush = [&](int t) { // staged step t -> records t
+        const double2 *o = reinterpret_cast<const double2 *>(&sm.out[t & 1][0][0]);
+#pragma unroll
+        for (int k = 0; k < kPiecesPerRec; ++k)
+            if (st_src[k] != -2)
+                rec16[st_off[k] + (size_t)t * kPiecesPerRec] = st_src[k] >= 0 ? o[st_src[k]] : make_double2(0.0, 0.0);
+    };
+    for (int t0 = 0; t0 < N; t0 += kInitTile) {
+        const int nt = min(kInitTile, N - t0);
+        __syncwarp(); // the previous tile (or the header rows) has been read
+        // controls t0 .. t0 + nt - 1 of every scenario: half a warp per row segment
+        for (int r = lane >> 4; r < nact; r += 2) {
+            const int col = lane & 15;
+            if (col < 2 * nt)
+                sm.u[r][col] = U[(size_t)(b0 + r) * 2 * N + 2 * t0 + col]; // caller memory: no alignment assumed
+        }
+        __syncwarp();
+        for (int k = 0; k < nt; ++k) {
+            const int t = t0 + k;
+            const double2 u = *reinterpret_cast<const double2 *>(&sm.u[lane][2 * k]);
+            double *o = &sm.out[t & 1][lane][0];
+            *reinterpret_cast<double2 *>(o + 0) = make_double2(n0, n1);
+            *reinterpret_cast<double2 *>(o + 2) = make_double2(n2, n3);
+            *reinterpret_cast<double2 *>(o + 4) = make_double2(c, s);
+            *reinterpret_cast<double2 *>(o + 6) = u;
+            __syncwarp();
+            flush(t);
+            double m0, m1, m2, m3;
+            dyn_step(P, n0, n1, n2, n3, c, s, u.x, u.y, m0, m1, m2, m3);
+            sincos(m3, &s, &c);
+            n0 = m0; n1 = m1; n2 = m2; n3 = m3;
+        }
+    }
+    double *o = &sm.out[N & 1][lane][0];
+    *reinterpret_cast<double2 *>(o + 0) = make_double2(n0, n1);
+    *reinterpret_cast<double2 *>(o + 2) = make_double2(n2, n3);
+    *reinterpret_cast<double2 *>(o + 4) = make_double2(c, s);
+    *reinterpret_cast<double2 *>(o + 6) = make_double2(0.0, 0.0);
+    __syncwarp();
+    flush(N);
 }
 
 // Results back in the caller's layouts: U [B][2N] (in/out), X [B][4(N+1)], J, iterations, status.
@@ -328,7 +392,7 @@ __global__ void __launch_bounds__(kCostThreads) batch_cost_kernel(DevParams P, B
             const double ex = xy.x - cx, ey = xy.y - cy, ev = v - P.v_des;
             sJ[idx] = tracking_cost(P, ex, ey, ev, u.x, u.y);
             st2(r + S_R, 2.0 * P.w_pos * ex, 2.0 * P.w_pos * ey);
-            r[S_R + 2] = 2.0 * P.w_vel * ev;
+            st2(r + S_R + 2, 2.0 * P.w_vel * ev, 0.0); // (R3 is rewritten by the derivative kernel; the sector is written whole)
         }
         __syncthreads();
         // ---- per scenario: J in the reference's summation order, then iLQR.cpp:217-239
@@ -517,9 +581,9 @@ __global__ void __launch_bounds__(kDerivThreads, 2) batch_derivs_kernel(DevParam
         }
         double lu0, lu1, luu0, luu1, bc;
         control_terms<true>(P, vv, uu.x, uu.y, lu0, lu1, luu0, luu1, bc);
-        const double2 tr = ld2(r + S_R); // tracking part written by batch_cost_kernel
+        const double2 tr = ld2(r + S_R), tr2 = ld2(r + S_R + 2); // tracking part written by batch_cost_kernel
         st2(r + S_R, tr.x + P.w_obs * g0, tr.y + P.w_obs * g1);
-        r[S_R + 3] = 2.0 * P.w_pos + P.w_obs * h00;
+        st2(r + S_R + 2, tr2.x, 2.0 * P.w_pos + P.w_obs * h00); // every sector is written whole
         st2(r + S_R + 4, P.w_obs * h01, 2.0 * P.w_pos + P.w_obs * h11);
         st2(r + S_R + 6, lu0, lu1);
         st2(r + S_R + 8, luu0, luu1);
@@ -550,12 +614,13 @@ __device__ __forceinline__ void prefetch_step(const double *r)
 // is the HBM rate for this traffic.
 constexpr int kSweepThreads = 32;
 constexpr int kRing = 3;                       // records in flight per lane
-constexpr int kPieces = kStepD / 2;            // 16-byte pieces per step record
-constexpr int kOutD = 10;                      // doubles per staged result row (80-byte rows: conflict-free)
+constexpr int kPieces = kStepUsed / 2;         // 16-byte pieces of a step record that carry data
+constexpr int kRecPieces = kStepD / 2;         // 16-byte pieces from one record to the next
+constexpr int kOutD = 10;                      // doubles per staged result row (80-byte rows: conflict-free 128-bit accesses)
 static_assert(kOutD >= kRec && kOutD % 2 == 0, "a result row holds the gains of one step");
 
 struct SweepSmem {
-    double ring[kRing][kSweepThreads][kStepD];
+    double ring[kRing][kSweepThreads][kStepUsed];
     double out[2][kSweepThreads][kOutD];
 };
 
@@ -568,8 +633,8 @@ __global__ void __launch_bounds__(kSweepThreads, 11) batch_sweep_kernel(DevParam
     const int *list = V.list(round + 1);
     const int lane = threadIdx.x;
     const uint32_t ring0 = (uint32_t)__cvta_generic_to_shared(&sm.ring[0][0][0]);
-    constexpr uint32_t kSlotBytes = kSweepThreads * kStepD * 8;
-    const size_t stride16 = (size_t)(N + 1) * kPieces; // 16-byte pieces per scenario
+    constexpr uint32_t kSlotBytes = kSweepThreads * kStepUsed * 8;
+    const size_t stride16 = (size_t)(N + 1) * kRecPieces; // 16-byte pieces per scenario
 
     for (int i0 = blockIdx.x * kSweepThreads; i0 < cnt; i0 += gridDim.x * kSweepThreads) {
         const int nact = min(kSweepThreads, cnt - i0);
@@ -591,11 +656,12 @@ __global__ void __launch_bounds__(kSweepThreads, 11) batch_sweep_kernel(DevParam
 #pragma unroll
             for (int k = 0; k < kPieces; ++k)
                 if (ld_on[k])
-                    cp_async16(ring0 + slot * kSlotBytes + (k * kSweepThreads + lane) * 16, rec16 + ld_off[k] + (size_t)t * kPieces);
+                    cp_async16(ring0 + slot * kSlotBytes + (k * kSweepThreads + lane) * 16, rec16 + ld_off[k] + (size_t)t * kRecPieces);
         };
 
         // ---- iLQR::backward_pass (iLQR.cpp:91-195): gains overwrite the derivative records
         constexpr int kGainPieces = kRec / 2;
+        static_assert(kGainPieces * 2 == kOutD, "staged gain rows are dense: piece p of the warp sits at byte 16 p");
         size_t st_off[kGainPieces];
         bool st_on[kGainPieces];
 #pragma unroll
@@ -610,7 +676,7 @@ __global__ void __launch_bounds__(kSweepThreads, 11) batch_sweep_kernel(DevParam
 #pragma unroll
             for (int k = 0; k < kGainPieces; ++k)
                 if (st_on[k])
-                    g16[st_off[k] + (size_t)j * kPieces] = o[k * kSweepThreads + lane];
+                    g16[st_off[k] + (size_t)j * kRecPieces] = o[k * kSweepThreads + lane];
         };
         RiccatiState S;
         RiccatiIn I;
@@ -684,7 +750,7 @@ __global__ void __launch_bounds__(kSweepThreads, 11) batch_sweep_kernel(DevParam
 #pragma unroll
         for (int k = 0; k < kRollPieces; ++k) {
             const int p = k * kSweepThreads + lane, src = p / kRollPieces, f = p - src * kRollPieces;
-            ro_off[k] = (size_t)__shfl_sync(0xffffffffu, b, src) * stride16 + (f == 0 ? S_U0 / 2 : kPieces + f - 1);
+            ro_off[k] = (size_t)__shfl_sync(0xffffffffu, b, src) * stride16 + (f == 0 ? S_U0 / 2 : kRecPieces + f - 1);
             ro_on[k] = (roll_mask >> src) & 1u;
         }
         auto flush_roll = [&](int t) {
@@ -693,7 +759,7 @@ __global__ void __launch_bounds__(kSweepThreads, 11) batch_sweep_kernel(DevParam
             for (int k = 0; k < kRollPieces; ++k) {
                 const int p = k * kSweepThreads + lane, src = p / kRollPieces, f = p - src * kRollPieces;
                 if (ro_on[k])
-                    g16[ro_off[k] + (size_t)t * kPieces] = *reinterpret_cast<const double2 *>(&sm.out[t & 1][src][2 * f]);
+                    g16[ro_off[k] + (size_t)t * kRecPieces] = *reinterpret_cast<const double2 *>(&sm.out[t & 1][src][2 * f]);
             }
         };
         slot = 0;

@@ -710,7 +710,7 @@ static int issue_rounds(cilqr_handle h, const SolveArgs &A, const HostIO *io, cu
             CILQR_CUDA(cudaMemcpyAsync(const_cast<double *>(A.xlp) + 2 * so, io->xlp + 2 * so, sb * 2 * sizeof(double), cudaMemcpyHostToDevice, cs[c]));
         }
         CILQR_CUDA(cudaMemsetAsync(v.cnt, 0, (size_t)n_cnt * sizeof(int), cs[c]));
-        batch_init_kernel<<<(b + 127) / 128, 128, 0, cs[c]>>>(P, v, b, A.x0 + 4 * so, A.U + 2 * N * so, A.poly + P.npoly * so, A.xlp + 2 * so);
+        batch_init_kernel<<<(b + kInitThreads - 1) / kInitThreads, kInitThreads, 0, cs[c]>>>(P, v, b, A.x0 + 4 * so, A.U + 2 * N * so, A.poly + P.npoly * so, A.xlp + 2 * so);
         CILQR_LAUNCH_CHECK();
         const int cost_grid = std::min((b + E - 1) / E, h->num_sms * h->occ_cost);
         const long long items = (long long)b * N;
