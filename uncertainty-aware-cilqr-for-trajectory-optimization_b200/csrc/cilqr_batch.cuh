@@ -546,7 +546,7 @@ __global__ void __launch_bounds__(kDerivThreads, 2) batch_derivs_kernel(DevParam
                 double2 n0 = ld2(oc), n1 = ld2(oc + 2), n2 = ld2(oc + 4), n3 = ld2(oc + 6);
                 const double *col = deriv_smem + (size_t)stage * n_obs * kDerivThreads + threadIdx.x;
                 double nib = STAGED ? col[0] : ld_stream(ob, stream_policy), nib2 = STAGED || n_obs < 2 ? 0.0 : ld_stream(ob + N, stream_policy);
-#pragma unroll 1
+#pragma unroll 2
                 for (int j = 0; j < n_obs; ++j) {
                     const double xo = n0.x + n1.x * tt, yo = n0.y + n1.y * tt; // cv_position
                     const double co = n2.x, so = n2.y, ia2 = n3.x, ib2 = nib;
