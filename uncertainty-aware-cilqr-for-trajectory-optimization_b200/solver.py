@@ -100,10 +100,14 @@ class _Arg:
         self.keep.append(arr)
         return arr, C.c_void_p(arr.ctypes.data)
 
-    def stream_ptr(self):
+    def stream_ptr(self, host_stream=None):
+        """torch's current stream for device arrays; for host arrays `host_stream` (an int handle or an object with a
+        .cuda_stream attribute, e.g. torch.cuda.Stream) or the default stream."""
         if self.mem == MEM_DEVICE:
             import torch
             return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+        if host_stream is not None:
+            return C.c_void_p(int(getattr(host_stream, "cuda_stream", host_stream)))
         return C.c_void_p(0)
 
 
@@ -124,8 +128,12 @@ class iLQR:
     Result members keep the reference's names: X_result, U_result (plus J_result, iterations, status);
     `control_seq` is the warm start carried between run_step() calls, un-shifted like the reference's."""
 
-    def __init__(self, params, max_batch=1, max_obs=0):
+    def __init__(self, params, max_batch=1, max_obs=0, stream=None):
+        """`stream`: CUDA stream for calls with host (numpy) arrays — give every handle its own when several host threads
+        drive one GPU, so that one thread's copies and kernels do not queue behind the other's (device arrays always use
+        torch's current stream)."""
         self.lib = load_library()
+        self.stream = stream
         self.params = params.copy()
         self.max_batch, self.max_obs = int(max_batch), int(max_obs)
         self._h = C.c_void_p()
@@ -170,7 +178,7 @@ class iLQR:
         a = _Arg()
         B, n = int(dim.shape[0]), int(dim.shape[1])
         pd, pp = a.inp(dim), a.inp(pos)
-        _check(self.lib.cilqr_set_obstacles(self._h, C.c_int(B), C.c_int(n), pd, pp, C.c_int(a.mem), a.stream_ptr()))
+        _check(self.lib.cilqr_set_obstacles(self._h, C.c_int(B), C.c_int(n), pd, pp, C.c_int(a.mem), a.stream_ptr(self.stream)))
         self.n_obs = n
 
     def set_obstacles_cv(self, state0, LW, sigma, kappa):
@@ -178,7 +186,7 @@ class iLQR:
         a = _Arg()
         B, n = int(state0.shape[0]), int(state0.shape[1])
         ps, pl, pg = a.inp(state0), a.inp(LW), a.inp(sigma)
-        _check(self.lib.cilqr_set_obstacles_cv(self._h, C.c_int(B), C.c_int(n), ps, pl, pg, C.c_double(kappa), C.c_int(a.mem), a.stream_ptr()))
+        _check(self.lib.cilqr_set_obstacles_cv(self._h, C.c_int(B), C.c_int(n), ps, pl, pg, C.c_double(kappa), C.c_int(a.mem), a.stream_ptr(self.stream)))
         self.n_obs = n
 
     def clear_Obstacle(self):
@@ -201,7 +209,7 @@ class iLQR:
         B = self._batch(x_0)
         px, pu = a.inp(x_0), a.inp(U)
         X, pX = a.out((B, 4 * (self.params.horizon + 1)), np.float64, a.mem == MEM_DEVICE, getattr(x_0, "device", None))
-        _check(self.lib.cilqr_rollout(self._h, C.c_int(B), px, pu, pX, C.c_int(a.mem), a.stream_ptr()))
+        _check(self.lib.cilqr_rollout(self._h, C.c_int(B), px, pu, pX, C.c_int(a.mem), a.stream_ptr(self.stream)))
         return X
 
     def get_state_cost(self, X, poly_coeffs, x_local_plan):
@@ -212,7 +220,7 @@ class iLQR:
         dev = a.mem == MEM_DEVICE
         lx, plx = a.out((B, 4 * N), np.float64, dev, getattr(X, "device", None))
         lxx, plxx = a.out((B, 16 * N), np.float64, dev, getattr(X, "device", None))
-        _check(self.lib.cilqr_state_cost(self._h, C.c_int(B), pX, pp, pl, plx, plxx, C.c_int(a.mem), a.stream_ptr()))
+        _check(self.lib.cilqr_state_cost(self._h, C.c_int(B), pX, pp, pl, plx, plxx, C.c_int(a.mem), a.stream_ptr(self.stream)))
         return lx, lxx
 
     def get_control_cost(self, X, U):
@@ -222,7 +230,7 @@ class iLQR:
         dev = a.mem == MEM_DEVICE
         lu, plu = a.out((B, 2 * N), np.float64, dev, getattr(X, "device", None))
         luu, pluu = a.out((B, 4 * N), np.float64, dev, getattr(X, "device", None))
-        _check(self.lib.cilqr_control_cost(self._h, C.c_int(B), pX, pU, plu, pluu, C.c_int(a.mem), a.stream_ptr()))
+        _check(self.lib.cilqr_control_cost(self._h, C.c_int(B), pX, pU, plu, pluu, C.c_int(a.mem), a.stream_ptr(self.stream)))
         return lu, luu
 
     def get_J(self, X, U, poly_coeffs, x_local_plan):
@@ -230,7 +238,7 @@ class iLQR:
         B = self._batch(X)
         pX, pU, pp, pl = a.inp(X), a.inp(U), a.inp(poly_coeffs), a.inp(x_local_plan)
         J, pJ = a.out((B,), np.float64, a.mem == MEM_DEVICE, getattr(X, "device", None))
-        _check(self.lib.cilqr_cost(self._h, C.c_int(B), pX, pU, pp, pl, pJ, C.c_int(a.mem), a.stream_ptr()))
+        _check(self.lib.cilqr_cost(self._h, C.c_int(B), pX, pU, pp, pl, pJ, C.c_int(a.mem), a.stream_ptr(self.stream)))
         return J
 
     def backward_pass(self, X, U, poly_coeffs, x_local_plan, lamb):
@@ -248,7 +256,7 @@ class iLQR:
         k, pk = a.out((B, 2 * N), np.float64, dev, getattr(X, "device", None))
         K, pK = a.out((B, 8 * N), np.float64, dev, getattr(X, "device", None))
         ok, pok = a.out((B,), np.int32, dev, getattr(X, "device", None))
-        _check(self.lib.cilqr_backward(self._h, C.c_int(B), pX, pU, pp, pl, plam, pk, pK, pok, C.c_int(a.mem), a.stream_ptr()))
+        _check(self.lib.cilqr_backward(self._h, C.c_int(B), pX, pU, pp, pl, plam, pk, pK, pok, C.c_int(a.mem), a.stream_ptr(self.stream)))
         self.k, self.K = k, K
         return ok
 
@@ -269,7 +277,7 @@ class iLQR:
             pal = a.inp(alpha)
         Xn, pXn = a.out((B, 4 * (N + 1)), np.float64, dev, getattr(X, "device", None))
         Un, pUn = a.out((B, 2 * N), np.float64, dev, getattr(X, "device", None))
-        _check(self.lib.cilqr_forward(self._h, C.c_int(B), pX, pU, pk, pK, pal, pXn, pUn, C.c_int(a.mem), a.stream_ptr()))
+        _check(self.lib.cilqr_forward(self._h, C.c_int(B), pX, pU, pk, pK, pal, pXn, pUn, C.c_int(a.mem), a.stream_ptr(self.stream)))
         self.X_new, self.U_new = Xn, Un
         return Xn, Un
 
@@ -310,7 +318,7 @@ class iLQR:
         it, pit = result("iters", (B,), np.int32)
         stt, pst = result("status", (B,), np.int32)
         _check(self.lib.cilqr_solve_batch(self._h, C.c_int(B), px, pU, pp, pl, C.c_int(n_alphas), C.c_int(merit), pX, pJ, pit, pst,
-                                          C.c_int(a.mem), a.stream_ptr()))
+                                          C.c_int(a.mem), a.stream_ptr(self.stream)))
         self.X_result, self.U_result, self.J_result, self.iterations, self.status = X, Uarr, J, it, stt
         return Uarr
 
