@@ -24,6 +24,7 @@ Nothing here reads /root/reference.  oracle/ is only executed by the cpu_baselin
 """
 import argparse
 import json
+import math
 import os
 import subprocess
 import sys
@@ -292,6 +293,43 @@ def bench_warp(args, device, hbm_peak, peak_kind):
             "launches": 2 * 2 * ((WARP_POSES + chunk - 1) // chunk)}
 
 
+def bench_propagate(args, device, hbm_peak, peak_kind):
+    """costmap_propagate_uncertainty (rows W2-W4: per-cell covariance -> ellipse -> Gaussian average), the reference's
+    experiment sigmas on BASELINE config 2's 400 x 400 local costmap at 0.2 m.  The work per cell grows with the square of its
+    distance from the map origin (the heading sigma's lever arm sets the ellipse), so the map size is part of the metric; the
+    2.6 MB working set is L2-resident, which is the kernel's operating point in the reference's node as well."""
+    import torch
+    import cilqr_b200
+    from cilqr_b200 import scenarios
+    S = 400
+    g = cilqr_b200.CostmapGeom(S * 0.2, S * 0.2, 0.2, 0.0, 0.0)
+    src = torch.from_numpy(scenarios.make_source_map(S, S, nan_band=False)).to(device)
+    sig = scenarios.SIGMA_EXPERIMENT
+
+    def once():
+        return cilqr_b200.propagate_uncertainty(src, g, math.sin(0.7), math.cos(0.7), *sig)
+
+    for _ in range(2):
+        once()
+    torch.cuda.synchronize()
+    reps = 20
+    e0, e1 = event_pair()
+    e0.record()
+    for _ in range(reps):
+        once()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / reps
+    by = S * S * (4 + 4 + 8)
+    return {"metric": "uncertainty propagation Mcells/s", "value": S * S / ms / 1e3, "unit": "Mcells/s", "ms_per_map": ms,
+            "config": {"workload": "%dx%d map, 0.2 m cells, sigma (x, y, theta) = %s, all cells" % (S, S, tuple(sig)),
+                       "l2": "L2-resident (2.6 MB per map), as in the reference's map node"},
+            "roofline": {"bound": "hbm", "achieved": by / ms / 1e6, "peak": hbm_peak, "unit": "GB/s", "frac": by / ms / 1e6 / hbm_peak, "traffic": None,
+                         "peak_source": peak_kind, "algorithmic_bytes_per_cell": "4 B map read + 4 B count + 8 B value written",
+                         "note": "FP64 / divergence bound: each cell averages the map over its own uncertainty ellipse (a data-dependent number of cells)"},
+            "launches": reps + 2}
+
+
 def run_b200_arm(args):
     import ctypes as C
     import torch
@@ -477,6 +515,7 @@ def run_b200_arm(args):
         torch.distributed.destroy_process_group()
     if not args.no_warp:
         line["costmap_warp"] = bench_warp(args, device, hbm_peak, peak_kind)
+        line["costmap_propagate"] = bench_propagate(args, device, hbm_peak, peak_kind)
     if world == 1 and not args.no_cpu:
         line["cpu_baseline"] = cpu_baseline_leg(p, args)
     print(json.dumps(line), flush=True)

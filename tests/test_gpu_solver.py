@@ -265,6 +265,52 @@ def test_chunked_streams_give_the_bits_of_one_stream(monkeypatch, chunks):
     assert out[1][5][:2] == out[chunks][5][:2]  # cost / derivative passes summed over the chunks
 
 
+def test_two_host_threads_two_handles_give_the_single_thread_bits():
+    """Handles are independent: two host threads, one handle and one stream each, blocking host-buffer calls in a loop
+    (the way bench.py's end-to-end leg hides PCIe time) — every result equals the one-thread result."""
+    import threading
+    import torch
+    p = cilqr_b200.Parameters()
+    cilqr_b200.load_library().cilqr_params_default(__import__("ctypes").byref(p))
+    p = p.replace(horizon=50)
+    B, n_obs, N = 4099, 6, 50
+    sc = [scenarios.make_scenarios(p, 500 + 5000 * i, B, n_obs, curved=bool(i), dense=False) for i in range(2)]
+    want = []
+    for i in range(2):
+        s = cilqr_b200.iLQR(p, max_batch=B, max_obs=n_obs)
+        s.set_obstacles_cv(sc[i]["obs_state0"], sc[i]["obs_LW"], sc[i]["obs_sigma"], sc[i]["kappa"])
+        U = sc[i]["U0"].copy()
+        s.get_optimal_control_seq(sc[i]["x0"], U, sc[i]["poly"], sc[i]["xlp"])
+        want.append((U, s.X_result.copy(), s.J_result.copy(), s.iterations.copy()))
+        s.close()
+    errors = []
+
+    def worker(i):
+        try:
+            torch.cuda.set_device(0)
+            s = cilqr_b200.iLQR(p, max_batch=B, max_obs=n_obs, stream=torch.cuda.Stream())
+            pin = {k: torch.from_numpy(sc[i][k]).pin_memory().numpy() for k in ("x0", "U0", "poly", "xlp", "obs_state0", "obs_LW", "obs_sigma")}
+            U = torch.empty((B, 2 * N), dtype=torch.float64).pin_memory().numpy()
+            out = {"X": torch.empty((B, 4 * (N + 1)), dtype=torch.float64).pin_memory().numpy(), "J": torch.empty(B, dtype=torch.float64).pin_memory().numpy(),
+                   "iters": torch.empty(B, dtype=torch.int32).pin_memory().numpy()}
+            for rep in range(6):  # the same buffers again and again: direct launches, then the recorded graph
+                s.set_obstacles_cv(pin["obs_state0"], pin["obs_LW"], pin["obs_sigma"], sc[i]["kappa"])
+                U[...] = pin["U0"]
+                s.get_optimal_control_seq(pin["x0"], U, pin["poly"], pin["xlp"], outputs=out, want=())
+                for a, b in zip(want[i], (U, out["X"], out["J"], out["iters"])):
+                    assert np.array_equal(a, b), (i, rep)
+            s.close()
+        except Exception as e:  # noqa: BLE001
+            errors.append((i, repr(e)))
+
+    th = [threading.Thread(target=worker, args=(i,)) for i in range(2)]
+    for t in th:
+        t.start()
+    for t in th:
+        t.join()
+    assert errors == []
+
+
 def test_edge_cases_and_error_codes(checker):
     p = checker.params_default(horizon=50)
     sc = scenarios.make_scenarios(p, 0, 4, 2)
