@@ -265,6 +265,35 @@ def test_chunked_streams_give_the_bits_of_one_stream(monkeypatch, chunks):
     assert out[1][5][:2] == out[chunks][5][:2]  # cost / derivative passes summed over the chunks
 
 
+def test_solve_trace_lists_every_launch_in_order(monkeypatch, checker):
+    """cilqr_solve_trace (CILQR_TRACE=1): one entry per launch of the last solve, rounds in order on each chunk's stream."""
+    p = checker.params_default(horizon=50)
+    B, n_obs = 96, 3
+    sc = scenarios.make_scenarios(p, 77, B, n_obs, dense=False)
+    monkeypatch.setenv("CILQR_TRACE", "1")
+    monkeypatch.setenv("CILQR_CHUNKS", "2")
+    s = cilqr_b200.iLQR(p, max_batch=B, max_obs=n_obs)
+    monkeypatch.delenv("CILQR_TRACE")
+    s.set_obstacles_cv(sc["obs_state0"], sc["obs_LW"], sc["obs_sigma"], sc["kappa"])
+    U = sc["U0"].copy()
+    s.get_optimal_control_seq(sc["x0"], U, sc["poly"], sc["xlp"])
+    tl = s.solve_trace()
+    M = p.max_iterations
+    assert len(tl) == 2 * (1 + (M + 1) + M + M + 1)  # per chunk: init, cost x (M + 1), derivs x M, sweep x M, output
+    for c in range(2):
+        mine = [e for e in tl if e[0] == c]
+        assert mine[0][2] == "init" and mine[-1][2] == "output"
+        for a, b in zip(mine, mine[1:]):
+            assert a[4] <= b[3] + 1000, (a, b)  # one stream per chunk: a launch starts after the previous one ended (1 us timer slack)
+        order = [(e[1], e[2]) for e in mine[1:-1]]
+        assert order[:4] == [(0, "cost"), (0, "derivs"), (0, "sweep"), (1, "cost")]
+    s2 = cilqr_b200.iLQR(p, max_batch=B, max_obs=n_obs)  # a handle created without the switch has no trace
+    with pytest.raises(cilqr_b200.CilqrError, match="CILQR_TRACE"):
+        s2.solve_trace()
+    s.close()
+    s2.close()
+
+
 def test_two_host_threads_two_handles_give_the_single_thread_bits():
     """Handles are independent: two host threads, one handle and one stream each, blocking host-buffer calls in a loop
     (the way bench.py's end-to-end leg hides PCIe time) — every result equals the one-thread result."""
