@@ -413,11 +413,15 @@ def test_full_size_properties_config4_shard(checker):
     assert torch.isfinite(U1).all() and torch.isfinite(J1).all()
     assert int(it1.min()) >= 1 and int(it1.max()) <= p.max_iterations
     Uh, Jh, ih = U1.cpu().numpy(), J1.cpu().numpy(), it1.cpu().numpy()
-    for b in range(0, B, B // 32):
+    flips = []
+    for b in range(0, B, B // 256):  # 256 scenarios of the shard against the reference itself
         dim, pos = scenarios.expand_obstacles_cv(p, sc["obs_state0"][b], sc["obs_LW"][b], sc["obs_sigma"][b], sc["kappa"])
         r = checker.solve(p, dim, pos, sc["x0"][b], sc["U0"][b], sc["poly"][b], sc["xlp"][b])
-        assert int(ih[b]) == r["iters"], b
+        if int(ih[b]) != r["iters"]:
+            flips.append(b)
+            continue
         assert rel(Uh[b], r["U"]) < TOL and abs(Jh[b] - r["J"]) <= TOL * abs(r["J"]), b
+    assert flips == [], "iteration counts differ from the reference in scenarios %s" % flips
     s.close()
 
 
