@@ -50,8 +50,8 @@ WARP_CHUNK = 64
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
-    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--batch", type=int, default=BATCH_PER_GPU, help="scenarios per GPU")
     ap.add_argument("--n-obs", type=int, default=N_OBS)
@@ -456,7 +456,7 @@ def run_b200_arm(args):
         for w in workers:  # warm-up: allocations, and the third call of a handle replays the recorded graph
             for _ in range(max(3, min(args.warmup, 3))):
                 w.step()
-        ksteps = max(1, min(args.steps, 10))
+        ksteps = max(1, min(args.steps, 12))
         dt1 = run(workers[:1], ksteps)
         each = max(1, (ksteps + n_thr - 1) // n_thr)
         dtp = run(workers, each) if n_thr > 1 else dt1

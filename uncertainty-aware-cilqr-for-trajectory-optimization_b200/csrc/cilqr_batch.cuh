@@ -26,7 +26,7 @@
 
 namespace cilqr
 {
-enum { MODE_ITERATE = 0, MODE_FINAL = 1, MODE_DONE = 2 };
+enum { MODE_ITERATE = 0, MODE_FINAL = 1, MODE_DONE = 2, MODE_LS = 3 }; // MODE_LS: iterating with the line-search extension
 
 // Step record of (scenario, t), t = 0..N: state column t, cos/sin of its heading, control column t, and the derivative
 // record of step t (overwritten by the gains in the sweep).  16-byte aligned pairs -> 128-bit loads.
@@ -218,7 +218,7 @@ static_assert(kHdrD >= 2 * kInitTile && kHdrD % 2 == 0, "the header rows double 
 
 __global__ void __launch_bounds__(kInitThreads) batch_init_kernel(DevParams P, BatchView V, int B, const double *__restrict__ x0,
                                                                   const double *__restrict__ U, const double *__restrict__ poly,
-                                                                  const double *__restrict__ xlp)
+                                                                  const double *__restrict__ xlp, int mode0)
 {
     TraceScope trace_scope(V, TRACE_IO, 0);
     __shared__ __align__(16) InitSmem smw[kInitThreads / 32];
@@ -252,7 +252,7 @@ __global__ void __launch_bounds__(kInitThreads) batch_init_kernel(DevParams P, B
         h[H_JOLD] = DBL_MAX;
         h[H_JNEW] = 0.0;
         h[H_JRES] = 0.0;
-        hdr_ints(h, H_ITERS_MODE) = make_int2(0, MODE_ITERATE);
+        hdr_ints(h, H_ITERS_MODE) = make_int2(0, mode0);
         hdr_ints(h, H_CONV_STATUS) = make_int2(0, CILQR_ST_MAX_ITER);
         __syncwarp();
         const double2 *src = reinterpret_cast<const double2 *>(&sm.u[0][0]);
@@ -403,7 +403,9 @@ __global__ void __launch_bounds__(kCostThreads) batch_cost_kernel(DevParams P, B
                 b = list[first + tid];
                 double *h = V.header(b);
                 int2 im = hdr_ints(h, H_ITERS_MODE);
-                if (im.y != MODE_DONE) {
+                if (im.y == MODE_LS) {
+                    accepted = true; // line search: the accept decision is taken by ls_select_kernel; this pass only compacts the list
+                } else if (im.y != MODE_DONE) {
                     double J = 0.0; // J += x_cost + u_cost, t ascending (Constraints.cpp:558)
                     const double *sj = sJ + tid * N;
                     for (int t = 0; t < N; ++t)
@@ -624,6 +626,8 @@ struct SweepSmem {
     double out[2][kSweepThreads][kOutD];
 };
 
+// ROLL = false (line search): the backward pass only; the candidates are rolled out by ls_candidates_kernel.
+template <bool ROLL>
 __global__ void __launch_bounds__(kSweepThreads, 11) batch_sweep_kernel(DevParams P, BatchView V, int round)
 {
     TraceScope trace_scope(V, TRACE_SWEEP, round);
@@ -736,9 +740,15 @@ __global__ void __launch_bounds__(kSweepThreads, 11) batch_sweep_kernel(DevParam
         const bool roll = active && finite;
         if (active && !finite) {
             hdr_ints(h, H_CONV_STATUS).y = CILQR_ST_NONFINITE;
-            h[H_JRES] = h[H_JNEW];
-            hdr_ints(h, H_ITERS_MODE).y = MODE_DONE;
+            if (ROLL) {
+                h[H_JRES] = h[H_JNEW];
+                hdr_ints(h, H_ITERS_MODE).y = MODE_DONE;
+            } else {
+                hdr_ints(h, H_ITERS_MODE) = make_int2(round + 1, MODE_FINAL); // J = get_J(X_result, U_result) comes from the next cost pass
+            }
         }
+        if (!ROLL)
+            continue;
         const unsigned roll_mask = __ballot_sync(0xffffffffu, roll);
 
         // ---- iLQR::forward_pass (iLQR.cpp:68-86), full step, in place: the candidate is accepted by construction (lagged test)
@@ -825,6 +835,186 @@ __global__ void __launch_bounds__(kSweepThreads, 11) batch_sweep_kernel(DevParam
             } else {
                 h[H_JOLD] = h[H_JNEW];
             }
+        }
+    }
+}
+// ------------------------------------------------------------------------------------------------- line search (extension)
+// n_alphas > 1: per round  cost (tracking gradient, list compaction) -> derivs -> backward sweep -> candidates -> merits -> select.
+// Same arithmetic as the first-pass fused kernel (cilqr_solver.cu: solve_kernel<true>, pinned on the plain-C port), in the
+// shape of the round kernels: every phase parallel over what it can be parallel over.
+//
+// Candidate trajectories: cand[b][a][t][8] = (x, y, v, theta, cos, sin, u0, u1) — the first 8 fields of a step record, so the
+// merit kernel reads nominal records (round 0: J of the initial nominal) and candidates through the same strides.
+constexpr int kCandD = S_R;
+struct LsView {
+    double *cand;  // [B][n_alphas][N + 1][kCandD]
+    double *merit; // [B][n_alphas][N]
+    int n_alphas, merit_total;
+};
+
+// Lane = (scenario, alpha): U + alpha k + K dx with alpha = 2^-a (iLQR.cpp:68-86 with a step length), sequential in t.
+// The 8 lanes of a scenario read the same nominal record: a warp instruction touches 4 records.
+__global__ void __launch_bounds__(128) ls_candidates_kernel(DevParams P, BatchView V, LsView L, int round)
+{
+    const int N = P.N, A = L.n_alphas;
+    const int cnt = V.cnt[round + 1];
+    const int *list = V.list(round + 1);
+    const long long total = (long long)cnt * A;
+    for (long long g = blockIdx.x * (long long)blockDim.x + threadIdx.x; g < total; g += (long long)gridDim.x * blockDim.x) {
+        const int e = (int)(g / A), a = (int)(g - (long long)e * A);
+        const int b = list[e];
+        if (hdr_ints(V.header(b), H_ITERS_MODE).y != MODE_LS)
+            continue; // the backward pass of this round ended the scenario
+        const double alpha = ldexp(1.0, -a);
+        const double *r = V.step(b, 0);
+        double *c = L.cand + ((size_t)b * A + a) * (N + 1) * kCandD;
+        double2 xy = ld2(r + S_X), vt = ld2(r + S_V), cs = ld2(r + S_C);
+        double n0 = xy.x, n1 = xy.y, n2 = vt.x, n3 = vt.y, co = cs.x, si = cs.y;
+        for (int t = 0; t < N; ++t, r += kStepD, c += kCandD) {
+            xy = ld2(r + S_X);
+            vt = ld2(r + S_V);
+            const double2 u = ld2(r + S_U0);
+            double g_[kRec];
+#pragma unroll
+            for (int f = 0; f < kRec; f += 2) {
+                const double2 q = ld2(r + S_R + f);
+                g_[f] = q.x;
+                g_[f + 1] = q.y;
+            }
+            const double d0 = n0 - xy.x, d1 = n1 - xy.y, d2 = n2 - vt.x, d3 = n3 - vt.y;
+            const double u0 = (u.x + alpha * g_[0]) + (g_[2] * d0 + g_[4] * d1 + g_[6] * d2 + g_[8] * d3);
+            const double u1 = (u.y + alpha * g_[1]) + (g_[3] * d0 + g_[5] * d1 + g_[7] * d2 + g_[9] * d3);
+            st2(c + S_X, n0, n1);
+            st2(c + S_V, n2, n3);
+            st2(c + S_C, co, si);
+            st2(c + S_U0, u0, u1);
+            double m0, m1, m2, m3;
+            dyn_step(P, n0, n1, n2, n3, co, si, u0, u1, m0, m1, m2, m3);
+            sincos(m3, &si, &co);
+            n0 = m0; n1 = m1; n2 = m2; n3 = m3;
+        }
+        st2(c + S_X, n0, n1);
+        st2(c + S_V, n2, n3);
+        st2(c + S_C, co, si);
+        st2(c + S_U0, 0.0, 0.0);
+    }
+}
+
+// Merit term of every (scenario, alpha, t): the per-step expression of the fused kernel's phase_candidate_merits /
+// finish_step — tracking cost, plus w_obs * (obstacle barriers) + control barriers when merit_total.
+// `nominal`: evaluate the nominal records instead (one "alpha"), for J of the initial nominal.
+template <bool CV>
+__global__ void __launch_bounds__(256) ls_merit_kernel(DevParams P, BatchView V, LsView L, int round, int nominal)
+{
+    const int N = P.N, A = nominal ? 1 : L.n_alphas, n_obs = V.n_obs;
+    const int cnt = V.cnt[round + 1];
+    const int *list = V.list(round + 1);
+    const long long total = (long long)cnt * A * N;
+    for (long long g = blockIdx.x * (long long)blockDim.x + threadIdx.x; g < total; g += (long long)gridDim.x * blockDim.x) {
+        const int e = (int)(g / (A * N)), rem = (int)(g - (long long)e * A * N), a = rem / N, t = rem - a * N;
+        const int b = list[e];
+        const double *h = V.header(b);
+        if (hdr_ints(const_cast<double *>(h), H_ITERS_MODE).y != MODE_LS)
+            continue;
+        const double *c = nominal ? V.step(b, t) : L.cand + (((size_t)b * L.n_alphas + a) * (N + 1) + t) * kCandD;
+        const double2 xy = ld2(c + S_X), cs = ld2(c + S_C), u = ld2(c + S_U0);
+        const double v = c[S_V];
+        PolyY yf;
+        const double2 pl = ld2(h + H_XF);
+        yf.pl.x_first = pl.x;
+        yf.pl.dxs = pl.y;
+        yf.npoly = P.npoly;
+#pragma unroll
+        for (int k = 0; k < kMaxPoly; k += 2) {
+            const double2 c2 = ld2(h + H_POLY + k);
+            yf.c[k] = c2.x;
+            yf.c[k + 1] = c2.y;
+        }
+        double cx, cy;
+        closest_point_lip(P, yf.pl, yf, h[H_LIP], xy.x, xy.y, cx, cy);
+        double jt = tracking_cost(P, xy.x - cx, xy.y - cy, v - P.v_des, u.x, u.y);
+        if (L.merit_total) {
+            double g0, g1, h00, h01, h11, bo = 0, bc = 0, l0, l1, l2, l3;
+            if (CV) {
+                const double tt = t * P.dt;
+                const double *oc = V.ocv + (size_t)b * n_obs * CV_FIELDS, *ob = V.oib2 + (size_t)b * n_obs * N + t;
+                for (int j = 0; j < n_obs; ++j, oc += CV_FIELDS, ob += N) {
+                    const double2 n0 = ld2(oc), n1 = ld2(oc + 2), n2 = ld2(oc + 4);
+                    obstacle_terms<false>(P, xy.x, xy.y, cs.x, cs.y, n0.x + n1.x * tt, n0.y + n1.y * tt, n2.x, n2.y, oc[CV_IA2], ob[0], g0, g1, h00,
+                                          h01, h11, bo);
+                }
+            } else {
+                const double *o = V.orec + (size_t)b * n_obs * OB_FIELDS * N + t;
+                for (int j = 0; j < n_obs; ++j, o += (size_t)OB_FIELDS * N)
+                    obstacle_terms<false>(P, xy.x, xy.y, cs.x, cs.y, o[OB_X * N], o[OB_Y * N], o[OB_C * N], o[OB_S * N], o[OB_IA2 * N],
+                                          o[OB_IB2 * N], g0, g1, h00, h01, h11, bo);
+            }
+            control_terms<false>(P, v, u.x, u.y, l0, l1, l2, l3, bc);
+            jt += P.w_obs * bo + bc;
+        }
+        L.merit[((size_t)b * L.n_alphas + a) * N + t] = jt;
+    }
+}
+
+// One warp per scenario: lane a sums the merit of candidate a in t order, the warp votes for the largest step that improves,
+// copies that candidate over the nominal and applies the lamb / termination logic of the fused kernel's line-search branch.
+// `init`: J_cur = merit of the initial nominal (round 0, before the first backward pass).
+__global__ void __launch_bounds__(128) ls_select_kernel(DevParams P, BatchView V, LsView L, int round, int init)
+{
+    const int N = P.N, A = L.n_alphas, lane = threadIdx.x & 31;
+    const int cnt = V.cnt[round + 1];
+    const int *list = V.list(round + 1);
+    const int warps = (gridDim.x * blockDim.x) >> 5;
+    for (int e = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; e < cnt; e += warps) {
+        const int b = list[e];
+        double *h = V.header(b);
+        if (hdr_ints(h, H_ITERS_MODE).y != MODE_LS)
+            continue;
+        double Ja = 0.0;
+        if (lane < (init ? 1 : A)) {
+            const double *m = L.merit + ((size_t)b * A + lane) * N;
+            for (int t = 0; t < N; ++t)
+                Ja += m[t];
+        }
+        if (init) {
+            if (lane == 0)
+                h[H_JOLD] = Ja;
+            continue;
+        }
+        const double J_cur = h[H_JOLD];
+        double lamb = h[H_LAMB];
+        const unsigned ok = __ballot_sync(0xffffffffu, lane < A && Ja < J_cur);
+        int mode = MODE_LS, status = CILQR_ST_MAX_ITER;
+        if (ok) {
+            const int a = __ffs(ok) - 1;
+            const double Jw = __shfl_sync(0xffffffffu, Ja, a);
+            const double2 *win = reinterpret_cast<const double2 *>(L.cand + ((size_t)b * A + a) * (N + 1) * kCandD);
+            double2 *rec = reinterpret_cast<double2 *>(V.step(b, 0));
+            for (int p = lane; p < (N + 1) * (kCandD / 2); p += 32) { // X, cos/sin, U of every step: the first four pieces of its record
+                const int t = p / (kCandD / 2), f = p - t * (kCandD / 2);
+                rec[(size_t)t * (kStepD / 2) + f] = win[p];
+            }
+            const double dJ = J_cur - Jw;
+            lamb = lamb / P.lamb_factor;
+            if (lane == 0)
+                h[H_JOLD] = Jw;
+            if (fabs(dJ) < P.tol) {
+                status = CILQR_ST_TOLERANCE;
+                mode = MODE_FINAL;
+            }
+        } else {
+            lamb = lamb * P.lamb_factor;
+            if (lamb > P.lamb_max) {
+                status = CILQR_ST_LAMB_MAX;
+                mode = MODE_FINAL;
+            }
+        }
+        if (mode == MODE_LS && round + 1 >= P.max_iter)
+            mode = MODE_FINAL; // out of iterations: status stays CILQR_ST_MAX_ITER
+        if (lane == 0) {
+            h[H_LAMB] = lamb;
+            hdr_ints(h, H_ITERS_MODE) = make_int2(round + 1, mode);
+            hdr_ints(h, H_CONV_STATUS) = make_int2(0, status);
         }
     }
 }

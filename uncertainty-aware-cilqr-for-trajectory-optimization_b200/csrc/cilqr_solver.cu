@@ -519,7 +519,7 @@ int cilqr_create(const cilqr_params *p, int max_batch, int max_obs, cilqr_handle
         CILQR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o0, batch_cost_kernel, kCostThreads, cost_smem));
         CILQR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o1, batch_derivs_kernel<true>, kDerivThreads, 0));
         CILQR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o2, batch_derivs_kernel<false>, kDerivThreads, 0));
-        CILQR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o3, batch_sweep_kernel, kSweepThreads, 0));
+        CILQR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o3, batch_sweep_kernel<true>, kSweepThreads, 0));
         h->occ_cost = std::max(1, o0);
         h->occ_deriv = std::max(1, std::min(o1, o2));
         h->occ_sweep = std::max(1, o3);
@@ -710,7 +710,7 @@ static int issue_rounds(cilqr_handle h, const SolveArgs &A, const HostIO *io, cu
             CILQR_CUDA(cudaMemcpyAsync(const_cast<double *>(A.xlp) + 2 * so, io->xlp + 2 * so, sb * 2 * sizeof(double), cudaMemcpyHostToDevice, cs[c]));
         }
         CILQR_CUDA(cudaMemsetAsync(v.cnt, 0, (size_t)n_cnt * sizeof(int), cs[c]));
-        batch_init_kernel<<<(b + kInitThreads - 1) / kInitThreads, kInitThreads, 0, cs[c]>>>(P, v, b, A.x0 + 4 * so, A.U + 2 * N * so, A.poly + P.npoly * so, A.xlp + 2 * so);
+        batch_init_kernel<<<(b + kInitThreads - 1) / kInitThreads, kInitThreads, 0, cs[c]>>>(P, v, b, A.x0 + 4 * so, A.U + 2 * N * so, A.poly + P.npoly * so, A.xlp + 2 * so, MODE_ITERATE);
         CILQR_LAUNCH_CHECK();
         const int cost_grid = std::min((b + E - 1) / E, h->num_sms * h->occ_cost);
         const long long items = (long long)b * N;
@@ -727,7 +727,7 @@ static int issue_rounds(cilqr_handle h, const SolveArgs &A, const HostIO *io, cu
             else
                 batch_derivs_kernel<false><<<deriv_grid, kDerivThreads, 0, cs[c]>>>(P, v, r);
             CILQR_LAUNCH_CHECK();
-            batch_sweep_kernel<<<sweep_grid, kSweepThreads, 0, cs[c]>>>(P, v, r);
+            batch_sweep_kernel<true><<<sweep_grid, kSweepThreads, 0, cs[c]>>>(P, v, r);
             CILQR_LAUNCH_CHECK();
         }
         const size_t out_items = sb * (N + 1);
@@ -838,6 +838,98 @@ static int solve_rounds(cilqr_handle h, const SolveArgs &A, const HostIO *io, cu
     return 0;
 }
 
+// Line-search extension (n_alphas > 1) as rounds: cost (tracking gradient + list compaction) -> derivatives -> backward sweep ->
+// candidates (one lane per step length) -> merits (one thread per candidate step) -> select (one warp per scenario).
+static int solve_rounds_ls(cilqr_handle h, const SolveArgs &A, cudaStream_t st)
+{
+    const DevParams &P = h->dp;
+    const int N = P.N, B = A.B, n_obs = h->cur_nobs, na = A.n_alphas;
+    const int n_cnt = P.max_iter + 3;
+    const size_t n_dbl = (size_t)B * kHdrD + (size_t)B * (N + 1) * kStepD;
+    if (int rc = h->bws.reserve(n_dbl * sizeof(double) + ((size_t)2 * B + (size_t)kMaxChunks * n_cnt) * sizeof(int))) return rc;
+    const size_t n_cand = (size_t)B * na * (N + 1) * kCandD, n_merit = (size_t)B * na * N;
+    if (int rc = h->scratch.reserve((n_cand + n_merit) * sizeof(double))) return rc;
+    if (h->trace_on)
+        if (int rc = h->trace.reserve((size_t)kMaxChunks * n_cnt * kTraceKinds * 2 * sizeof(unsigned long long))) return rc;
+    BatchView v;
+    v.N = N;
+    v.hdr = h->bws.as<double>();
+    v.rec = v.hdr + (size_t)B * kHdrD;
+    v.list0 = reinterpret_cast<int *>(v.rec + (size_t)B * (N + 1) * kStepD);
+    v.list1 = v.list0 + B;
+    v.cnt = v.list1 + B;
+    v.n_obs = n_obs;
+    v.cv = h->obs_cv;
+    v.ocv = h->obs_b.as<double>();
+    v.oib2 = v.ocv ? v.ocv + (size_t)B * n_obs * CV_FIELDS : nullptr;
+    v.orec = h->obs.as<double>();
+    v.trace = nullptr;
+    if (h->trace_on) {
+        CILQR_CUDA(cudaMemsetAsync(h->trace.p, 0xff, (size_t)kMaxChunks * n_cnt * kTraceKinds * 2 * sizeof(unsigned long long), st));
+        v.trace = h->trace.as<unsigned long long>();
+    }
+    h->last_cnt = v.cnt;
+    h->last_chunks = 1;
+    drop_graph(h);
+    h->seen_key.clear();
+    LsView L;
+    L.cand = h->scratch.as<double>();
+    L.merit = L.cand + n_cand;
+    L.n_alphas = na;
+    L.merit_total = A.merit == CILQR_MERIT_TOTAL;
+
+    CILQR_CUDA(cudaMemsetAsync(v.cnt, 0, (size_t)n_cnt * sizeof(int), st));
+    batch_init_kernel<<<(B + kInitThreads - 1) / kInitThreads, kInitThreads, 0, st>>>(P, v, B, A.x0, A.U, A.poly, A.xlp, MODE_LS);
+    CILQR_LAUNCH_CHECK();
+    const bool staged = h->obs_cv && n_obs > 0 && h->deriv_staged && 2 * (deriv_stage_bytes(n_obs) + 1024) <= (size_t)h->smem_per_sm;
+    const int E = cost_entries_per_cta(N);
+    const size_t cost_smem = (size_t)E * N * sizeof(double);
+    const int cost_grid = std::min((B + E - 1) / E, h->num_sms * h->occ_cost);
+    const long long items = (long long)B * N;
+    const int deriv_grid = (int)std::min<long long>((items + kDerivThreads - 1) / kDerivThreads, (long long)h->num_sms * h->occ_deriv);
+    const int sweep_grid = std::min((B + kSweepThreads - 1) / kSweepThreads, h->num_sms * h->occ_sweep);
+    const int cand_grid = (int)std::min<long long>(((long long)B * na + 127) / 128, (long long)h->num_sms * 8);
+    const int merit_grid = (int)std::min<long long>((items * na + 255) / 256, (long long)h->num_sms * 4);
+    const int select_grid = std::min((B + 3) / 4, h->num_sms * 8);
+    auto merits = [&](int r, int nominal) -> int {
+        if (v.cv)
+            ls_merit_kernel<true><<<merit_grid, 256, 0, st>>>(P, v, L, r, nominal);
+        else
+            ls_merit_kernel<false><<<merit_grid, 256, 0, st>>>(P, v, L, r, nominal);
+        CILQR_LAUNCH_CHECK();
+        return 0;
+    };
+    for (int r = 0; r <= P.max_iter; ++r) {
+        batch_cost_kernel<<<cost_grid, kCostThreads, cost_smem, st>>>(P, v, r);
+        CILQR_LAUNCH_CHECK();
+        if (r == P.max_iter) break; // J = get_J(X_result, U_result) of the scenarios that ended in the last round
+        if (r == 0) { // J of the initial nominal, in the merit's terms
+            if (int rc = merits(0, 1)) return rc;
+            ls_select_kernel<<<select_grid, 128, 0, st>>>(P, v, L, 0, 1);
+            CILQR_LAUNCH_CHECK();
+        }
+        if (v.cv && staged)
+            batch_derivs_kernel<true, true><<<deriv_grid, kDerivThreads, deriv_stage_bytes(n_obs), st>>>(P, v, r);
+        else if (v.cv)
+            batch_derivs_kernel<true><<<deriv_grid, kDerivThreads, 0, st>>>(P, v, r);
+        else
+            batch_derivs_kernel<false><<<deriv_grid, kDerivThreads, 0, st>>>(P, v, r);
+        CILQR_LAUNCH_CHECK();
+        batch_sweep_kernel<false><<<sweep_grid, kSweepThreads, 0, st>>>(P, v, r);
+        CILQR_LAUNCH_CHECK();
+        ls_candidates_kernel<<<cand_grid, 128, 0, st>>>(P, v, L, r);
+        CILQR_LAUNCH_CHECK();
+        if (int rc = merits(r, 0)) return rc;
+        ls_select_kernel<<<select_grid, 128, 0, st>>>(P, v, L, r, 0);
+        CILQR_LAUNCH_CHECK();
+    }
+    const size_t out_items = (size_t)B * (N + 1);
+    batch_output_kernel<<<(int)std::min<size_t>((out_items + 255) / 256, (size_t)h->num_sms * 8), 256, 0, st>>>(P, v, B, A.U, A.X, A.J, A.iters,
+                                                                                                                A.status);
+    CILQR_LAUNCH_CHECK();
+    return 0;
+}
+
 int cilqr_solve_trace(cilqr_handle h, uint64_t *out, int capacity, int32_t *chunks, int32_t *rounds, void *stream)
 {
     if (!h || !out) return fail(CILQR_E_ARG, "null argument");
@@ -934,6 +1026,19 @@ int cilqr_solve_batch(cilqr_handle h, int B, const double *x0, double *U, const 
     if (int rc = stage_out(h, 10, status, (size_t)B, mem, &A.status)) return rc;
     A.counter = h->counter.as<int>();
 
+    if (n_alphas > 1 && h->variant == 3) {
+        if (!h->obs_cv && h->cur_nobs > 0) {
+            if (int rc = ensure_records(h, st)) return rc;
+        }
+        if (int rc = solve_rounds_ls(h, A, st)) return rc;
+        if (int rc = fetch_out(U, A.U, (size_t)B * 2 * N, mem, st)) return rc;
+        if (int rc = fetch_out(X, A.X, (size_t)B * 4 * (N + 1), mem, st)) return rc;
+        if (int rc = fetch_out(J, A.J, (size_t)B, mem, st)) return rc;
+        if (int rc = fetch_out(iters, A.iters, (size_t)B, mem, st)) return rc;
+        if (int rc = fetch_out(status, A.status, (size_t)B, mem, st)) return rc;
+        if (mem == CILQR_MEM_HOST) CILQR_CUDA(cudaStreamSynchronize(st));
+        return 0;
+    }
     if (h->cur_nobs > 0) {
         if (int rc = ensure_records(h, st)) return rc;
         A.obs = h->obs.as<double>();
