@@ -847,72 +847,179 @@ __global__ void __launch_bounds__(kSweepThreads, 11) batch_sweep_kernel(DevParam
 // merit kernel reads nominal records (round 0: J of the initial nominal) and candidates through the same strides.
 constexpr int kCandD = S_R;
 struct LsView {
-    double *cand;  // [B][n_alphas][N + 1][kCandD]
-    double *merit; // [B][n_alphas][N]
+    double *cand;   // [B][n_alphas][N + 1][kCandD]
+    double *merit;  // [B][n_alphas][N]
+    int *retry;     // scenarios whose full step did not improve in this round (second wave)
+    int *retry_cnt; // [max_iter + 1]
     int n_alphas, merit_total;
 };
+// Two waves per round, same result as all step lengths at once (the largest improving step wins): wave 1 rolls out and
+// rates alpha = 1 only; the scenarios it does not improve (about one in five in config 3) go on the retry list and wave 2
+// rolls out alpha = 1/2 ... 2^-(n_alphas-1) for them, side by side, and votes.
+struct LsWave {
+    const int *list;
+    int cnt, a0, na;
+};
+__device__ __forceinline__ LsWave ls_wave(const BatchView &V, const LsView &L, int round, int wave)
+{
+    LsWave w;
+    if (wave == 2) {
+        w.list = L.retry;
+        w.cnt = L.retry_cnt[round];
+        w.a0 = 1;
+        w.na = L.n_alphas - 1;
+    } else {
+        w.list = V.list(round + 1);
+        w.cnt = V.cnt[round + 1];
+        w.a0 = 0;
+        w.na = 1;
+    }
+    return w;
+}
+
+// ---- bulk-copy (TMA unit) helpers: contiguous runs global <-> shared memory, completion on an mbarrier / a bulk group
+__device__ __forceinline__ void mbar_init(uint32_t bar, int count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
+{
+    uint32_t ok = 0;
+    while (!ok)
+        asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }" : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void bulk_s2g(void *dst, uint32_t src, uint32_t bytes)
+{
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(src), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+__device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
 // Lane = (scenario, alpha): U + alpha k + K dx with alpha = 2^-a (iLQR.cpp:68-86 with a step length), sequential in t.
-// The 8 lanes of a scenario read the same nominal record: a warp instruction touches 4 records.
-__global__ void __launch_bounds__(128) ls_candidates_kernel(DevParams P, BatchView V, LsView L, int round)
+// One warp per CTA.  The chain of a step is short (gains, bicycle step, one sincos); what a warp cannot do fast is fetch 32
+// scattered records per step: 14 per-lane 16-byte loads per step cost ~1 800 cycles in the load/store unit, and the same
+// pieces moved cooperatively with cp.async still keep only one warp's worth of requests in flight per SM (46 / 52 us per
+// launch, with or without the arithmetic).  So the TMA unit moves them: kLsT consecutive steps of one scenario are one
+// contiguous run (kLsT x 144 bytes), one `cp.async.bulk` per scenario and chunk issued by the scenario's lane, completion
+// on an mbarrier, one chunk ahead of the arithmetic.  Each lane reads its scenario's row (the lanes of one scenario:
+// broadcast; rows 16 bytes apart modulo 128: no bank conflicts on 128-bit accesses) and leaves its candidate the same way:
+// kLsT x 64 bytes staged in its own shared-memory row, one bulk store per lane and chunk.
+constexpr int kLsT = 8; // 92 KB of shared memory: two CTAs per SM
+constexpr int ls_pad_row(int bytes) { return bytes + ((16 - bytes % 128) + 128) % 128; } // row stride = 16 bytes modulo 128
+constexpr int kLsInRow = ls_pad_row(kLsT * kStepD * 8) / 8, kLsOutRow = ls_pad_row(kLsT * kCandD * 8) / 8;
+struct LsCandSmem {
+    double in[2][32][kLsInRow];
+    double out[32][kLsOutRow];
+    unsigned long long full[2];
+};
+__global__ void __launch_bounds__(32) ls_candidates_kernel(DevParams P, BatchView V, LsView L, int round, int wave)
 {
-    const int N = P.N, A = L.n_alphas;
-    const int cnt = V.cnt[round + 1];
-    const int *list = V.list(round + 1);
-    const long long total = (long long)cnt * A;
-    for (long long g = blockIdx.x * (long long)blockDim.x + threadIdx.x; g < total; g += (long long)gridDim.x * blockDim.x) {
-        const int e = (int)(g / A), a = (int)(g - (long long)e * A);
-        const int b = list[e];
-        if (hdr_ints(V.header(b), H_ITERS_MODE).y != MODE_LS)
-            continue; // the backward pass of this round ended the scenario
+    extern __shared__ __align__(128) unsigned char ls_smem_raw[];
+    LsCandSmem &sm = *reinterpret_cast<LsCandSmem *>(ls_smem_raw);
+    const int N = P.N, A = L.n_alphas, lane = threadIdx.x;
+    const LsWave w = ls_wave(V, L, round, wave);
+    const long long total = (long long)w.cnt * w.na;
+    const int nchunks = (N + kLsT - 1) / kLsT;
+    const uint32_t bar0 = (uint32_t)__cvta_generic_to_shared(&sm.full[0]);
+    if (lane == 0) {
+        mbar_init(bar0, 1);
+        mbar_init(bar0 + 8, 1);
+    }
+    __syncwarp();
+    uint32_t parity = 0; // bit i: the phase of full[i] to wait for next
+    for (long long g0 = (long long)blockIdx.x * 32; g0 < total; g0 += (long long)gridDim.x * 32) {
+        const long long g = g0 + lane;
+        const bool valid = g < total;
+        const int e_first = (int)(g0 / w.na), e_last = (int)(min(g0 + 31, total - 1) / w.na), n_slots = e_last - e_first + 1;
+        const int e = valid ? (int)(g / w.na) : e_first, a = valid ? w.a0 + (int)(g - (long long)e * w.na) : w.a0;
+        const int slot = e - e_first;
+        const int b = w.list[e];
+        const bool run = valid && hdr_ints(V.header(b), H_ITERS_MODE).y == MODE_LS; // else: the backward pass ended the scenario
         const double alpha = ldexp(1.0, -a);
-        const double *r = V.step(b, 0);
-        double *c = L.cand + ((size_t)b * A + a) * (N + 1) * kCandD;
-        double2 xy = ld2(r + S_X), vt = ld2(r + S_V), cs = ld2(r + S_C);
-        double n0 = xy.x, n1 = xy.y, n2 = vt.x, n3 = vt.y, co = cs.x, si = cs.y;
-        for (int t = 0; t < N; ++t, r += kStepD, c += kCandD) {
-            xy = ld2(r + S_X);
-            vt = ld2(r + S_V);
-            const double2 u = ld2(r + S_U0);
-            double g_[kRec];
-#pragma unroll
-            for (int f = 0; f < kRec; f += 2) {
-                const double2 q = ld2(r + S_R + f);
-                g_[f] = q.x;
-                g_[f + 1] = q.y;
+        double *cand = L.cand + ((size_t)b * A + a) * (N + 1) * kCandD;
+        const int b_slot = lane < n_slots ? w.list[e_first + lane] : 0; // scenario of row `lane`
+        auto stage = [&](int c) {
+            const int t0 = c * kLsT;
+            const uint32_t bytes = (uint32_t)min(kLsT, N - t0) * kStepD * 8, bar = bar0 + 8 * (c & 1);
+            if (lane == 0)
+                mbar_expect_tx(bar, bytes * n_slots);
+            __syncwarp();
+            if (lane < n_slots)
+                bulk_g2s((uint32_t)__cvta_generic_to_shared(&sm.in[c & 1][lane][0]), V.step(b_slot, t0), bytes, bar);
+        };
+        stage(0);
+        double n0 = 0, n1 = 0, n2 = 0, n3 = 0, co = 1, si = 0;
+        for (int c = 0; c < nchunks; ++c) {
+            const int t0 = c * kLsT, steps = min(kLsT, N - t0);
+            if (c + 1 < nchunks)
+                stage(c + 1); // its buffer was read two chunks ago (the __syncwarp below)
+            mbar_wait(bar0 + 8 * (c & 1), (parity >> (c & 1)) & 1);
+            parity ^= 1u << (c & 1);
+            const double *__restrict__ row = &sm.in[c & 1][slot][0];
+            double *__restrict__ orow = &sm.out[lane][0];
+            if (c == 0) {
+                const double2 xy = ld2(row + S_X), vt = ld2(row + S_V), cs = ld2(row + S_C);
+                n0 = xy.x; n1 = xy.y; n2 = vt.x; n3 = vt.y; co = cs.x; si = cs.y;
             }
-            const double d0 = n0 - xy.x, d1 = n1 - xy.y, d2 = n2 - vt.x, d3 = n3 - vt.y;
-            const double u0 = (u.x + alpha * g_[0]) + (g_[2] * d0 + g_[4] * d1 + g_[6] * d2 + g_[8] * d3);
-            const double u1 = (u.y + alpha * g_[1]) + (g_[3] * d0 + g_[5] * d1 + g_[7] * d2 + g_[9] * d3);
+            if (run) {
+                if (c > 0)
+                    bulk_wait_read(); // this lane's previous bulk store has read its row
+                for (int tt = 0; tt < steps; ++tt, row += kStepD, orow += kCandD) {
+                    const double2 xy = ld2(row + S_X), vt = ld2(row + S_V), u = ld2(row + S_U0);
+                    const double2 k = ld2(row + S_R), K0 = ld2(row + S_R + 2), K1 = ld2(row + S_R + 4), K2 = ld2(row + S_R + 6),
+                                  K3 = ld2(row + S_R + 8);
+                    const double d0 = n0 - xy.x, d1 = n1 - xy.y, d2 = n2 - vt.x, d3 = n3 - vt.y;
+                    const double u0 = (u.x + alpha * k.x) + (K0.x * d0 + K1.x * d1 + K2.x * d2 + K3.x * d3);
+                    const double u1 = (u.y + alpha * k.y) + (K0.y * d0 + K1.y * d1 + K2.y * d2 + K3.y * d3);
+                    st2(orow + S_X, n0, n1);
+                    st2(orow + S_V, n2, n3);
+                    st2(orow + S_C, co, si);
+                    st2(orow + S_U0, u0, u1);
+                    double m0, m1, m2, m3;
+                    dyn_step(P, n0, n1, n2, n3, co, si, u0, u1, m0, m1, m2, m3);
+                    sincos(m3, &si, &co);
+                    n0 = m0; n1 = m1; n2 = m2; n3 = m3;
+                }
+                fence_proxy_async(); // the row was written through the generic proxy, the bulk store reads it through the async one
+                bulk_s2g(cand + (size_t)t0 * kCandD, (uint32_t)__cvta_generic_to_shared(&sm.out[lane][0]), (uint32_t)steps * kCandD * 8);
+            }
+            __syncwarp();
+        }
+        if (run) {
+            double *c = cand + (size_t)N * kCandD;
             st2(c + S_X, n0, n1);
             st2(c + S_V, n2, n3);
             st2(c + S_C, co, si);
-            st2(c + S_U0, u0, u1);
-            double m0, m1, m2, m3;
-            dyn_step(P, n0, n1, n2, n3, co, si, u0, u1, m0, m1, m2, m3);
-            sincos(m3, &si, &co);
-            n0 = m0; n1 = m1; n2 = m2; n3 = m3;
+            st2(c + S_U0, 0.0, 0.0);
+            asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); // the candidate is in memory when the kernel ends
         }
-        st2(c + S_X, n0, n1);
-        st2(c + S_V, n2, n3);
-        st2(c + S_C, co, si);
-        st2(c + S_U0, 0.0, 0.0);
     }
 }
 
 // Merit term of every (scenario, alpha, t): the per-step expression of the fused kernel's phase_candidate_merits /
 // finish_step — tracking cost, plus w_obs * (obstacle barriers) + control barriers when merit_total.
-// `nominal`: evaluate the nominal records instead (one "alpha"), for J of the initial nominal.
+// wave 0: the nominal records; wave 1 / 2: see LsWave.
 template <bool CV>
-__global__ void __launch_bounds__(256) ls_merit_kernel(DevParams P, BatchView V, LsView L, int round, int nominal)
+__global__ void __launch_bounds__(256) ls_merit_kernel(DevParams P, BatchView V, LsView L, int round, int wave)
 {
-    const int N = P.N, A = nominal ? 1 : L.n_alphas, n_obs = V.n_obs;
-    const int cnt = V.cnt[round + 1];
-    const int *list = V.list(round + 1);
-    const long long total = (long long)cnt * A * N;
+    const int N = P.N, n_obs = V.n_obs;
+    const bool nominal = wave == 0;
+    const LsWave w = ls_wave(V, L, round, wave);
+    const int A = w.na;
+    const long long total = (long long)w.cnt * A * N;
     for (long long g = blockIdx.x * (long long)blockDim.x + threadIdx.x; g < total; g += (long long)gridDim.x * blockDim.x) {
-        const int e = (int)(g / (A * N)), rem = (int)(g - (long long)e * A * N), a = rem / N, t = rem - a * N;
-        const int b = list[e];
+        const int e = (int)(g / (A * N)), rem = (int)(g - (long long)e * A * N), ai = rem / N, t = rem - ai * N, a = w.a0 + ai;
+        const int b = w.list[e];
         const double *h = V.header(b);
         if (hdr_ints(const_cast<double *>(h), H_ITERS_MODE).y != MODE_LS)
             continue;
@@ -938,7 +1045,8 @@ __global__ void __launch_bounds__(256) ls_merit_kernel(DevParams P, BatchView V,
             if (CV) {
                 const double tt = t * P.dt;
                 const double *oc = V.ocv + (size_t)b * n_obs * CV_FIELDS, *ob = V.oib2 + (size_t)b * n_obs * N + t;
-                for (int j = 0; j < n_obs; ++j, oc += CV_FIELDS, ob += N) {
+#pragma unroll 2
+                for (int j = 0; j < n_obs; ++j, oc += CV_FIELDS, ob += N) { // two obstacles' exp chains side by side; bo in j order
                     const double2 n0 = ld2(oc), n1 = ld2(oc + 2), n2 = ld2(oc + 4);
                     obstacle_terms<false>(P, xy.x, xy.y, cs.x, cs.y, n0.x + n1.x * tt, n0.y + n1.y * tt, n2.x, n2.y, oc[CV_IA2], ob[0], g0, g1, h00,
                                           h01, h11, bo);
@@ -958,32 +1066,38 @@ __global__ void __launch_bounds__(256) ls_merit_kernel(DevParams P, BatchView V,
 
 // One warp per scenario: lane a sums the merit of candidate a in t order, the warp votes for the largest step that improves,
 // copies that candidate over the nominal and applies the lamb / termination logic of the fused kernel's line-search branch.
-// `init`: J_cur = merit of the initial nominal (round 0, before the first backward pass).
-__global__ void __launch_bounds__(128) ls_select_kernel(DevParams P, BatchView V, LsView L, int round, int init)
+// wave 0: J_cur = merit of the initial nominal (round 0, before the first backward pass).  wave 1: alpha = 1 alone; a scenario
+// it does not improve goes on the retry list untouched.  wave 2: the remaining step lengths of the retry list.
+__global__ void __launch_bounds__(128) ls_select_kernel(DevParams P, BatchView V, LsView L, int round, int wave)
 {
     const int N = P.N, A = L.n_alphas, lane = threadIdx.x & 31;
-    const int cnt = V.cnt[round + 1];
-    const int *list = V.list(round + 1);
+    const LsWave w = ls_wave(V, L, round, wave);
+    const int a_lo = w.a0, a_hi = w.a0 + w.na;
     const int warps = (gridDim.x * blockDim.x) >> 5;
-    for (int e = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; e < cnt; e += warps) {
-        const int b = list[e];
+    for (int e = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; e < w.cnt; e += warps) {
+        const int b = w.list[e];
         double *h = V.header(b);
         if (hdr_ints(h, H_ITERS_MODE).y != MODE_LS)
             continue;
         double Ja = 0.0;
-        if (lane < (init ? 1 : A)) {
+        if (w.na == 1 && N <= 64) { // one candidate: the warp fetches its N terms together, the sum stays in t order
+            const double *m = L.merit + ((size_t)b * A + a_lo) * N;
+            const double m0 = lane < N ? m[lane] : 0.0, m1 = lane + 32 < N ? m[lane + 32] : 0.0;
+            for (int t = 0; t < N; ++t)
+                Ja += __shfl_sync(0xffffffffu, t < 32 ? m0 : m1, t & 31);
+        } else if (lane >= a_lo && lane < a_hi) {
             const double *m = L.merit + ((size_t)b * A + lane) * N;
             for (int t = 0; t < N; ++t)
                 Ja += m[t];
         }
-        if (init) {
+        if (wave == 0) {
             if (lane == 0)
                 h[H_JOLD] = Ja;
             continue;
         }
         const double J_cur = h[H_JOLD];
         double lamb = h[H_LAMB];
-        const unsigned ok = __ballot_sync(0xffffffffu, lane < A && Ja < J_cur);
+        const unsigned ok = __ballot_sync(0xffffffffu, lane >= a_lo && lane < a_hi && Ja < J_cur);
         int mode = MODE_LS, status = CILQR_ST_MAX_ITER;
         if (ok) {
             const int a = __ffs(ok) - 1;
@@ -1002,6 +1116,10 @@ __global__ void __launch_bounds__(128) ls_select_kernel(DevParams P, BatchView V
                 status = CILQR_ST_TOLERANCE;
                 mode = MODE_FINAL;
             }
+        } else if (wave == 1 && A > 1) {
+            if (lane == 0)
+                L.retry[atomicAdd(&L.retry_cnt[round], 1)] = b;
+            continue;
         } else {
             lamb = lamb * P.lamb_factor;
             if (lamb > P.lamb_max) {

@@ -514,6 +514,7 @@ int cilqr_create(const cilqr_params *p, int max_batch, int max_obs, cilqr_handle
         CILQR_CUDA(cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
         h->smem_per_sm = std::min(h->smem_per_sm, 2 * optin);
         CILQR_CUDA(cudaFuncSetAttribute(batch_derivs_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, std::min(optin, h->smem_per_sm / 2 - 1024)));
+        CILQR_CUDA(cudaFuncSetAttribute(ls_candidates_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(LsCandSmem)));
 
         int o0 = 0, o1 = 0, o2 = 0, o3 = 0;
         CILQR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o0, batch_cost_kernel, kCostThreads, cost_smem));
@@ -848,7 +849,7 @@ static int solve_rounds_ls(cilqr_handle h, const SolveArgs &A, cudaStream_t st)
     const size_t n_dbl = (size_t)B * kHdrD + (size_t)B * (N + 1) * kStepD;
     if (int rc = h->bws.reserve(n_dbl * sizeof(double) + ((size_t)2 * B + (size_t)kMaxChunks * n_cnt) * sizeof(int))) return rc;
     const size_t n_cand = (size_t)B * na * (N + 1) * kCandD, n_merit = (size_t)B * na * N;
-    if (int rc = h->scratch.reserve((n_cand + n_merit) * sizeof(double))) return rc;
+    if (int rc = h->scratch.reserve((n_cand + n_merit) * sizeof(double) + ((size_t)B + n_cnt) * sizeof(int))) return rc;
     if (h->trace_on)
         if (int rc = h->trace.reserve((size_t)kMaxChunks * n_cnt * kTraceKinds * 2 * sizeof(unsigned long long))) return rc;
     BatchView v;
@@ -875,10 +876,13 @@ static int solve_rounds_ls(cilqr_handle h, const SolveArgs &A, cudaStream_t st)
     LsView L;
     L.cand = h->scratch.as<double>();
     L.merit = L.cand + n_cand;
+    L.retry = reinterpret_cast<int *>(L.merit + n_merit);
+    L.retry_cnt = L.retry + B;
     L.n_alphas = na;
     L.merit_total = A.merit == CILQR_MERIT_TOTAL;
 
     CILQR_CUDA(cudaMemsetAsync(v.cnt, 0, (size_t)n_cnt * sizeof(int), st));
+    CILQR_CUDA(cudaMemsetAsync(L.retry_cnt, 0, (size_t)n_cnt * sizeof(int), st));
     batch_init_kernel<<<(B + kInitThreads - 1) / kInitThreads, kInitThreads, 0, st>>>(P, v, B, A.x0, A.U, A.poly, A.xlp, MODE_LS);
     CILQR_LAUNCH_CHECK();
     const bool staged = h->obs_cv && n_obs > 0 && h->deriv_staged && 2 * (deriv_stage_bytes(n_obs) + 1024) <= (size_t)h->smem_per_sm;
@@ -888,14 +892,19 @@ static int solve_rounds_ls(cilqr_handle h, const SolveArgs &A, cudaStream_t st)
     const long long items = (long long)B * N;
     const int deriv_grid = (int)std::min<long long>((items + kDerivThreads - 1) / kDerivThreads, (long long)h->num_sms * h->occ_deriv);
     const int sweep_grid = std::min((B + kSweepThreads - 1) / kSweepThreads, h->num_sms * h->occ_sweep);
-    const int cand_grid = (int)std::min<long long>(((long long)B * na + 127) / 128, (long long)h->num_sms * 8);
-    const int merit_grid = (int)std::min<long long>((items * na + 255) / 256, (long long)h->num_sms * 4);
+    // wave 1 (alpha = 1 of every scenario) and wave 2 (the other step lengths of the scenarios wave 1 did not improve, a
+    // device-side list whose length the host does not know: the grids are sized for the whole batch and run empty past it)
+    const int cand_grid1 = (int)std::min<long long>((B + 31) / 32, (long long)h->num_sms * 2);
+    const int cand_grid2 = (int)std::min<long long>(((long long)B * (na - 1) + 31) / 32, (long long)h->num_sms * 2);
+    const int merit_grid1 = (int)std::min<long long>((items + 255) / 256, (long long)h->num_sms * 4);
+    const int merit_grid2 = (int)std::min<long long>((items * (na - 1) + 255) / 256, (long long)h->num_sms * 4);
     const int select_grid = std::min((B + 3) / 4, h->num_sms * 8);
-    auto merits = [&](int r, int nominal) -> int {
+    auto merits = [&](int r, int wave) -> int {
+        const int grid = wave == 2 ? merit_grid2 : merit_grid1;
         if (v.cv)
-            ls_merit_kernel<true><<<merit_grid, 256, 0, st>>>(P, v, L, r, nominal);
+            ls_merit_kernel<true><<<grid, 256, 0, st>>>(P, v, L, r, wave);
         else
-            ls_merit_kernel<false><<<merit_grid, 256, 0, st>>>(P, v, L, r, nominal);
+            ls_merit_kernel<false><<<grid, 256, 0, st>>>(P, v, L, r, wave);
         CILQR_LAUNCH_CHECK();
         return 0;
     };
@@ -904,8 +913,8 @@ static int solve_rounds_ls(cilqr_handle h, const SolveArgs &A, cudaStream_t st)
         CILQR_LAUNCH_CHECK();
         if (r == P.max_iter) break; // J = get_J(X_result, U_result) of the scenarios that ended in the last round
         if (r == 0) { // J of the initial nominal, in the merit's terms
-            if (int rc = merits(0, 1)) return rc;
-            ls_select_kernel<<<select_grid, 128, 0, st>>>(P, v, L, 0, 1);
+            if (int rc = merits(0, 0)) return rc;
+            ls_select_kernel<<<select_grid, 128, 0, st>>>(P, v, L, 0, 0);
             CILQR_LAUNCH_CHECK();
         }
         if (v.cv && staged)
@@ -917,11 +926,13 @@ static int solve_rounds_ls(cilqr_handle h, const SolveArgs &A, cudaStream_t st)
         CILQR_LAUNCH_CHECK();
         batch_sweep_kernel<false><<<sweep_grid, kSweepThreads, 0, st>>>(P, v, r);
         CILQR_LAUNCH_CHECK();
-        ls_candidates_kernel<<<cand_grid, 128, 0, st>>>(P, v, L, r);
-        CILQR_LAUNCH_CHECK();
-        if (int rc = merits(r, 0)) return rc;
-        ls_select_kernel<<<select_grid, 128, 0, st>>>(P, v, L, r, 0);
-        CILQR_LAUNCH_CHECK();
+        for (int wave = 1; wave <= 2; ++wave) {
+            ls_candidates_kernel<<<wave == 1 ? cand_grid1 : cand_grid2, 32, sizeof(LsCandSmem), st>>>(P, v, L, r, wave);
+            CILQR_LAUNCH_CHECK();
+            if (int rc = merits(r, wave)) return rc;
+            ls_select_kernel<<<select_grid, 128, 0, st>>>(P, v, L, r, wave);
+            CILQR_LAUNCH_CHECK();
+        }
     }
     const size_t out_items = (size_t)B * (N + 1);
     batch_output_kernel<<<(int)std::min<size_t>((out_items + 255) / 256, (size_t)h->num_sms * 8), 256, 0, st>>>(P, v, B, A.U, A.X, A.J, A.iters,
