@@ -60,7 +60,7 @@ def parse_args():
     ap.add_argument("--no-warp", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--e2e-threads", type=int, default=3, help="host threads (one solver handle each) in the end-to-end measurement")
+    ap.add_argument("--e2e-threads", type=int, default=4, help="host threads (one solver handle each) in the end-to-end measurement")
     return ap.parse_args()
 
 
@@ -361,6 +361,15 @@ def run_b200_arm(args):
     res = {"X": torch.empty((B, 4 * (N + 1)), dtype=torch.float64, device=device), "J": torch.empty(B, dtype=torch.float64, device=device),
            "iters": torch.empty(B, dtype=torch.int32, device=device), "status": torch.empty(B, dtype=torch.int32, device=device)}
 
+    # The exchange step runs on its own stream from a snapshot of U*: step i's all-gather travels over NVLink
+    # under step i+1's rounds (the solver's U buffer is in/out and is reset at the start of the next step).  The timed region
+    # ends with a device-wide synchronize, so the last gather is inside it.
+    if world > 1:
+        U_snap = torch.empty_like(U)
+        comm_stream = torch.cuda.Stream(device=device)
+        solved, gathered_ev = torch.cuda.Event(), torch.cuda.Event()
+        gathered_ev.record()
+
     def step(timed):
         solver.set_obstacles_cv(d["obs_state0"], d["obs_LW"], d["obs_sigma"], sc["kappa"])  # covariance propagation on device
         U.copy_(d["U0"])
@@ -372,7 +381,14 @@ def run_b200_arm(args):
             ev[1].record()
             kern_ev.append(ev)
         if world > 1:
-            torch.distributed.all_gather_into_tensor(gathered, U)  # the one exchange step
+            cur = torch.cuda.current_stream()
+            cur.wait_event(gathered_ev)  # the previous gather has read the snapshot
+            U_snap.copy_(U)
+            solved.record(cur)
+            with torch.cuda.stream(comm_stream):
+                comm_stream.wait_event(solved)
+                torch.distributed.all_gather_into_tensor(gathered, U_snap)
+                gathered_ev.record(comm_stream)
 
     for _ in range(max(args.warmup, 0)):
         step(False)
@@ -391,6 +407,8 @@ def run_b200_arm(args):
     if world > 1:
         torch.distributed.barrier()
     total_ms = max_over_ranks(e0.elapsed_time(e1), world, device)
+    if world > 1:
+        assert torch.equal(gathered[rank * B:(rank + 1) * B], U), "all-gather of U*: this rank's slice differs from its own result"
     clocks = sampler.stop() if sampler else None
     launches = cilqr_b200.launch_count() - launches0
     kernel_ms = float(np.mean([a.elapsed_time(b) for a, b in kern_ev]))
@@ -500,7 +518,7 @@ def run_b200_arm(args):
                          % ("working set larger than L2" if B * (n_obs * 8 * (8 + N) + (18 + 18 * (N + 1)) * 8) > 126e6 else
                             "working set L2-resident: a parity-size configuration, not the headline", B * n_obs * 8 * (8 + N) / 1e9,
                             B * (18 + 18 * (N + 1)) * 8 / 1e9),
-                   "collective": "all_gather U* (NCCL)" if world > 1 else "none"},
+                   "collective": "all_gather U* (NCCL), on its own stream under the next step's rounds" if world > 1 else "none"},
         "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches),
         "roofline": {"kernel": ("cilqr_solve_batch = batch_init + <= %d rounds of batch_cost / batch_derivs / batch_sweep + batch_output "
                                 "(one 'launch' = one solve of the batch; batch_derivs_kernel dominates, see profiles/)" % (p.max_iterations + 1))
