@@ -23,6 +23,7 @@ data-path collective, so per-GPU work is fixed as N grows ("scaling": "weak").
 Nothing here reads /root/reference.  oracle/ is only executed by the cpu_baseline leg and by --impl reference.
 """
 import argparse
+import datetime
 import json
 import math
 import os
@@ -111,23 +112,68 @@ def solver_flops(N, n_obs, cost_passes, deriv_passes):
 
 # ------------------------------------------------------------------------------------------------ clocks during the timed region
 class ClockSampler:
-    """nvidia-smi sampler running DURING the timed region (B200_PROFILING.md's clocks line)."""
-    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+    """nvidia-smi sampler (B200_PROFILING.md's clocks line).  Started before the warm-up — nvidia-smi needs a second or two to
+    come up on an 8-GPU box, longer than a short timed region — and every sample carries nvidia-smi's timestamp, so that only
+    the samples taken DURING the timed region (mark_begin / mark_end) are reported.  If the region was too short to hold a
+    sample, the samples taken under load during the warm-up stand in and `window` says so."""
+    Q = ("timestamp,index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    NAMES = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
 
     def __init__(self, gpu_index):
         self.tmp = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
         self.proc = None
+        self.t0 = self.t1 = None
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(gpu_index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
                                           "-lms", "20"], stdout=self.tmp, stderr=subprocess.DEVNULL)
         except Exception:
             self.proc = None
 
-    def stop(self):
+    def mark_begin(self):
+        self.t0 = datetime.datetime.now()
+
+    def mark_end(self):
+        self.t1 = datetime.datetime.now()
+
+    @classmethod
+    def parse(cls, text):
+        """[(time or None, sm MHz, max MHz, watts, {reasons})] from the sampler's CSV."""
+        rows = []
+        for line in text.splitlines():
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 10:
+                continue
+            try:
+                sm, mx, pw = float(f[2]), float(f[3]), float(f[4])
+            except ValueError:
+                continue
+            try:
+                ts = datetime.datetime.strptime(f[0], "%Y/%m/%d %H:%M:%S.%f")
+            except ValueError:
+                ts = None
+            rows.append((ts, sm, mx, pw, {n for n, v in zip(cls.NAMES, f[6:10]) if v.lower().startswith("active")}))
+        return rows
+
+    @staticmethod
+    def summarise(rows, t0, t1):
         out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
-        if self.proc is None:
+        if not rows:
             return out
+        inside = [r for r in rows if r[0] is not None and t0 is not None and t1 is not None and t0 <= r[0] <= t1]
+        if inside:
+            use, out["window"] = inside, "timed region"
+        else:  # a region shorter than the sampling period: the samples taken under load (warm-up included)
+            top = max(r[3] for r in rows)
+            use, out["window"] = [r for r in rows if r[3] >= 0.5 * top] or rows, "no sample inside the timed region; samples under load around it"
+        out.update(sm_mhz=float(np.median([r[1] for r in use])), sm_max_mhz=float(max(r[2] for r in use)),
+                   power_w_max=float(max(r[3] for r in use)), samples=len(use))
+        out["reasons"] = sorted(set().union(*[r[4] for r in use]))
+        return out
+
+    def stop(self):
+        if self.proc is None:
+            return self.summarise([], None, None)
         self.proc.terminate()
         try:
             self.proc.wait(timeout=5)
@@ -135,27 +181,12 @@ class ClockSampler:
             self.proc.kill()
         self.tmp.flush()
         self.tmp.seek(0)
-        sm, mx, pw, reasons = [], [], [], set()
-        for line in self.tmp.read().splitlines():
-            f = [x.strip() for x in line.split(",")]
-            if len(f) < 9:
-                continue
-            try:
-                sm.append(float(f[1])); mx.append(float(f[2])); pw.append(float(f[3]))
-            except ValueError:
-                continue
-            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
-                if v.lower().startswith("active"):
-                    reasons.add(name)
+        rows = self.parse(self.tmp.read())
         try:
             os.unlink(self.tmp.name)
         except OSError:
             pass
-        if sm:
-            busy = [s for s, p in zip(sm, pw) if p >= 0.5 * max(pw)] or sm
-            out.update(sm_mhz=float(np.median(busy)), sm_max_mhz=float(max(mx)), power_w_max=float(max(pw)), samples=len(sm))
-        out["reasons"] = sorted(reasons)
-        return out
+        return self.summarise(rows, self.t0, self.t1)
 
 
 # ------------------------------------------------------------------------------------------------ CPU legs (the only users of oracle/)
@@ -341,6 +372,7 @@ def run_b200_arm(args):
     rank, local_rank, world = cdist.init_process_group("nccl")
     torch.cuda.set_device(local_rank)
     device = torch.device("cuda", local_rank)
+    sampler = ClockSampler(local_rank) if rank == 0 else None  # started here: it is up and sampling well before the timed region
     lib = cilqr_b200.load_library()
     p = cilqr_b200.Parameters()
     lib.cilqr_params_default(C.byref(p))
@@ -394,16 +426,19 @@ def run_b200_arm(args):
         step(False)
     torch.cuda.synchronize()
     launches0 = cilqr_b200.launch_count()
-    sampler = ClockSampler(local_rank) if rank == 0 else None
     if world > 1:
         torch.distributed.barrier()
     torch.cuda.synchronize()
     e0, e1 = event_pair()
+    if sampler:
+        sampler.mark_begin()
     e0.record()
     for _ in range(args.steps):
         step(True)
     e1.record()
     torch.cuda.synchronize()
+    if sampler:
+        sampler.mark_end()
     if world > 1:
         torch.distributed.barrier()
     total_ms = max_over_ranks(e0.elapsed_time(e1), world, device)

@@ -151,3 +151,31 @@ def test_receding_horizon_noise_log_and_shift(port, tmp_path):
     assert np.array_equal(rec["start_pos"][:B], x0) and np.all(rec["planning_time"] >= 0.0)
     assert np.array_equal(rec["X"][:B], np.tile(ego0, (1, N + 1)) + np.arange(4 * (N + 1)))
     assert np.array_equal(rec["start_pos"][B:2 * B], x0 + 0.1 * loop.commands[0][:, [0, 1, 0, 1]])
+
+
+def test_bench_clock_sampler_window():
+    """bench.py's nvidia-smi sampler: only samples stamped inside the timed region are reported; a region too short to hold
+    one falls back to the samples under load and says so."""
+    import datetime
+    import importlib.util
+    import os
+    spec = importlib.util.spec_from_file_location("bench_mod", os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "bench.py"))
+    bench = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bench)
+    text = "\n".join([
+        "2026/11/05 00:00:00.100, 0, 345, 1965, 140.0, 0x0000000000000001, Not Active, Not Active, Not Active, Not Active",
+        "2026/11/05 00:00:01.100, 0, 1965, 1965, 600.0, 0x0000000000000000, Not Active, Not Active, Not Active, Not Active",
+        "2026/11/05 00:00:01.120, 0, 1950, 1965, 640.0, 0x0000000000000004, Not Active, Not Active, Not Active, Active",
+        "2026/11/05 00:00:02.000, 0, 1200, 1965, 650.0, 0x0000000000000008, Active, Not Active, Not Active, Not Active",
+        "garbage line",
+    ])
+    rows = bench.ClockSampler.parse(text)
+    assert len(rows) == 4
+    t = lambda s: datetime.datetime.strptime("2026/11/05 " + s, "%Y/%m/%d %H:%M:%S.%f")
+    out = bench.ClockSampler.summarise(rows, t("00:00:01.000"), t("00:00:01.500"))
+    assert out["samples"] == 2 and out["window"] == "timed region"
+    assert out["sm_mhz"] == 1957.5 and out["sm_max_mhz"] == 1965.0 and out["reasons"] == ["sw_power_cap"]
+    out = bench.ClockSampler.summarise(rows, t("00:00:03.000"), t("00:00:03.010"))
+    assert out["samples"] == 3 and out["window"].startswith("no sample inside")
+    assert "hw_slowdown" in out["reasons"]
+    assert bench.ClockSampler.summarise([], None, None)["sm_mhz"] is None
