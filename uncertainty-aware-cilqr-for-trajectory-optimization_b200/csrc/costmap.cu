@@ -68,14 +68,6 @@ __device__ __noinline__ int source_index_exact(double p, double hL, double Ps, d
     return __double2int_rz(t);
 }
 
-__device__ __noinline__ int source_floor_exact(double p, double hL, double Ps, double r)
-{
-    const double t = -__ddiv_rn(__dsub_rn(__dsub_rn(p, hL), Ps), r);
-    if (!(fabs(t) < 2.0e9))
-        return t < 0.0 ? INT_MIN : INT_MAX;
-    return __double2int_rd(t);
-}
-
 // checkIfPositionWithinMap (GridMapMath.cpp:144-157) && checkIfIndexInRange (:191-198).  Note the different
 // subtraction order ((p - P) - 0.5*L) from the index computation.
 __device__ __forceinline__ bool source_valid_exact(const WarpGeom &G, double px, double py, int g0, int g1)
@@ -110,47 +102,54 @@ __device__ __forceinline__ void cell_position(const TileShared &T, int li, int l
 // guard band; about 3e-5 of all cells fall in the band and are recomputed exactly.
 __device__ __forceinline__ void tile_setup(const WarpGeom &G, TileShared &T, int i0, int j0, double Vx, double Vy, double sn, double cn, int tid)
 {
-    if (tid < kTile) {
-        const double Cx = cell_centre(G.base_x, G.r_t, i0 + tid);
-        T.rowC[tid] = __dmul_rn(Cx, cn);
-        T.rowS[tid] = __dmul_rn(Cx, sn);
-    } else if (tid < 2 * kTile) {
-        const int q = tid - kTile;
+    // Warps 2..5 fill the row/column products; warp 0 finds the bounding box meanwhile — one lane per tile corner and one for
+    // cell (0,0), each forming the products it needs itself (the same single rounded multiplies, so the same bits as the
+    // table entries) — and one barrier closes the setup.  (First version: thread 0 walked the four corners one after the
+    // other behind a barrier of its own; `barrier` was the kernel's top stall reason, profiles/r01h_warp_full.txt.)
+    if (tid >= 2 * 32 && tid < 2 * 32 + kTile) {
+        const int q = tid - 2 * 32;
+        const double Cx = cell_centre(G.base_x, G.r_t, i0 + q);
+        T.rowC[q] = __dmul_rn(Cx, cn);
+        T.rowS[q] = __dmul_rn(Cx, sn);
+    } else if (tid >= 2 * 32 + kTile && tid < 2 * 32 + 2 * kTile) {
+        const int q = tid - 2 * 32 - kTile;
         const double Cy = cell_centre(G.base_y, G.r_t, j0 + q);
         T.colS[q] = __dmul_rn(Cy, sn);
         T.colC[q] = __dmul_rn(Cy, cn);
-    }
-    __syncthreads();
-    if (tid == 0) {
+    } else if (tid < 32) {
         const int li1 = min(kTile, G.rows_t - i0) - 1, lj1 = min(kTile, G.cols_t - j0) - 1;
-        int lo0 = INT_MAX, lo1 = INT_MAX, hi0 = INT_MIN, hi1 = INT_MIN;
-#pragma unroll 1
-        for (int cnr = 0; cnr < 4; ++cnr) {
-            double px, py;
-            cell_position(T, (cnr & 1) ? li1 : 0, (cnr & 2) ? lj1 : 0, Vx, Vy, px, py);
-            // FLOOR of the reference's coordinate (its index truncates toward zero, which is not monotone below zero)
-            const int g0 = source_floor_exact(px, G.hLx, G.Psx, G.r_s), g1 = source_floor_exact(py, G.hLy, G.Psy, G.r_s);
-            lo0 = min(lo0, g0); hi0 = max(hi0, g0);
-            lo1 = min(lo1, g1); hi1 = max(hi1, g1);
-        }
-        const double mag = G.mag + (fabs(Vx) + fabs(Vy)) * G.rinv_s;
-        bool exact_only = !(mag < kMaxCells) || !(G.ratio <= 1.0 + 1e-9);
-        // TMA needs the innermost start coordinate on a 16-byte boundary (a misaligned one raises "illegal instruction",
-        // measured on B200): round index 0 down to a multiple of 4 floats (two's complement: right for negatives too).
-        if (!exact_only) {
-            lo0 &= ~3;
-            exact_only = (long long)hi0 - lo0 >= kBoxW || (long long)hi1 - lo1 >= kBoxH;
-        }
-        if (exact_only) { lo0 = 0; lo1 = 0; }
-        double px, py;
-        cell_position(T, 0, 0, Vx, Vy, px, py);
+        // lanes 0..3: corners; lane 4 (and the idle lanes, harmlessly): cell (0,0)
+        const int li = (tid < 4 && (tid & 1)) ? li1 : 0, lj = (tid < 4 && (tid & 2)) ? lj1 : 0;
+        const double Cx = cell_centre(G.base_x, G.r_t, i0 + li), Cy = cell_centre(G.base_y, G.r_t, j0 + lj);
+        const double px = __dadd_rn(__dsub_rn(__dmul_rn(Cx, cn), __dmul_rn(Cy, sn)), Vx); // cell_position, local_costmap.cpp:249-250
+        const double py = __dadd_rn(__dadd_rn(__dmul_rn(Cx, sn), __dmul_rn(Cy, cn)), Vy);
         const double tx = -__ddiv_rn(__dsub_rn(__dsub_rn(px, G.hLx), G.Psx), G.r_s), ty = -__ddiv_rn(__dsub_rn(__dsub_rn(py, G.hLy), G.Psy), G.r_s);
-        T.Tx0 = exact_only ? 0u : (unsigned)__double2ll_rd((tx - (double)lo0) * (double)(1u << kFrac));
-        T.Ty0 = exact_only ? 0u : (unsigned)__double2ll_rd((ty - (double)lo1) * (double)(1u << kFrac));
-        T.org0 = lo0;
-        T.org1 = lo1;
-        T.exact_only = exact_only ? 1 : 0;
-        T.inside = (!exact_only && lo0 >= 0 && lo1 >= 0 && lo0 + kBoxW <= G.rows_s && lo1 + kBoxH <= G.cols_s) ? 1 : 0;
+        // FLOOR of the reference's coordinate (its index truncates toward zero, which is not monotone below zero)
+        const int g0 = !(fabs(tx) < 2.0e9) ? (tx < 0.0 ? INT_MIN : INT_MAX) : __double2int_rd(tx);
+        const int g1 = !(fabs(ty) < 2.0e9) ? (ty < 0.0 ? INT_MIN : INT_MAX) : __double2int_rd(ty);
+        int lo0 = g0, hi0 = g0, lo1 = g1, hi1 = g1; // lanes >= 4 repeat corner 0: neutral in the min / max
+#pragma unroll
+        for (int d = 1; d < 4; d <<= 1) {
+            lo0 = min(lo0, __shfl_xor_sync(0xffffffffu, lo0, d)); hi0 = max(hi0, __shfl_xor_sync(0xffffffffu, hi0, d));
+            lo1 = min(lo1, __shfl_xor_sync(0xffffffffu, lo1, d)); hi1 = max(hi1, __shfl_xor_sync(0xffffffffu, hi1, d));
+        }
+        if (tid == 0) {
+            const double mag = G.mag + (fabs(Vx) + fabs(Vy)) * G.rinv_s;
+            bool exact_only = !(mag < kMaxCells) || !(G.ratio <= 1.0 + 1e-9);
+            // TMA needs the innermost start coordinate on a 16-byte boundary (a misaligned one raises "illegal instruction",
+            // measured on B200): round index 0 down to a multiple of 4 floats (two's complement: right for negatives too).
+            if (!exact_only) {
+                lo0 &= ~3;
+                exact_only = (long long)hi0 - lo0 >= kBoxW || (long long)hi1 - lo1 >= kBoxH;
+            }
+            if (exact_only) { lo0 = 0; lo1 = 0; }
+            T.Tx0 = exact_only ? 0u : (unsigned)__double2ll_rd((tx - (double)lo0) * (double)(1u << kFrac));
+            T.Ty0 = exact_only ? 0u : (unsigned)__double2ll_rd((ty - (double)lo1) * (double)(1u << kFrac));
+            T.org0 = lo0;
+            T.org1 = lo1;
+            T.exact_only = exact_only ? 1 : 0;
+            T.inside = (!exact_only && lo0 >= 0 && lo1 >= 0 && lo0 + kBoxW <= G.rows_s && lo1 + kBoxH <= G.cols_s) ? 1 : 0;
+        }
     }
     __syncthreads();
 }
