@@ -45,7 +45,7 @@ N_OBS = 20
 BATCH_PER_GPU = 65536
 WARP_T = 2048          # config 5 grid edge timed by the default run (source 2T x 2T = 67 MB, poses x 16.8 MB targets)
 WARP_POSES = 1024      # BASELINE config 5: 1024 poses, processed in chunks
-WARP_CHUNK = 64
+WARP_CHUNK_BYTES = 2 << 30   # poses per costmap_warp_batch call: as many as fit 2 GiB of value + index maps (64 at T = 2048), at most all 1024
 
 
 def parse_args():
@@ -293,7 +293,7 @@ def bench_warp(args, device, hbm_peak, peak_kind):
     G = cilqr_b200.CostmapGeom
     sg, tg = G(S * 0.2, S * 0.2, 0.2, 0.0, 0.0), G(T * 0.2, T * 0.2, 0.2, 0.0, 0.0)
     src = torch.from_numpy(scenarios.make_source_map(S, S, nan_band=False)).to(device)
-    chunk = max(1, min(WARP_CHUNK, (3 << 30) // (T * T * 8)))
+    chunk = max(1, min(WARP_POSES, WARP_CHUNK_BYTES // (T * T * 8)))
     poses = torch.from_numpy(scenarios.make_poses(WARP_POSES, (0.0, 0.0), 0.05 * T * 0.2)).to(device)
     out = torch.empty((chunk, T * T), dtype=torch.float32, device=device)
     idx = torch.empty((chunk, T * T), dtype=torch.int32, device=device)
