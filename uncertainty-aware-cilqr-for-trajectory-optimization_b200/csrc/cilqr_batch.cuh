@@ -353,17 +353,36 @@ __global__ void __launch_bounds__(256) batch_output_kernel(DevParams P, BatchVie
 constexpr int kCostThreads = 256;
 __host__ __device__ inline int cost_entries_per_cta(int N) { return N >= kCostThreads ? 1 : (kCostThreads / N < 32 ? kCostThreads / N : 32); }
 
-// Dynamic shared memory: entries_per_cta * N doubles (the per-step cost terms of the CTA's scenarios).
+// Dynamic shared memory: 2 x entries_per_cta * N doubles (the per-step cost terms of the CTA's scenarios, two buffers: warp 0
+// closes group g from one buffer while the other warps already fill the other with group g + 1, so there is one barrier per
+// group — the buffer of group g is written again by group g + 2, after the barrier of g + 1, which warp 0 reaches only when it
+// has finished reading).
 __global__ void __launch_bounds__(kCostThreads) batch_cost_kernel(DevParams P, BatchView V, int round)
 {
     TraceScope trace_scope(V, TRACE_COST, round);
-    extern __shared__ double sJ[];
+    extern __shared__ double sJ2[];
     const int N = P.N;
     const int E = cost_entries_per_cta(N);
+    int buf = 0;
     const int cnt = V.cnt[round];
     const int *list = V.list(round);
     const int tid = threadIdx.x;
     for (int first = blockIdx.x * E; first < cnt; first += gridDim.x * E) {
+        // The threads that will close the group's scenarios after the barrier fetch what they need of the headers now: the
+        // loads are in flight during the per-step pass instead of stalling the whole CTA behind the barrier (nothing in this
+        // kernel writes these fields before then).
+        int b_sel = -1;
+        int2 im_sel = make_int2(0, MODE_DONE);
+        double lamb_sel = 0.0, jold_sel = 0.0;
+        double *sJ = sJ2 + (size_t)buf * E * N;
+        buf ^= 1;
+        if (tid < E && first + tid < cnt) {
+            b_sel = list[first + tid];
+            double *h = V.header(b_sel);
+            im_sel = hdr_ints(h, H_ITERS_MODE);
+            lamb_sel = h[H_LAMB];
+            jold_sel = h[H_JOLD];
+        }
         // ---- Constraints::get_J term of step t (Constraints.cpp:547-558) and the tracking part of l_x (Constraints.cpp:160-176)
         for (int idx = tid; idx < E * N; idx += kCostThreads) {
             const int e = idx / N, t = idx - e * N;
@@ -400,23 +419,33 @@ __global__ void __launch_bounds__(kCostThreads) batch_cost_kernel(DevParams P, B
             bool accepted = false;
             int b = -1;
             if (tid < E && first + tid < cnt) {
-                b = list[first + tid];
+                b = b_sel;
                 double *h = V.header(b);
-                int2 im = hdr_ints(h, H_ITERS_MODE);
+                int2 im = im_sel;
                 if (im.y == MODE_LS) {
                     accepted = true; // line search: the accept decision is taken by ls_select_kernel; this pass only compacts the list
                 } else if (im.y != MODE_DONE) {
                     double J = 0.0; // J += x_cost + u_cost, t ascending (Constraints.cpp:558)
                     const double *sj = sJ + tid * N;
-                    for (int t = 0; t < N; ++t)
+                    int t = 0;
+                    for (; t + 10 <= N; t += 10) { // ten loads in flight, then the ten additions in order
+                        double v[10];
+#pragma unroll
+                        for (int k = 0; k < 10; ++k)
+                            v[k] = sj[t + k];
+#pragma unroll
+                        for (int k = 0; k < 10; ++k)
+                            J += v[k];
+                    }
+                    for (; t < N; ++t)
                         J += sj[t];
                     if (im.y == MODE_FINAL) { // J = get_J(X_result, U_result)
                         h[H_JRES] = J;
                         im.y = MODE_DONE;
                     } else {
                         int iters = im.x + 1;
-                        double lamb = h[H_LAMB];
-                        const double J_old = h[H_JOLD];
+                        double lamb = lamb_sel;
+                        const double J_old = jold_sel;
                         if (!(J < J_old)) {
                             // rejected (iLQR.cpp:229-236): J_new is the cost of the CURRENT nominal (:217), which never changes again,
                             // so every later iteration rejects too — only lamb and the iteration counter advance
@@ -451,7 +480,6 @@ __global__ void __launch_bounds__(kCostThreads) batch_cost_kernel(DevParams P, B
                     V.list(round + 1)[base + __popc(m & ((1u << tid) - 1u))] = b;
             }
         }
-        __syncthreads();
     }
 }
 

@@ -506,7 +506,7 @@ int cilqr_create(const cilqr_params *p, int max_batch, int max_obs, cilqr_handle
     CILQR_CUDA(cudaFuncSetAttribute(solve_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     CILQR_CUDA(cudaFuncSetAttribute(stage_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     {
-        const size_t cost_smem = (size_t)cost_entries_per_cta(h->dp.N) * h->dp.N * sizeof(double);
+        const size_t cost_smem = 2 * (size_t)cost_entries_per_cta(h->dp.N) * h->dp.N * sizeof(double); // two buffers, see batch_cost_kernel
         if (cost_smem > 48 * 1024)
             CILQR_CUDA(cudaFuncSetAttribute(batch_cost_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cost_smem));
         CILQR_CUDA(cudaDeviceGetAttribute(&h->smem_per_sm, cudaDevAttrMaxSharedMemoryPerMultiprocessor, dev));
@@ -684,7 +684,7 @@ static int issue_rounds(cilqr_handle h, const SolveArgs &A, const HostIO *io, cu
     const bool staged = h->obs_cv && n_obs > 0 && h->deriv_staged && 2 * (deriv_stage_bytes(n_obs) + 1024) <= (size_t)h->smem_per_sm;
     // persistent grids sized once per chunk; later rounds find shorter lists and leave early
     const int E = cost_entries_per_cta(N);
-    const size_t cost_smem = (size_t)E * N * sizeof(double);
+    const size_t cost_smem = 2 * (size_t)E * N * sizeof(double);
     // Chunk after chunk in issue order, earlier chunks on higher-priority streams: chunk c runs ahead of chunk c+1, so its
     // short latency-bound late rounds run under the next chunk's full early rounds, and with host buffers its results travel
     // back while the later chunks are still iterating.
@@ -887,7 +887,7 @@ static int solve_rounds_ls(cilqr_handle h, const SolveArgs &A, cudaStream_t st)
     CILQR_LAUNCH_CHECK();
     const bool staged = h->obs_cv && n_obs > 0 && h->deriv_staged && 2 * (deriv_stage_bytes(n_obs) + 1024) <= (size_t)h->smem_per_sm;
     const int E = cost_entries_per_cta(N);
-    const size_t cost_smem = (size_t)E * N * sizeof(double);
+    const size_t cost_smem = 2 * (size_t)E * N * sizeof(double);
     const int cost_grid = std::min((B + E - 1) / E, h->num_sms * h->occ_cost);
     const long long items = (long long)B * N;
     const int deriv_grid = (int)std::min<long long>((items + kDerivThreads - 1) / kDerivThreads, (long long)h->num_sms * h->occ_deriv);
