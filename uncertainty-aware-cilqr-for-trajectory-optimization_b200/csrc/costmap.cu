@@ -305,7 +305,7 @@ __global__ void __launch_bounds__(kWarpThreads, 4) warp_direct_kernel(const __gr
 
 __device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
 
-__global__ void __launch_bounds__(kWarpThreads, 4) warp_tma_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ WarpGeom G,
+__global__ void __launch_bounds__(kWarpThreads, 5) warp_tma_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ WarpGeom G,
                                                                 const float *__restrict__ src, const double *__restrict__ poses,
                                                                 const float *__restrict__ bbox, float *__restrict__ out,
                                                                 int32_t *__restrict__ idx)
