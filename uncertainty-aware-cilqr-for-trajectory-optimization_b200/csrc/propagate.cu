@@ -115,11 +115,18 @@ __device__ __forceinline__ bool index_from_position(const PropGeom &G, double x,
     return qx >= 0.0 && qy >= 0.0 && qx < G.Lx && qy < G.Ly && i0 >= 0 && i1 >= 0 && i0 < G.rows && i1 < G.cols;
 }
 
-__global__ void __launch_bounds__(128) propagate_kernel(const PropGeom G, const float *__restrict__ map, double sn, double cn, double sigma_x,
+constexpr int kPropThreads = 64; // small blocks: the per-cell work varies by two orders of magnitude across the map
+__global__ void __launch_bounds__(kPropThreads) propagate_kernel(const PropGeom G, const float *__restrict__ map, double sn, double cn, double sigma_x,
                                                         double sigma_y, double sigma_theta, int index, int n, int32_t *__restrict__ count,
                                                         double *__restrict__ value)
 {
-    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    // The work of a cell grows with the square of its distance from the map origin (the heading sigma's lever arm sets the
+    // ellipse), so in linear cell order both ends of the grid are heavy and the middle is light.  Blocks are dealt from the two
+    // ends inwards — even block ids from the front, odd ones from the back — so the heavy cells start first and the light ones
+    // fill the tail; the cells a block owns and everything computed for them are unchanged.
+    const int half = blockIdx.x >> 1;
+    const int blk = (blockIdx.x & 1) ? (int)gridDim.x - 1 - half : half;
+    const int k = blk * blockDim.x + threadIdx.x;
     if (k >= n)
         return;
     const int l = index + k, ci = l % G.rows, cj = l / G.rows; // GridMapIterator order: linear, column-major
@@ -161,6 +168,8 @@ __global__ void __launch_bounds__(128) propagate_kernel(const PropGeom G, const 
     const double sxx = sxi * sxi, sxy = sxi * syi, syy = syi * syi;
     double numerator = 0, denominator = 0;
     int cnt = 0;
+    const double inv_sas0 = 1.0 / sas0, inv_sas1 = 1.0 / sas1;
+    const bool centre_exact = (fabs(G.Px) + G.Lx) < 1.0995e12 * G.r && (fabs(G.Py) + G.Ly) < 1.0995e12 * G.r; // 2^40 cells
     for (int a0 = 0; a0 < n0; ++a0) { // SubmapIterator order: index 1 fastest (GridMapMath.cpp:459-488)
         const int i0 = s0 + a0;
         if (i0 < 0 || i0 >= G.rows) continue;
@@ -172,11 +181,25 @@ __global__ void __launch_bounds__(128) propagate_kernel(const PropGeom G, const 
             const double py = (G.Py + G.offy) + G.r * (double)(-i1);
             const double dy = py - Cy;
             const double q0 = cosR * dx + sinR * dy, q1 = sinR * dx + (-cosR) * dy; // transformMatrix_ (EllipseIterator.cpp:25)
-            if (!(q0 * q0 / sas0 + q1 * q1 / sas1 <= 1)) continue;                  // isInside (:80-86)
+            // isInside (:80-86): q0^2/sas0 + q1^2/sas1 <= 1.  The two IEEE divisions are only needed when the sum is within
+            // 1e-9 of the threshold; everywhere else a reciprocal-multiply estimate (off by a few ulp) gives the same decision.
+            const double est = q0 * q0 * inv_sas0 + q1 * q1 * inv_sas1;
+            bool inside = est <= 1.0;
+            if (!(fabs(est - 1.0) > 1e-9)) // near the border, or NaN
+                inside = q0 * q0 / sas0 + q1 * q1 / sas1 <= 1;
+            if (!inside) continue;
             const double f = pref * exp(ecoef * ((dx * dx / sxx - 2 * rho * dx * dy / sxy) + dy * dy / syy)); // nomal2
-            int j0, j1;
-            float mv = __int_as_float(0x7fc00000);
-            if (index_from_position(G, px, py, j0, j1)) mv = __ldg(map + j0 + G.rows * j1); // atPosition (GridMap.cpp:160-166)
+            // atPosition (GridMap.cpp:160-166) of a cell CENTRE: the reference's position -> index chain lands half a cell
+            // away from every border, so for any geometry whose coordinates stay below 2^40 cells its result is (i0, i1)
+            // itself (rounding moves it by < 2^-10 cell); beyond that the chain is evaluated as written.
+            float mv;
+            if (centre_exact) {
+                mv = __ldg(map + i0 + G.rows * i1);
+            } else {
+                int j0, j1;
+                mv = __int_as_float(0x7fc00000);
+                if (index_from_position(G, px, py, j0, j1)) mv = __ldg(map + j0 + G.rows * j1);
+            }
             numerator += f * mv; // float promoted to double, as in the reference expression
             denominator += f;
             cnt++;
@@ -232,7 +255,7 @@ extern "C" int costmap_propagate_uncertainty(const float *map, const costmap_geo
         d_count = g_pw.count.as<int32_t>();
         d_value = g_pw.value.as<double>();
     }
-    propagate_kernel<<<(n + 127) / 128, 128, 0, st>>>(G, d_map, sin_theta, cos_theta, sigma_x, sigma_y, sigma_theta, index, n, d_count, d_value);
+    propagate_kernel<<<(n + kPropThreads - 1) / kPropThreads, kPropThreads, 0, st>>>(G, d_map, sin_theta, cos_theta, sigma_x, sigma_y, sigma_theta, index, n, d_count, d_value);
     CILQR_LAUNCH_CHECK();
     if (mem == CILQR_MEM_HOST) {
         CILQR_CUDA(cudaMemcpyAsync(count, d_count, (size_t)n * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
