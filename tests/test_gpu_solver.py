@@ -425,6 +425,35 @@ def test_full_size_properties_config4_shard(checker):
     s.close()
 
 
+def test_config4_parity_across_all_rank_shards(checker):
+    """512 consecutive scenarios from each of the 8 rank shards of config 4 (ids g * 65 536 + 30 000 ...: 4 096 solves, 20
+    uncertain obstacles, N = 50), every one against the checker on all host threads: U*, X* and J within 1e-9 relative, and
+    no scenario may take a different accept / reject path (which would show up as a difference of order one)."""
+    import torch
+    if not hasattr(checker, "solve_batch"):
+        pytest.skip("needs a batch checker")
+    p = checker.params_default(horizon=50)
+    per, n_obs = 512, 20
+    dev = torch.device("cuda:0")
+    s = cilqr_b200.iLQR(p, max_batch=per, max_obs=n_obs)
+    worst = 0.0
+    for g in range(8):
+        sc = scenarios.make_scenarios(p, g * 65536 + 30000, per, n_obs, dense=True)
+        t = {k: torch.from_numpy(sc[k]).to(dev) for k in ("x0", "U0", "poly", "xlp", "obs_state0", "obs_LW", "obs_sigma")}
+        s.set_obstacles_cv(t["obs_state0"], t["obs_LW"], t["obs_sigma"], sc["kappa"])
+        U = t["U0"].clone()
+        s.get_optimal_control_seq(t["x0"], U, t["poly"], t["xlp"])
+        Uh, Xh, Jh = U.cpu().numpy(), s.X_result.cpu().numpy(), s.J_result.cpu().numpy()
+        r = checker.solve_batch(p, per, n_obs, sc["dim"], sc["pos"], sc["x0"], sc["U0"], sc["poly"], sc["xlp"])
+        for b in range(per):
+            eu, ex = rel(Uh[b], r["U"][b]), rel(Xh[b], r["X"][b])
+            ej = abs(Jh[b] - r["J"][b]) / abs(r["J"][b])
+            assert eu < TOL and ex < TOL and ej < TOL, (g, b, eu, ex, ej)
+            worst = max(worst, eu, ex, ej)
+    s.close()
+    print("config 4, 4096 scenarios over 8 shards: worst relative difference %.3g" % worst)
+
+
 # ------------------------------------------------------------------------------------------------ row N1: LocalPlanner on the device
 @pytest.mark.parametrize("curved", [False, True])
 def test_local_planner_on_device_matches_reference(checker, curved):
