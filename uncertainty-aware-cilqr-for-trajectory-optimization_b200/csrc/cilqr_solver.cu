@@ -16,6 +16,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <new>
+#include <mutex>
 #include <vector>
 
 namespace cilqr
@@ -322,6 +323,8 @@ struct cilqr_solver {
     int *last_cnt = nullptr;     // work-list lengths of the last batch-synchronous solve (device), one block per chunk
     int last_chunks = 1;
     int force_chunks = 0;        // CILQR_CHUNKS: override the number of chunks (A/B switch)
+    int exclusive = -1;          // host-buffer solves take the process-wide compute token (see issue_rounds); -1 = decide per call
+    cudaEvent_t ev_in = nullptr, ev_kdone = nullptr;
     bool deriv_staged = true;    // CILQR_DERIV_STAGED=0: plain loads for the 1/b^2 stream (A/B switch)
     int smem_per_sm = 0;
     bool trace_on = false;       // CILQR_TRACE=1: kernels record their start / end times (cilqr_solve_trace)
@@ -530,6 +533,7 @@ int cilqr_create(const cilqr_params *p, int max_batch, int max_obs, cilqr_handle
         if (v == 1 || v == 3) h->variant = v;
     }
     if (const char *e = getenv("CILQR_CHUNKS")) h->force_chunks = std::max(0, atoi(e));
+    if (const char *e = getenv("CILQR_EXCLUSIVE")) h->exclusive = atoi(e) != 0;
     if (const char *e = getenv("CILQR_GRAPH")) h->use_graph = atoi(e) != 0;
     if (const char *e = getenv("CILQR_DERIV_STAGED")) h->deriv_staged = atoi(e) != 0;
     if (const char *e = getenv("CILQR_TRACE")) h->trace_on = atoi(e) != 0;
@@ -565,6 +569,8 @@ int cilqr_destroy(cilqr_handle h)
         if (h->chunk_stream[c]) cudaStreamDestroy(h->chunk_stream[c]);
         if (h->ev_join[c]) cudaEventDestroy(h->ev_join[c]);
     }
+    if (h->ev_in) cudaEventDestroy(h->ev_in);
+    if (h->ev_kdone) cudaEventDestroy(h->ev_kdone);
     if (h->ev_fork) cudaEventDestroy(h->ev_fork);
     if (h->ev_copied) cudaEventDestroy(h->ev_copied);
     if (h->graph_exec) cudaGraphExecDestroy(h->graph_exec);
@@ -653,6 +659,8 @@ static int need_obstacles(cilqr_handle h, int B)
 // latency-bound (a sweep over a few thousand scenarios takes as long as the dependent chain of one thread), so the chunks'
 // sweeps, cost and derivative kernels overlap each other; (2) with host buffers each chunk's host->device copies, rounds and
 // device->host copies form a pipeline, so PCIe transfers run under the other chunks' kernels.
+static std::mutex g_compute_token;
+
 struct HostIO { // caller's host arrays (CILQR_MEM_HOST) — null members when the caller's buffers are device memory
     const double *x0 = nullptr, *U_in = nullptr, *poly = nullptr, *xlp = nullptr;
     double *U = nullptr, *X = nullptr, *J = nullptr;
@@ -670,6 +678,12 @@ static int issue_rounds(cilqr_handle h, const SolveArgs &A, const HostIO *io, cu
     const double *ocv = h->obs_b.as<double>(), *oib2 = ocv ? ocv + (size_t)B * n_obs * CV_FIELDS : nullptr, *orec = h->obs.as<double>();
     const size_t trace_per_chunk = (size_t)n_cnt * kTraceKinds * 2;
     if (h->trace_on) CILQR_CUDA(cudaMemsetAsync(h->trace.p, 0xff, (size_t)kMaxChunks * trace_per_chunk * sizeof(unsigned long long), st));
+    // Compute token (host buffers, one chunk, direct launches): several handles driven from several host threads would otherwise
+    // interleave their round kernels on the GPU — every solve takes longer and all of them finish, and copy their results back,
+    // at about the same time.  With the token the solves' kernels run one handle after the other at full speed, and a handle's
+    // host<->device copies run under the other handles' kernels.
+    const bool token = io && K == 1 && h->exclusive == 1;
+    std::unique_lock<std::mutex> compute_token(g_compute_token, std::defer_lock);
     cudaStream_t cs[kMaxChunks];
     if (K == 1) {
         cs[0] = st;
@@ -710,6 +724,11 @@ static int issue_rounds(cilqr_handle h, const SolveArgs &A, const HostIO *io, cu
             CILQR_CUDA(cudaMemcpyAsync(const_cast<double *>(A.poly) + P.npoly * so, io->poly + P.npoly * so, sb * P.npoly * sizeof(double), cudaMemcpyHostToDevice, cs[c]));
             CILQR_CUDA(cudaMemcpyAsync(const_cast<double *>(A.xlp) + 2 * so, io->xlp + 2 * so, sb * 2 * sizeof(double), cudaMemcpyHostToDevice, cs[c]));
         }
+        if (token) { // inputs are on the device before the token is taken: the copy runs under another handle's kernels
+            CILQR_CUDA(cudaEventRecord(h->ev_in, cs[c]));
+            CILQR_CUDA(cudaEventSynchronize(h->ev_in));
+            compute_token.lock();
+        }
         CILQR_CUDA(cudaMemsetAsync(v.cnt, 0, (size_t)n_cnt * sizeof(int), cs[c]));
         batch_init_kernel<<<(b + kInitThreads - 1) / kInitThreads, kInitThreads, 0, cs[c]>>>(P, v, b, A.x0 + 4 * so, A.U + 2 * N * so, A.poly + P.npoly * so, A.xlp + 2 * so, MODE_ITERATE);
         CILQR_LAUNCH_CHECK();
@@ -736,6 +755,7 @@ static int issue_rounds(cilqr_handle h, const SolveArgs &A, const HostIO *io, cu
             P, v, b, A.U + 2 * N * so, A.X ? A.X + 4 * (N + 1) * so : nullptr, A.J ? A.J + so : nullptr, A.iters ? A.iters + so : nullptr,
             A.status ? A.status + so : nullptr);
         CILQR_LAUNCH_CHECK();
+        if (token) CILQR_CUDA(cudaEventRecord(h->ev_kdone, cs[c]));
         if (io) { // this chunk's results: staging -> host
             CILQR_CUDA(cudaMemcpyAsync(io->U + 2 * N * so, A.U + 2 * N * so, sb * 2 * N * sizeof(double), cudaMemcpyDeviceToHost, cs[c]));
             if (io->X) CILQR_CUDA(cudaMemcpyAsync(io->X + 4 * (N + 1) * so, A.X + 4 * (N + 1) * so, sb * 4 * (N + 1) * sizeof(double), cudaMemcpyDeviceToHost, cs[c]));
@@ -746,6 +766,10 @@ static int issue_rounds(cilqr_handle h, const SolveArgs &A, const HostIO *io, cu
         if (K > 1) {
             CILQR_CUDA(cudaEventRecord(h->ev_join[c], cs[c]));
             CILQR_CUDA(cudaStreamWaitEvent(st, h->ev_join[c], 0));
+        }
+        if (token) { // the kernels are done: the next handle may start while this one's results travel back
+            CILQR_CUDA(cudaEventSynchronize(h->ev_kdone));
+            compute_token.unlock();
         }
     }
     return 0;
@@ -781,6 +805,7 @@ static int solve_rounds(cilqr_handle h, const SolveArgs &A, const HostIO *io, cu
     // chunks pay off when there are transfers to hide; on device buffers the rounds of one chunk already fill the GPU
     int K = io ? (B >= 16384 ? 4 : (B >= 2048 ? 2 : 1)) : 1;
     if (h->force_chunks > 0) K = std::min(h->force_chunks, kMaxChunks);
+    if (io && h->exclusive == 1) K = 1;
     const int Bc = ((B + K - 1) / K + 31) / 32 * 32; // chunk size, a multiple of the warp size
     K = (B + Bc - 1) / Bc;
     const size_t n_dbl = (size_t)B * kHdrD + (size_t)B * (N + 1) * kStepD;
@@ -797,6 +822,11 @@ static int solve_rounds(cilqr_handle h, const SolveArgs &A, const HostIO *io, cu
         for (const void *q : {(const void *)io->x0, (const void *)io->U, (const void *)io->poly, (const void *)io->xlp, (const void *)io->X,
                               (const void *)io->J, (const void *)io->iters, (const void *)io->status})
             key.push_back((uintptr_t)q);
+    if (io && h->exclusive == 1) { // the token is taken and released by host code between the launches: no graph
+        if (!h->ev_in) CILQR_CUDA(cudaEventCreateWithFlags(&h->ev_in, cudaEventDisableTiming));
+        if (!h->ev_kdone) CILQR_CUDA(cudaEventCreateWithFlags(&h->ev_kdone, cudaEventDisableTiming));
+        return issue_rounds(h, A, io, st, K, Bc);
+    }
     if (h->graph_exec && key == h->graph_key) {
         CILQR_CUDA(cudaGraphLaunch(h->graph_exec, st));
         g_launches.fetch_add(h->graph_kernels, std::memory_order_relaxed);
