@@ -294,11 +294,17 @@ def test_solve_trace_lists_every_launch_in_order(monkeypatch, checker):
     s2.close()
 
 
-def test_two_host_threads_two_handles_give_the_single_thread_bits():
+@pytest.mark.parametrize("token", [False, True])
+def test_two_host_threads_two_handles_give_the_single_thread_bits(monkeypatch, token):
     """Handles are independent: two host threads, one handle and one stream each, blocking host-buffer calls in a loop
-    (the way bench.py's end-to-end leg hides PCIe time) — every result equals the one-thread result."""
+    (the way bench.py's end-to-end leg hides PCIe time) — every result equals the one-thread result.  With the opt-in compute
+    token (CILQR_EXCLUSIVE=1, read when a handle is created) the two handles' kernels take turns; same bits."""
     import threading
     import torch
+    if token:
+        monkeypatch.setenv("CILQR_EXCLUSIVE", "1")
+    else:
+        monkeypatch.delenv("CILQR_EXCLUSIVE", raising=False)
     p = cilqr_b200.Parameters()
     cilqr_b200.load_library().cilqr_params_default(__import__("ctypes").byref(p))
     p = p.replace(horizon=50)
