@@ -166,6 +166,15 @@ int cilqr_solve_batch(cilqr_handle h, int B, const double *x0, double *U, const 
 int cilqr_solve_stats(cilqr_handle h, int64_t *cost_passes, int64_t *deriv_passes, int32_t *rounds,
                       void *stream);
 
+/* Several handles driven from several host threads with host buffers (CILQR_MEM_HOST): with `on` != 0 this handle's
+ * cilqr_solve_batch calls copy their inputs, take a process-wide compute token, run their rounds (one chunk, direct launches),
+ * release the token when the last kernel has finished and then copy the results back — the handles' kernels run one solve after
+ * the other at full speed, their copies under each other's kernels.  Off by default (a single caller is faster with the
+ * chunked, graph-replayed path); CILQR_EXCLUSIVE=1 in the environment turns it on for every handle created afterwards.
+ * Results are bit-identical either way.  No reference counterpart (the reference's node is single-threaded,
+ * ilqr_uncertainty_node.cpp:111-130). */
+int cilqr_set_compute_token(cilqr_handle h, int on);
+
 /* Diagnostics: timeline of the last batch-synchronous solve on a handle created with CILQR_TRACE=1 in the environment.
  * out[chunk][round][kind][2] (kind 0 cost, 1 derivatives, 2 sweep, 3 init (round 0) / output (round 1)): %globaltimer
  * nanoseconds of the first CTA's start and the last CTA's end of that launch, 0 when it did not run.  *rounds receives the

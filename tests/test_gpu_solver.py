@@ -298,13 +298,10 @@ def test_solve_trace_lists_every_launch_in_order(monkeypatch, checker):
 def test_two_host_threads_two_handles_give_the_single_thread_bits(monkeypatch, token):
     """Handles are independent: two host threads, one handle and one stream each, blocking host-buffer calls in a loop
     (the way bench.py's end-to-end leg hides PCIe time) — every result equals the one-thread result.  With the opt-in compute
-    token (CILQR_EXCLUSIVE=1, read when a handle is created) the two handles' kernels take turns; same bits."""
+    token (cilqr_set_compute_token) the two handles' kernels take turns; same bits."""
     import threading
     import torch
-    if token:
-        monkeypatch.setenv("CILQR_EXCLUSIVE", "1")
-    else:
-        monkeypatch.delenv("CILQR_EXCLUSIVE", raising=False)
+    monkeypatch.delenv("CILQR_EXCLUSIVE", raising=False)
     p = cilqr_b200.Parameters()
     cilqr_b200.load_library().cilqr_params_default(__import__("ctypes").byref(p))
     p = p.replace(horizon=50)
@@ -323,7 +320,7 @@ def test_two_host_threads_two_handles_give_the_single_thread_bits(monkeypatch, t
     def worker(i):
         try:
             torch.cuda.set_device(0)
-            s = cilqr_b200.iLQR(p, max_batch=B, max_obs=n_obs, stream=torch.cuda.Stream())
+            s = cilqr_b200.iLQR(p, max_batch=B, max_obs=n_obs, stream=torch.cuda.Stream(), compute_token=True if token else None)
             pin = {k: torch.from_numpy(sc[i][k]).pin_memory().numpy() for k in ("x0", "U0", "poly", "xlp", "obs_state0", "obs_LW", "obs_sigma")}
             U = torch.empty((B, 2 * N), dtype=torch.float64).pin_memory().numpy()
             out = {"X": torch.empty((B, 4 * (N + 1)), dtype=torch.float64).pin_memory().numpy(), "J": torch.empty(B, dtype=torch.float64).pin_memory().numpy(),
@@ -432,14 +429,14 @@ def test_full_size_properties_config4_shard(checker):
 
 
 def test_config4_parity_across_all_rank_shards(checker):
-    """512 consecutive scenarios from each of the 8 rank shards of config 4 (ids g * 65 536 + 30 000 ...: 4 096 solves, 20
+    """256 consecutive scenarios from each of the 8 rank shards of config 4 (ids g * 65 536 + 30 000 ...: 2 048 solves, 20
     uncertain obstacles, N = 50), every one against the checker on all host threads: U*, X* and J within 1e-9 relative, and
     no scenario may take a different accept / reject path (which would show up as a difference of order one)."""
     import torch
     if not hasattr(checker, "solve_batch"):
         pytest.skip("needs a batch checker")
     p = checker.params_default(horizon=50)
-    per, n_obs = 512, 20
+    per, n_obs = 256, 20
     dev = torch.device("cuda:0")
     s = cilqr_b200.iLQR(p, max_batch=per, max_obs=n_obs)
     worst = 0.0
@@ -450,14 +447,14 @@ def test_config4_parity_across_all_rank_shards(checker):
         U = t["U0"].clone()
         s.get_optimal_control_seq(t["x0"], U, t["poly"], t["xlp"])
         Uh, Xh, Jh = U.cpu().numpy(), s.X_result.cpu().numpy(), s.J_result.cpu().numpy()
-        r = checker.solve_batch(p, per, n_obs, sc["dim"], sc["pos"], sc["x0"], sc["U0"], sc["poly"], sc["xlp"])
+        r = checker.solve_batch(p, per, n_obs, sc["dim"], sc["pos"], sc["x0"], sc["U0"], sc["poly"], sc["xlp"], threads=os.cpu_count() or 1)
         for b in range(per):
             eu, ex = rel(Uh[b], r["U"][b]), rel(Xh[b], r["X"][b])
             ej = abs(Jh[b] - r["J"][b]) / abs(r["J"][b])
             assert eu < TOL and ex < TOL and ej < TOL, (g, b, eu, ex, ej)
             worst = max(worst, eu, ex, ej)
     s.close()
-    print("config 4, 4096 scenarios over 8 shards: worst relative difference %.3g" % worst)
+    print("config 4, %d scenarios over 8 shards" % (8 * per) + ": worst relative difference %.3g" % worst)
 
 
 # ------------------------------------------------------------------------------------------------ row N1: LocalPlanner on the device

@@ -989,6 +989,13 @@ int cilqr_solve_trace(cilqr_handle h, uint64_t *out, int capacity, int32_t *chun
     return 0;
 }
 
+int cilqr_set_compute_token(cilqr_handle h, int on)
+{
+    if (!h) return fail(CILQR_E_ARG, "null handle");
+    h->exclusive = on ? 1 : 0;
+    return 0;
+}
+
 int cilqr_solve_stats(cilqr_handle h, int64_t *cost_passes, int64_t *deriv_passes, int32_t *rounds, void *stream)
 {
     if (!h) return fail(CILQR_E_ARG, "null handle");

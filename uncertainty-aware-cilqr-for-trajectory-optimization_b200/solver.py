@@ -128,16 +128,19 @@ class iLQR:
     Result members keep the reference's names: X_result, U_result (plus J_result, iterations, status);
     `control_seq` is the warm start carried between run_step() calls, un-shifted like the reference's."""
 
-    def __init__(self, params, max_batch=1, max_obs=0, stream=None):
+    def __init__(self, params, max_batch=1, max_obs=0, stream=None, compute_token=None):
         """`stream`: CUDA stream for calls with host (numpy) arrays — give every handle its own when several host threads
         drive one GPU, so that one thread's copies and kernels do not queue behind the other's (device arrays always use
-        torch's current stream)."""
+        torch's current stream).  `compute_token`: True when several such handles are solving at the same time
+        (cilqr_set_compute_token: their kernels take turns, their copies overlap); None leaves the library's default."""
         self.lib = load_library()
         self.stream = stream
         self.params = params.copy()
         self.max_batch, self.max_obs = int(max_batch), int(max_obs)
         self._h = C.c_void_p()
         _check(self.lib.cilqr_create(C.byref(self.params), C.c_int(self.max_batch), C.c_int(self.max_obs), C.byref(self._h)))
+        if compute_token is not None:
+            _check(self.lib.cilqr_set_compute_token(self._h, C.c_int(1 if compute_token else 0)))
         N = self.params.horizon
         u = np.zeros(2 * N)
         _check(self.lib.cilqr_default_controls(C.byref(self.params), u.ctypes.data_as(_dp)))
