@@ -200,6 +200,8 @@ def cpu_solver():
 
 def cpu_solve_sample(chk, p, sc, n, threads=0):
     """Times chk.solve_batch on the first n scenarios of `sc` with every host thread; returns (seconds, threads)."""
+    if threads <= 0:  # every host thread, named explicitly: torchrun exports OMP_NUM_THREADS=1 to the ranks it launches
+        threads = os.cpu_count() or 1
     t0 = time.perf_counter()
     r = chk.solve_batch(p, n, sc["n_obs"], sc["dim"][:n], sc["pos"][:n], sc["x0"][:n], sc["U0"][:n], sc["poly"][:n], sc["xlp"][:n],
                         threads=threads, want_X=False)
