@@ -62,6 +62,9 @@ def parse_args():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--e2e-threads", type=int, default=4, help="host threads (one solver handle each) in the end-to-end measurement")
+    ap.add_argument("--fused-from", type=int, default=-1, help="CILQR_OPT_FUSED_FROM_ROUND (-1 automatic, 0 fused from the start, 99 round kernels only)")
+    ap.add_argument("--fused-slots", type=int, default=0, help="CILQR_OPT_FUSED_SLOTS (0 automatic)")
+    ap.add_argument("--no-graph", action="store_true", help="CILQR_OPT_GRAPH = 0: direct launches (for ncu launch lists)")
     return ap.parse_args()
 
 
@@ -388,7 +391,9 @@ def run_b200_arm(args):
     d = {k: torch.from_numpy(sc[k]).to(device) for k in keys}
     U = torch.empty_like(d["U0"])
     gathered = torch.empty((world * B, 2 * N), dtype=torch.float64, device=device) if world > 1 else None
-    solver = cilqr_b200.iLQR(p, max_batch=B, max_obs=n_obs)
+    opts = {cilqr_b200.OPT_FUSED_FROM_ROUND: args.fused_from, cilqr_b200.OPT_FUSED_SLOTS: args.fused_slots,
+            cilqr_b200.OPT_GRAPH: 0 if args.no_graph else 1}
+    solver = cilqr_b200.iLQR(p, max_batch=B, max_obs=n_obs, options=opts)
     merit = cilqr_b200.MERIT_TOTAL if args.n_alphas > 1 else cilqr_b200.MERIT_TRACKING
     kern_ev = []
     # results in preallocated device buffers: a call that repeats the previous call's buffers replays the recorded launch graph
@@ -471,7 +476,7 @@ def run_b200_arm(args):
             def __init__(self, token=False):
                 self.stream = torch.cuda.Stream(device=device)
                 # several handles solving at once: their kernels take turns (cilqr_set_compute_token), their copies overlap
-                self.hs = cilqr_b200.iLQR(p, max_batch=B, max_obs=n_obs, stream=self.stream, compute_token=True if token else None)
+                self.hs = cilqr_b200.iLQR(p, max_batch=B, max_obs=n_obs, stream=self.stream, compute_token=True if token else None, options=opts)
                 self.Uh = torch.empty((B, 2 * N), dtype=torch.float64).pin_memory()
                 self.outs = {"X": torch.empty((B, 4 * (N + 1)), dtype=torch.float64).pin_memory().numpy(),
                              "J": torch.empty(B, dtype=torch.float64).pin_memory().numpy(),

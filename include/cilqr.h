@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define CILQR_ABI_VERSION 1
+#define CILQR_ABI_VERSION 2
 
 enum { CILQR_MEM_HOST = 0, CILQR_MEM_DEVICE = 1 };
 
@@ -111,7 +111,32 @@ int cilqr_params_default(cilqr_params *p);
 /* iLQR::iLQR(const Parameters&) (iLQR.cpp:3-19): allocates device workspaces for up to
  * max_batch scenarios with up to max_obs obstacles each. */
 int cilqr_create(const cilqr_params *p, int max_batch, int max_obs, cilqr_handle *out);
+/* The same on a given CUDA device (-1 = the calling thread's current device, which is what cilqr_create uses).  A handle
+ * stays on its device: every entry point that takes the handle switches to it for the duration of the call and restores
+ * the caller's device, so one host thread can drive one handle per GPU.  Buffers passed with CILQR_MEM_DEVICE and the
+ * stream must belong to the handle's device. */
+int cilqr_create_on(const cilqr_params *p, int max_batch, int max_obs, int device, cilqr_handle *out);
 int cilqr_destroy(cilqr_handle h);
+
+/* Scheduling options of a handle (no reference counterpart; results are bit-identical for every setting).
+ *   CILQR_OPT_FUSED_FROM_ROUND  r: cilqr_solve_batch (n_alphas = 1) runs solver rounds 0 .. r-1 as batch-synchronous
+ *                               round kernels and the rest in the fused on-chip kernel; 0 = fused from the start,
+ *                               r > max_iterations = round kernels only, -1 = automatic (default).
+ *   CILQR_OPT_FUSED_SLOTS       scenario slots per CTA of the fused kernel (0 = automatic).
+ *   CILQR_OPT_CHUNKS            number of stream chunks of a host-buffer solve (0 = automatic).
+ *   CILQR_OPT_GRAPH             0 = never record repeated solves as a CUDA graph (default 1).
+ *   CILQR_OPT_DERIV_STAGED      0 = the round kernels read the 1/b^2 stream with plain loads (default 1: cp.async staging).
+ *   CILQR_OPT_TRACE             1 = the round kernels record their start/end times for cilqr_solve_trace (default 0;
+ *                               implies round kernels only). */
+enum {
+    CILQR_OPT_FUSED_FROM_ROUND = 1,
+    CILQR_OPT_FUSED_SLOTS = 2,
+    CILQR_OPT_CHUNKS = 3,
+    CILQR_OPT_GRAPH = 4,
+    CILQR_OPT_DERIV_STAGED = 5,
+    CILQR_OPT_TRACE = 6
+};
+int cilqr_set_option(cilqr_handle h, int option, int value);
 
 /* The constructor's initial control sequence (iLQR.cpp:9-15): acc = 0.5, yaw-rate = 0 for
  * t < N/2 and 0.1 afterwards.  Pure host helper: fills U[2*N]. */
@@ -161,7 +186,7 @@ int cilqr_solve_batch(cilqr_handle h, int B, const double *x0, double *U, const 
 
 /* Work done by the last cilqr_solve_batch call with n_alphas == 1 (measurement helper, no reference counterpart): how many
  * times the cost (Constraints::get_J) and the derivative pass + backward/forward pass ran, summed over the scenarios, and
- * the number of solver rounds that had work.  The reference's own iteration counter (`iters`) also counts the iterations in
+ * the number of solver rounds that had work (round kernels) plus the largest number of iterations any CTA of the fused kernel made.  The reference's own iteration counter (`iters`) also counts the iterations in
  * which a rejected nominal only waits for lamb to exceed lamb_max; those cost nothing here.  Synchronises `stream`. */
 int cilqr_solve_stats(cilqr_handle h, int64_t *cost_passes, int64_t *deriv_passes, int32_t *rounds,
                       void *stream);
@@ -175,7 +200,7 @@ int cilqr_solve_stats(cilqr_handle h, int64_t *cost_passes, int64_t *deriv_passe
  * ilqr_uncertainty_node.cpp:111-130). */
 int cilqr_set_compute_token(cilqr_handle h, int on);
 
-/* Diagnostics: timeline of the last batch-synchronous solve on a handle created with CILQR_TRACE=1 in the environment.
+/* Diagnostics: timeline of the last batch-synchronous solve on a handle with CILQR_OPT_TRACE set.
  * out[chunk][round][kind][2] (kind 0 cost, 1 derivatives, 2 sweep, 3 init (round 0) / output (round 1)): %globaltimer
  * nanoseconds of the first CTA's start and the last CTA's end of that launch, 0 when it did not run.  *rounds receives the
  * round dimension (max_iterations + 3).  No reference counterpart (the reference times run_step with std::chrono,

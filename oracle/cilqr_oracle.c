@@ -763,9 +763,9 @@ static void propagate_cell(const float *map, const costmap_geom *g, int rows, in
     float Dmaj = major == 0 ? E.D0 : E.D1, Dmin = major == 0 ? E.D1 : E.D0;
     float Vm0 = major == 0 ? E.V00 : E.V10, Vm1 = major == 0 ? E.V01 : E.V11; /* ROW `major` of V (ARBIT.cuh:89) */
     /* ellipse_params_functor (ARBIT.cuh:84-98) */
-    double angle = atan2((double)Vm1, (double)Vm0);
+    double angle = (double)atan2f(Vm1, Vm0); /* float overload: unqualified atan2 on Matrix2f entries under `using namespace std` (ARBIT.cuh:47-48,91) */
     if (angle < 0) angle += 6.28318530718;
-    double half_major = 2.4477 * sqrt((double)Dmaj), half_minor = 2.4477 * sqrt((double)Dmin);
+    double half_major = 2.4477 * (double)sqrtf(Dmaj), half_minor = 2.4477 * (double)sqrtf(Dmin); /* ARBIT.cuh:96-97, float sqrt */
     if (ellipse) { ellipse[0] = half_major; ellipse[1] = half_minor; ellipse[2] = angle; }
     /* grid_map::EllipseIterator(map, centre, Length(2 a, 2 b), angle) — gmc/iterators/EllipseIterator.cpp:19-107 */
     const double len0 = 2 * half_major, len1 = 2 * half_minor;

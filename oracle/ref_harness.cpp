@@ -17,6 +17,7 @@
 //                       (local_costmap.cpp:517-648 + getConfidenceEllipse :410-454), driven through
 //                       the real grid_map::EllipseIterator and Eigen::EigenSolver<Matrix2f>.
 #include <algorithm>
+#include <type_traits>
 #include <cmath>
 #include <cstdint>
 #include <cstring>
@@ -674,10 +675,15 @@ extern "C"
             else { major_index = 1; minor_index = 0; }
             // ellipse_params_functor (ARBIT.cuh:84-98)
             double chisquare_val = 2.4477;
-            double angle = atan2(V(major_index, 1), V(major_index, 0));
+            // The reference calls unqualified atan2 / sqrt on FLOAT Matrix2f entries under `using namespace std`
+            // (ARBIT.cuh:47-48, 91-97; local_costmap.cpp:48, 435-443): overload resolution picks the float versions
+            // (atan2f / sqrtf), whose results are then widened to double.  Spelled out here with std:: so that this
+            // translation unit (no using-directive) resolves the same way.
+            double angle = std::atan2(V(major_index, 1), V(major_index, 0));
             if (angle < 0) angle += 6.28318530718;
-            double half_major_axis = chisquare_val * sqrt(D(major_index, major_index));
-            double half_minor_axis = chisquare_val * sqrt(D(minor_index, minor_index));
+            double half_major_axis = chisquare_val * std::sqrt(D(major_index, major_index));
+            double half_minor_axis = chisquare_val * std::sqrt(D(minor_index, minor_index));
+            static_assert(std::is_same<decltype(std::atan2(V(0, 1), V(0, 0))), float>::value, "float overload expected");
             if (ellipse)
             {
                 ellipse[3 * i + 0] = half_major_axis;

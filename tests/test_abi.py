@@ -25,7 +25,7 @@ def test_library_exports_every_declared_symbol(lib):
     assert len(names) >= 18
     for n in names:
         assert hasattr(lib, n), "libcilqr_b200.so does not export %s" % n
-    assert lib.cilqr_abi_version() == 1
+    assert lib.cilqr_abi_version() == 2
 
 
 def test_params_struct_layout_and_defaults(lib, port):

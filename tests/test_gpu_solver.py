@@ -208,8 +208,75 @@ def test_device_resident_and_host_buffers_give_identical_bits():
     s.close()
 
 
+@pytest.mark.parametrize("B,n_obs,cv,horizon", [(333, 6, True, 50), (97, 3, False, 50), (64, 0, True, 50), (41, 4, True, 33), (9, 2, False, 100)])
+def test_fused_kernel_gives_the_bits_of_the_round_kernels(B, n_obs, cv, horizon):
+    """cilqr_fused.cuh (scenario groups resident in shared memory from rollout to result) against the batch-synchronous round
+    kernels: the same per-step device functions in the same order, so U*, X*, J, iteration counts, status and the pass tallies are
+    identical — fused from the start, taking over after round 1 or 3, with 1 / 5 / automatic slots per CTA."""
+    import torch
+    p = cilqr_b200.Parameters()
+    cilqr_b200.load_library().cilqr_params_default(__import__("ctypes").byref(p))
+    p = p.replace(horizon=horizon)
+    sc = scenarios.make_scenarios(p, 2024, B, n_obs, curved=True, dense=not cv)
+    dev = torch.device("cuda:0")
+    keys = ("x0", "U0", "poly", "xlp") + (("obs_state0", "obs_LW", "obs_sigma") if cv else ("dim", "pos"))
+    t = {k: torch.from_numpy(sc[k]).to(dev) for k in keys if n_obs or not k.startswith(("obs", "dim", "pos"))}
+    ref = None
+    for r0, slots in [(99, 0), (0, 0), (0, 1), (0, 5), (1, 0), (3, 3)]:
+        s = cilqr_b200.iLQR(p, max_batch=B, max_obs=max(n_obs, 1), options={cilqr_b200.OPT_FUSED_FROM_ROUND: r0, cilqr_b200.OPT_FUSED_SLOTS: slots})
+        if n_obs:
+            if cv:
+                s.set_obstacles_cv(t["obs_state0"], t["obs_LW"], t["obs_sigma"], sc["kappa"])
+            else:
+                s.set_obstacles_dense(t["dim"], t["pos"])
+        for rep in range(3):  # direct launches, then (round kernels) the recorded graph
+            U = t["U0"].clone()
+            s.get_optimal_control_seq(t["x0"], U, t["poly"], t["xlp"])
+            torch.cuda.synchronize()
+            got = (U.cpu().numpy(), s.X_result.cpu().numpy(), s.J_result.cpu().numpy(), s.iterations.cpu().numpy(), s.status.cpu().numpy())
+            stats = s.solve_stats()[:2]
+            if ref is None:
+                ref = got + (stats,)
+            for a, b in zip(ref[:5], got):
+                assert np.array_equal(a, b), (r0, slots, rep)
+            assert stats == ref[5], (r0, slots, rep)
+        # host buffers through the same plan
+        Uh = sc["U0"].copy()
+        if n_obs:
+            if cv:
+                s.set_obstacles_cv(sc["obs_state0"], sc["obs_LW"], sc["obs_sigma"], sc["kappa"])
+            else:
+                s.set_obstacles_dense(sc["dim"], sc["pos"])
+        s.get_optimal_control_seq(sc["x0"], Uh, sc["poly"], sc["xlp"])
+        for a, b in zip(ref[:5], (Uh, s.X_result, s.J_result, s.iterations, s.status)):
+            assert np.array_equal(a, np.asarray(b)), (r0, slots, "host")
+        s.close()
+
+
+def test_two_live_handles_with_different_horizons(checker):
+    """Dynamic shared-memory limits are per kernel and process-wide: a second handle with a shorter horizon must not lower them
+    under a first one that needs more than 48 KB (N = 100, S = 200 -> 67 KB in the stage kernel)."""
+    pa, pb = checker.params_default(horizon=100), checker.params_default(horizon=20)
+    sa, sb_ = scenarios.make_scenarios(pa, 3, 5, 2), scenarios.make_scenarios(pb, 3, 5, 2)
+    a = make_solver(pa, sa, 5, 2)
+    b = make_solver(pb, sb_, 5, 2)  # created second, smaller
+    for s, p, sc in ((a, pa, sa), (b, pb, sb_), (a, pa, sa)):
+        X0 = s.get_nominal_trajectory(sc["x0"], sc["U0"])
+        lx, lxx = s.get_state_cost(X0, sc["poly"], sc["xlp"])
+        ok = s.backward_pass(X0, sc["U0"], sc["poly"], sc["xlp"], 1.0)
+        assert np.all(ok == 1) and np.isfinite(lx).all()
+        U = sc["U0"].copy()
+        s.get_optimal_control_seq(sc["x0"], U, sc["poly"], sc["xlp"])
+        r = checker.solve(p, sc["dim"][0], sc["pos"][0], sc["x0"][0], sc["U0"][0], sc["poly"][0], sc["xlp"][0])
+        assert int(s.iterations[0]) == r["iters"] and rel(U[0], r["U"]) < TOL
+        Xr = checker.rollout(p, sc["x0"][0], sc["U0"][0])
+        assert rel(X0[0], Xr) < 1e-12
+    a.close()
+    b.close()
+
+
 @pytest.mark.parametrize("chunks", [2, 3, 8])
-def test_chunked_streams_give_the_bits_of_one_stream(monkeypatch, chunks):
+def test_chunked_streams_give_the_bits_of_one_stream(chunks):
     """cilqr_solve_batch cuts the batch into chunks on internal streams (host->device copy, rounds, device->host copy per
     chunk); ragged last chunk, host and device buffers, constant-velocity obstacles: same bits as the single-stream solve."""
     import torch
@@ -220,8 +287,7 @@ def test_chunked_streams_give_the_bits_of_one_stream(monkeypatch, chunks):
     sc = scenarios.make_scenarios(p, 11, B, n_obs, curved=True, dense=False)
     out = {}
     for k in (1, chunks):
-        monkeypatch.setenv("CILQR_CHUNKS", str(k))  # read at cilqr_create
-        s = cilqr_b200.iLQR(p, max_batch=B, max_obs=n_obs)
+        s = cilqr_b200.iLQR(p, max_batch=B, max_obs=n_obs, options={cilqr_b200.OPT_CHUNKS: k, cilqr_b200.OPT_FUSED_FROM_ROUND: 99 if k == chunks else 2})
         s.set_obstacles_cv(sc["obs_state0"], sc["obs_LW"], sc["obs_sigma"], sc["kappa"])
         U = sc["U0"].copy()
         s.get_optimal_control_seq(sc["x0"], U, sc["poly"], sc["xlp"])
@@ -265,15 +331,12 @@ def test_chunked_streams_give_the_bits_of_one_stream(monkeypatch, chunks):
     assert out[1][5][:2] == out[chunks][5][:2]  # cost / derivative passes summed over the chunks
 
 
-def test_solve_trace_lists_every_launch_in_order(monkeypatch, checker):
-    """cilqr_solve_trace (CILQR_TRACE=1): one entry per launch of the last solve, rounds in order on each chunk's stream."""
+def test_solve_trace_lists_every_launch_in_order(checker):
+    """cilqr_solve_trace (OPT_TRACE): one entry per launch of the last solve, rounds in order on each chunk's stream."""
     p = checker.params_default(horizon=50)
     B, n_obs = 96, 3
     sc = scenarios.make_scenarios(p, 77, B, n_obs, dense=False)
-    monkeypatch.setenv("CILQR_TRACE", "1")
-    monkeypatch.setenv("CILQR_CHUNKS", "2")
-    s = cilqr_b200.iLQR(p, max_batch=B, max_obs=n_obs)
-    monkeypatch.delenv("CILQR_TRACE")
+    s = cilqr_b200.iLQR(p, max_batch=B, max_obs=n_obs, options={cilqr_b200.OPT_TRACE: 1, cilqr_b200.OPT_CHUNKS: 2})
     s.set_obstacles_cv(sc["obs_state0"], sc["obs_LW"], sc["obs_sigma"], sc["kappa"])
     U = sc["U0"].copy()
     s.get_optimal_control_seq(sc["x0"], U, sc["poly"], sc["xlp"])
@@ -288,7 +351,7 @@ def test_solve_trace_lists_every_launch_in_order(monkeypatch, checker):
         order = [(e[1], e[2]) for e in mine[1:-1]]
         assert order[:4] == [(0, "cost"), (0, "derivs"), (0, "sweep"), (1, "cost")]
     s2 = cilqr_b200.iLQR(p, max_batch=B, max_obs=n_obs)  # a handle created without the switch has no trace
-    with pytest.raises(cilqr_b200.CilqrError, match="CILQR_TRACE"):
+    with pytest.raises(cilqr_b200.CilqrError, match="CILQR_OPT_TRACE"):
         s2.solve_trace()
     s.close()
     s2.close()

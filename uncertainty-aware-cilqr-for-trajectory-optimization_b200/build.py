@@ -18,7 +18,7 @@ LIB = os.path.join(HERE, "libcilqr_b200.so")
 SOURCES = ["cilqr_solver.cu", "costmap.cu", "propagate.cu", "local_planner.cu", "costmap_io.cu"]
 # propagate.cu restates float/double expression chains of the reference operation by operation: no FMA contraction there
 EXTRA_FLAGS = {"propagate.cu": ["-fmad=false"]}
-HEADERS = ["common.cuh", "cilqr_device.cuh", "cilqr_batch.cuh", os.path.join("..", "..", "include", "cilqr.h")]
+HEADERS = sorted(f for f in os.listdir(CSRC) if f.endswith((".cuh", ".h"))) + [os.path.join("..", "..", "include", "cilqr.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC"]
 

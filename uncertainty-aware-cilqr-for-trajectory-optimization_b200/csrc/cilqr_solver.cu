@@ -4,13 +4,14 @@
 //   prep_obstacles_dense_kernel / prep_obstacles_cv_kernel : Obstacle ctor inputs -> per-(obstacle, t) records
 //       (x, y, cos, sin, 1/a^2, 1/b^2), Obstacle.cpp:39-48;  the _cv variant also does the covariance-inflated
 //       constant-velocity expansion on the device.
-//   solve_kernel<LS> : the fused driver iLQR::get_optimal_control_seq (iLQR.cpp:201-245), one warp per scenario,
-//       persistent CTAs pulling scenario indices from a global counter.
+//   cilqr_batch.cuh  : the batch-synchronous round kernels of iLQR::get_optimal_control_seq (iLQR.cpp:201-245)
+//   cilqr_fused.cuh  : the same solve with scenario groups resident in shared memory from rollout to result
 //   stage_kernel     : the individual reference stages behind cilqr_rollout / _state_cost / _control_cost /
-//       _cost / _backward / _forward (same device functions as the fused kernel; used by the parity tests).
+//       _cost / _backward / _forward (same device functions; used by the parity tests).
 #include "common.cuh"
 #include "cilqr_device.cuh"
 #include "cilqr_batch.cuh"
+#include "cilqr_fused.cuh"
 #include <cfloat>
 #include <cmath>
 #include <cstdlib>
@@ -40,14 +41,13 @@ __global__ void __launch_bounds__(256) fp64_peak_kernel(double *out, int iters, 
         out[0] = r; // never true: keeps the chains alive
 }
 
-// ------------------------------------------------------------------------------------------------- fused solve
+// ------------------------------------------------------------------------------------------------- solve arguments
 struct SolveArgs {
     DevParams P;
     int B, n_obs, n_alphas, merit;
     const double *x0, *poly, *xlp, *obs;
     double *U, *X, *J, *scratch;
     int32_t *iters, *status;
-    int *counter;
 };
 
 __device__ __forceinline__ void load_controls(const WarpSmem &W, const double *__restrict__ Ug, int N, int lane)
@@ -76,114 +76,6 @@ __device__ __forceinline__ void store_states(const WarpSmem &W, double *__restri
 {
     for (int i = lane; i < 4 * (N + 1); i += 32)
         Xg[i] = W.X[(i & 3) * (N + 1) + (i >> 2)];
-}
-
-template <bool LS>
-__global__ void __launch_bounds__(kWarpsPerBlock * 32, 4) solve_kernel(const SolveArgs A)
-{
-    extern __shared__ double smem[];
-    const DevParams &P = A.P;
-    const int N = P.N;
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const WarpSmem W = carve(smem + (size_t)warp * warp_smem_doubles(N, P.S), N, P.S);
-    double *cand = LS ? A.scratch + (size_t)(blockIdx.x * kWarpsPerBlock + warp) * A.n_alphas * traj_doubles(N) : nullptr;
-    const bool merit_total = A.merit == CILQR_MERIT_TOTAL;
-
-    for (;;) {
-        int b = 0;
-        if (lane == 0)
-            b = atomicAdd(A.counter, 1);
-        b = __shfl_sync(0xffffffffu, b, 0);
-        if (b >= A.B)
-            break;
-
-        Polyline pl;
-        pl.x_first = A.xlp[2 * b];
-        pl.dxs = (A.xlp[2 * b + 1] - A.xlp[2 * b]) / P.S; // Constraints.cpp:32
-        build_polyline(P, A.poly + (size_t)b * P.npoly, pl, W.Y, lane);
-        load_controls(W, A.U + (size_t)b * 2 * N, N, lane);
-        if (lane < 4)
-            W.X[lane * (N + 1)] = A.x0[4 * (size_t)b + lane];
-        __syncwarp();
-        phase_rollout(P, W, lane); // X = get_nominal_trajectory(x_0, U)   (iLQR.cpp:203)
-        const double *obs = A.obs + (size_t)b * A.n_obs * OB_FIELDS * N;
-
-        double lamb = 1.0;
-        int iters = 0, status = CILQR_ST_MAX_ITER;
-        if (!LS) {
-            // Reference semantics (iLQR.cpp:211-239).  J_new is the cost of the CURRENT nominal (:217), so the
-            // accept test is known before the candidate is rolled out: accepted -> the in-place rollout IS
-            // `X = X_new; U = U_new`; rejected -> the nominal never changes again, every later iteration
-            // rejects too (same J), so only lamb and the iteration counter advance.
-            double J_old = DBL_MAX;
-            for (int it = 0; it < P.max_iter; ++it) {
-                iters = it + 1;
-                phase_derivs<true>(P, W, pl, obs, A.n_obs, false, lane);
-                const double J_new = sum_sequential(W.Jt, N);
-                if (!(J_new < J_old)) {
-                    lamb = lamb * P.lamb_factor;
-                    for (;;) {
-                        if (lamb > P.lamb_max) { status = CILQR_ST_LAMB_MAX; break; }
-                        if (iters >= P.max_iter) { status = CILQR_ST_MAX_ITER; break; }
-                        ++iters;
-                        lamb = lamb * P.lamb_factor;
-                    }
-                    break;
-                }
-                const bool converged = fabs(J_new - J_old) < P.tol;
-                if (!phase_backward(P, W, lamb, lane)) { status = CILQR_ST_NONFINITE; break; }
-                phase_forward_inplace(P, W, lane);
-                lamb = lamb / P.lamb_factor;
-                if (converged) { status = CILQR_ST_TOLERANCE; break; }
-                J_old = J_new;
-            }
-        } else {
-            // Line-search extension: all alphas rolled out concurrently, warp vote picks the largest that improves.
-            double J_cur = 0.0;
-            for (int it = 0; it < P.max_iter; ++it) {
-                iters = it + 1;
-                phase_derivs<true>(P, W, pl, obs, A.n_obs, merit_total && it == 0, lane);
-                if (it == 0)
-                    J_cur = sum_sequential(W.Jt, N);
-                if (!phase_backward(P, W, lamb, lane)) { status = CILQR_ST_NONFINITE; break; }
-                phase_forward_candidates(P, W, cand, A.n_alphas, nullptr, lane);
-                phase_candidate_merits(P, W, pl, cand, A.n_alphas, obs, A.n_obs, merit_total, W.R, lane);
-                const double Ja = lane < A.n_alphas ? sum_sequential(W.R + lane * N, N) : 0.0;
-                const unsigned ok = __ballot_sync(0xffffffffu, lane < A.n_alphas && Ja < J_cur);
-                if (ok) {
-                    const int a = __ffs(ok) - 1;
-                    const double Jw = __shfl_sync(0xffffffffu, Ja, a);
-                    const double *win = cand + (size_t)a * traj_doubles(N);
-                    for (int i = lane; i < traj_doubles(N); i += 32)
-                        W.X[i] = win[i]; // X, U, CS are contiguous in both layouts
-                    __syncwarp();
-                    const double dJ = J_cur - Jw;
-                    J_cur = Jw;
-                    lamb = lamb / P.lamb_factor;
-                    if (fabs(dJ) < P.tol) { status = CILQR_ST_TOLERANCE; break; }
-                } else {
-                    lamb = lamb * P.lamb_factor;
-                    if (lamb > P.lamb_max) { status = CILQR_ST_LAMB_MAX; break; }
-                }
-            }
-        }
-
-        // results: U (in/out), X_result, J = get_J(X_result, U_result)
-        store_controls(W, A.U + (size_t)b * 2 * N, N, lane);
-        if (A.X)
-            store_states(W, A.X + (size_t)b * 4 * (N + 1), N, lane);
-        if (A.J) {
-            phase_derivs<false>(P, W, pl, obs, 0, false, lane);
-            const double J = sum_sequential(W.Jt, N);
-            if (lane == 0)
-                A.J[b] = J;
-        }
-        if (lane == 0) {
-            if (A.iters) A.iters[b] = iters;
-            if (A.status) A.status[b] = status;
-        }
-        __syncwarp();
-    }
 }
 
 // ------------------------------------------------------------------------------------------------- stage kernel
@@ -311,23 +203,27 @@ struct cilqr_solver {
     cilqr_params p;
     DevParams dp;
     int max_batch, max_obs;
+    int device = 0;              // the CUDA device this handle lives on (cilqr_create_on); every entry point switches to it
     int cur_B = 0, cur_nobs = 0; // obstacle set currently resident
     int num_sms = 0;
     int occ_cost = 1, occ_deriv = 1, occ_sweep = 1; // resident CTAs per SM of the round kernels
-    int variant = 3;             // 3 = batch-synchronous rounds (default), 1 = fused one-warp-per-scenario kernel (A/B switch CILQR_SOLVER)
     DevBuf obs;                  // obstacle records [scenario][obstacle][field][t]; expanded on demand when obs_cv
     bool obs_ready = false;
     DevBuf obs_b;                // compact constant-velocity obstacles (cilqr_batch.cuh)
     int obs_cv = 0;              // obs_b holds the compact constant-velocity form
-    DevBuf bws;                  // state of the batch-synchronous solve
-    int *last_cnt = nullptr;     // work-list lengths of the last batch-synchronous solve (device), one block per chunk
-    int last_chunks = 1;
-    int force_chunks = 0;        // CILQR_CHUNKS: override the number of chunks (A/B switch)
+    DevBuf bws;                  // state of the batch-synchronous rounds (headers, step records, work lists)
+    DevBuf ctl;                  // per chunk: work-list lengths, the fused kernel's scenario counter and pass tallies
+    int last_chunks = 0;         // chunks of the last n_alphas == 1 solve (0: none yet)
+    int last_r0 = 0;             // ... and the round from which the fused kernel ran it
+    int fused_from = -1;         // CILQR_OPT_FUSED_FROM_ROUND (-1 = automatic)
+    int fused_slots = 0;         // CILQR_OPT_FUSED_SLOTS (0 = automatic)
+    int fused_slots_max = 0;     // slots per CTA that fit shared memory with two CTAs per SM (0: the horizon is too long for the fused kernel)
+    int force_chunks = 0;        // CILQR_OPT_CHUNKS: override the number of chunks
     int exclusive = -1;          // host-buffer solves take the process-wide compute token (see issue_rounds); -1 = decide per call
     cudaEvent_t ev_in = nullptr, ev_kdone = nullptr;
-    bool deriv_staged = true;    // CILQR_DERIV_STAGED=0: plain loads for the 1/b^2 stream (A/B switch)
-    int smem_per_sm = 0;
-    bool trace_on = false;       // CILQR_TRACE=1: kernels record their start / end times (cilqr_solve_trace)
+    bool deriv_staged = true;    // CILQR_OPT_DERIV_STAGED = 0: plain loads for the 1/b^2 stream
+    int smem_per_sm = 0, smem_optin = 0;
+    bool trace_on = false;       // CILQR_OPT_TRACE: the round kernels record their start / end times (cilqr_solve_trace)
     DevBuf trace;
     cudaStream_t chunk_stream[kMaxChunks] = {};
     cudaEvent_t ev_fork = nullptr, ev_join[kMaxChunks] = {}, ev_copied = nullptr;
@@ -335,9 +231,29 @@ struct cilqr_solver {
     cudaGraphExec_t graph_exec = nullptr;    // the last repeated solve, recorded (solve_rounds)
     std::vector<uintptr_t> graph_key, seen_key;
     long long graph_kernels = 0;
-    bool use_graph = true;                   // CILQR_GRAPH=0: always issue the launches directly
-    DevBuf counter, scratch;
+    bool use_graph = true;                   // CILQR_OPT_GRAPH = 0: always issue the launches directly
+    DevBuf scratch;
     DevBuf stage[12];            // staging for CILQR_MEM_HOST callers / stage outputs
+};
+
+// Control block of one chunk in h->ctl: [n_cnt] work-list lengths, the fused kernel's counter, then 4 x uint64 (cost passes,
+// derivative passes, CTA iterations, spare).
+static size_t ctl_ints(int n_cnt) { return ((size_t)n_cnt + 1 + 1) / 2 * 2; }
+static size_t ctl_stride(int n_cnt) { return ctl_ints(n_cnt) * sizeof(int) + 4 * sizeof(unsigned long long); }
+
+// Switches to the handle's device for the duration of an entry point (a host that drives several GPUs from one thread).
+struct DeviceScope {
+    int prev = -1;
+    bool switched = false;
+    explicit DeviceScope(int dev)
+    {
+        if (cudaGetDevice(&prev) == cudaSuccess && prev != dev)
+            switched = cudaSetDevice(dev) == cudaSuccess;
+    }
+    ~DeviceScope()
+    {
+        if (switched) cudaSetDevice(prev);
+    }
 };
 
 static DevParams derive(const cilqr_params &p)
@@ -481,7 +397,70 @@ int cilqr_default_controls(const cilqr_params *p, double *U)
     return 0;
 }
 
-int cilqr_create(const cilqr_params *p, int max_batch, int max_obs, cilqr_handle *out)
+// Dynamic shared-memory limits are a per-kernel, process-wide attribute: every kernel that can need more than 48 KB is
+// raised to the device's opt-in maximum once per device, never to a size derived from one handle's horizon (a second handle
+// with a smaller horizon would lower it under the first one).
+static int raise_smem_limits(int dev, int optin)
+{
+    static std::mutex mu;
+    static std::vector<int> done;
+    std::lock_guard<std::mutex> lock(mu);
+    for (int d : done)
+        if (d == dev) return 0;
+    CILQR_CUDA(cudaFuncSetAttribute(stage_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
+    CILQR_CUDA(cudaFuncSetAttribute(batch_cost_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
+    CILQR_CUDA(cudaFuncSetAttribute(batch_derivs_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
+    CILQR_CUDA(cudaFuncSetAttribute(ls_candidates_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
+    CILQR_CUDA(cudaFuncSetAttribute(fused_solve_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
+    CILQR_CUDA(cudaFuncSetAttribute(fused_solve_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
+    done.push_back(dev);
+    return 0;
+}
+
+static int create_impl(cilqr_solver *h, int dev)
+{
+    h->device = dev;
+    CILQR_CUDA(cudaDeviceGetAttribute(&h->num_sms, cudaDevAttrMultiProcessorCount, dev));
+    CILQR_CUDA(cudaDeviceGetAttribute(&h->smem_per_sm, cudaDevAttrMaxSharedMemoryPerMultiprocessor, dev));
+    CILQR_CUDA(cudaDeviceGetAttribute(&h->smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
+    const size_t smem = (size_t)kWarpsPerBlock * warp_smem_doubles(h->dp.N, h->dp.S) * sizeof(double);
+    if (smem > (size_t)h->smem_optin) return fail(CILQR_E_ARG, "horizon/polyline too large for shared memory (%zu B per CTA)", smem);
+    if (int rc = raise_smem_limits(dev, h->smem_optin)) return rc;
+    h->smem_per_sm = std::min(h->smem_per_sm, 2 * h->smem_optin);
+    {
+        const size_t cost_smem = 2 * (size_t)cost_entries_per_cta(h->dp.N) * h->dp.N * sizeof(double); // two buffers, see batch_cost_kernel
+        int o0 = 0, o1 = 0, o2 = 0, o3 = 0;
+        CILQR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o0, batch_cost_kernel, kCostThreads, cost_smem));
+        CILQR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o1, batch_derivs_kernel<true>, kDerivThreads, 0));
+        CILQR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o2, batch_derivs_kernel<false>, kDerivThreads, 0));
+        CILQR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o3, batch_sweep_kernel<true>, kSweepThreads, 0));
+        h->occ_cost = std::max(1, o0);
+        h->occ_deriv = std::max(1, std::min(o1, o2));
+        h->occ_sweep = std::max(1, o3);
+    }
+    { // slots per CTA of the fused kernel: two CTAs per SM (1 KB per CTA is the system's), else one CTA with what fits
+        const size_t per_slot = fused_smem_bytes(h->dp.N, 1) - 16, two = (size_t)h->smem_per_sm / 2 - 1024, one = (size_t)h->smem_optin;
+        size_t g = (two - 16) / per_slot;
+        if (g < 4) g = (one - 16) / per_slot;
+        h->fused_slots_max = (int)std::min<size_t>(g, kFusedMaxSlots);
+    }
+    if (const char *e = getenv("CILQR_EXCLUSIVE")) h->exclusive = atoi(e) != 0; // documented in cilqr.h (cilqr_set_compute_token)
+    bool ok = cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming) == cudaSuccess;
+    int prio_least = 0, prio_greatest = 0; // earlier chunks get the higher priority: they finish first (see solve_rounds)
+    cudaDeviceGetStreamPriorityRange(&prio_least, &prio_greatest);
+    for (int c = 0; c < kMaxChunks && ok; ++c)
+        ok = cudaStreamCreateWithPriority(&h->chunk_stream[c], cudaStreamNonBlocking, std::min(prio_greatest + c, prio_least)) == cudaSuccess &&
+             cudaEventCreateWithFlags(&h->ev_join[c], cudaEventDisableTiming) == cudaSuccess;
+    ok = ok && cudaStreamCreateWithFlags(&h->cap_stream, cudaStreamNonBlocking) == cudaSuccess;
+    ok = ok && cudaEventCreateWithFlags(&h->ev_copied, cudaEventDisableTiming | cudaEventBlockingSync) == cudaSuccess;
+    if (!ok) {
+        const cudaError_t e = cudaGetLastError();
+        return fail(CILQR_E_CUDA, "stream/event creation failed: %s", cudaGetErrorString(e));
+    }
+    return 0;
+}
+
+int cilqr_create_on(const cilqr_params *p, int max_batch, int max_obs, int device, cilqr_handle *out)
 {
     if (!p || !out) return fail(CILQR_E_ARG, "null argument");
     if (p->num_states != 4 || p->num_ctrls != 2) return fail(CILQR_E_ARG, "only the 4-state / 2-control bicycle is supported");
@@ -494,75 +473,39 @@ int cilqr_create(const cilqr_params *p, int max_batch, int max_obs, cilqr_handle
         cudaGetLastError();
         return fail(CILQR_E_CUDA, "no CUDA device: this library has no CPU path");
     }
+    if (device < 0) CILQR_CUDA(cudaGetDevice(&device));
+    if (device >= ndev) return fail(CILQR_E_ARG, "device %d outside [0, %d)", device, ndev);
     cilqr_solver *h = new (std::nothrow) cilqr_solver();
     if (!h) return fail(CILQR_E_ALLOC, "out of host memory");
     h->p = *p;
     h->dp = derive(*p);
     h->max_batch = max_batch;
     h->max_obs = max_obs;
-    int dev = 0;
-    CILQR_CUDA(cudaGetDevice(&dev));
-    CILQR_CUDA(cudaDeviceGetAttribute(&h->num_sms, cudaDevAttrMultiProcessorCount, dev));
-    const size_t smem = (size_t)kWarpsPerBlock * warp_smem_doubles(h->dp.N, h->dp.S) * sizeof(double);
-    if (smem > 227 * 1024) { delete h; return fail(CILQR_E_ARG, "horizon/polyline too large for shared memory (%zu B per CTA)", smem); }
-    CILQR_CUDA(cudaFuncSetAttribute(solve_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    CILQR_CUDA(cudaFuncSetAttribute(solve_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    CILQR_CUDA(cudaFuncSetAttribute(stage_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int rc;
     {
-        const size_t cost_smem = 2 * (size_t)cost_entries_per_cta(h->dp.N) * h->dp.N * sizeof(double); // two buffers, see batch_cost_kernel
-        if (cost_smem > 48 * 1024)
-            CILQR_CUDA(cudaFuncSetAttribute(batch_cost_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cost_smem));
-        CILQR_CUDA(cudaDeviceGetAttribute(&h->smem_per_sm, cudaDevAttrMaxSharedMemoryPerMultiprocessor, dev));
-        int optin = 0;
-        CILQR_CUDA(cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
-        h->smem_per_sm = std::min(h->smem_per_sm, 2 * optin);
-        CILQR_CUDA(cudaFuncSetAttribute(batch_derivs_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, std::min(optin, h->smem_per_sm / 2 - 1024)));
-        CILQR_CUDA(cudaFuncSetAttribute(ls_candidates_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(LsCandSmem)));
-
-        int o0 = 0, o1 = 0, o2 = 0, o3 = 0;
-        CILQR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o0, batch_cost_kernel, kCostThreads, cost_smem));
-        CILQR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o1, batch_derivs_kernel<true>, kDerivThreads, 0));
-        CILQR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o2, batch_derivs_kernel<false>, kDerivThreads, 0));
-        CILQR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o3, batch_sweep_kernel<true>, kSweepThreads, 0));
-        h->occ_cost = std::max(1, o0);
-        h->occ_deriv = std::max(1, std::min(o1, o2));
-        h->occ_sweep = std::max(1, o3);
+        DeviceScope scope(device);
+        rc = create_impl(h, device);
+        if (rc != 0) cilqr_destroy(h); // releases whatever was created (the error text is already set)
     }
-    if (const char *e = getenv("CILQR_SOLVER")) { // A/B switch for measurements
-        const int v = atoi(e);
-        if (v == 1 || v == 3) h->variant = v;
-    }
-    if (const char *e = getenv("CILQR_CHUNKS")) h->force_chunks = std::max(0, atoi(e));
-    if (const char *e = getenv("CILQR_EXCLUSIVE")) h->exclusive = atoi(e) != 0;
-    if (const char *e = getenv("CILQR_GRAPH")) h->use_graph = atoi(e) != 0;
-    if (const char *e = getenv("CILQR_DERIV_STAGED")) h->deriv_staged = atoi(e) != 0;
-    if (const char *e = getenv("CILQR_TRACE")) h->trace_on = atoi(e) != 0;
-    if (int rc = h->counter.reserve(sizeof(int))) { delete h; return rc; }
-    bool ok = cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming) == cudaSuccess;
-    int prio_least = 0, prio_greatest = 0; // earlier chunks get the higher priority: they finish first (see solve_rounds)
-    cudaDeviceGetStreamPriorityRange(&prio_least, &prio_greatest);
-    for (int c = 0; c < kMaxChunks && ok; ++c)
-        ok = cudaStreamCreateWithPriority(&h->chunk_stream[c], cudaStreamNonBlocking, std::min(prio_greatest + c, prio_least)) == cudaSuccess &&
-             cudaEventCreateWithFlags(&h->ev_join[c], cudaEventDisableTiming) == cudaSuccess;
-    ok = ok && cudaStreamCreateWithFlags(&h->cap_stream, cudaStreamNonBlocking) == cudaSuccess;
-    ok = ok && cudaEventCreateWithFlags(&h->ev_copied, cudaEventDisableTiming | cudaEventBlockingSync) == cudaSuccess;
-    if (!ok) {
-        const cudaError_t e = cudaGetLastError();
-        cilqr_destroy(h);
-        return fail(CILQR_E_CUDA, "stream/event creation failed: %s", cudaGetErrorString(e));
-    }
+    if (rc != 0) return rc;
     *out = h;
     return 0;
+}
+
+int cilqr_create(const cilqr_params *p, int max_batch, int max_obs, cilqr_handle *out)
+{
+    return cilqr_create_on(p, max_batch, max_obs, -1, out);
 }
 
 int cilqr_destroy(cilqr_handle h)
 {
     if (!h) return 0;
+    DeviceScope scope(h->device);
     h->obs.release();
     h->obs_b.release();
     h->bws.release();
+    h->ctl.release();
     h->trace.release();
-    h->counter.release();
     h->scratch.release();
     for (auto &s : h->stage) s.release();
     for (int c = 0; c < kMaxChunks; ++c) {
@@ -576,6 +519,33 @@ int cilqr_destroy(cilqr_handle h)
     if (h->graph_exec) cudaGraphExecDestroy(h->graph_exec);
     if (h->cap_stream) cudaStreamDestroy(h->cap_stream);
     delete h;
+    return 0;
+}
+
+int cilqr_set_option(cilqr_handle h, int option, int value)
+{
+    if (!h) return fail(CILQR_E_ARG, "null handle");
+    switch (option) {
+    case CILQR_OPT_FUSED_FROM_ROUND: h->fused_from = value < 0 ? -1 : value; break;
+    case CILQR_OPT_FUSED_SLOTS:
+        if (value < 0 || value > kFusedMaxSlots) return fail(CILQR_E_ARG, "fused slots %d outside [0, %d]", value, kFusedMaxSlots);
+        h->fused_slots = value;
+        break;
+    case CILQR_OPT_CHUNKS:
+        if (value < 0 || value > kMaxChunks) return fail(CILQR_E_ARG, "chunks %d outside [0, %d]", value, kMaxChunks);
+        h->force_chunks = value;
+        break;
+    case CILQR_OPT_GRAPH: h->use_graph = value != 0; break;
+    case CILQR_OPT_DERIV_STAGED: h->deriv_staged = value != 0; break;
+    case CILQR_OPT_TRACE: h->trace_on = value != 0; break;
+    default: return fail(CILQR_E_ARG, "unknown option %d", option);
+    }
+    if (h->graph_exec) { // a recorded solve holds the old choice
+        cudaGraphExecDestroy(h->graph_exec);
+        h->graph_exec = nullptr;
+    }
+    h->graph_key.clear();
+    h->seen_key.clear();
     return 0;
 }
 
@@ -598,6 +568,7 @@ int cilqr_set_obstacles(cilqr_handle h, int B, int n_obs, const double *dim, con
 {
     if (int rc = check_handle(h, B)) return rc;
     if (n_obs < 0 || n_obs > h->max_obs) return fail(CILQR_E_ARG, "n_obs %d outside [0, %d]", n_obs, h->max_obs);
+    DeviceScope scope(h->device);
     cudaStream_t st = (cudaStream_t)stream;
     h->cur_B = B;
     h->cur_nobs = n_obs;
@@ -621,6 +592,7 @@ int cilqr_set_obstacles_cv(cilqr_handle h, int B, int n_obs, const double *state
 {
     if (int rc = check_handle(h, B)) return rc;
     if (n_obs < 0 || n_obs > h->max_obs) return fail(CILQR_E_ARG, "n_obs %d outside [0, %d]", n_obs, h->max_obs);
+    DeviceScope scope(h->device);
     cudaStream_t st = (cudaStream_t)stream;
     h->cur_B = B;
     h->cur_nobs = n_obs;
@@ -667,19 +639,38 @@ struct HostIO { // caller's host arrays (CILQR_MEM_HOST) — null members when t
     int32_t *iters = nullptr, *status = nullptr;
 };
 
+// How one n_alphas == 1 solve is laid out: K chunks of Bc scenarios; rounds 0 .. r0 - 1 as batch-synchronous round kernels,
+// the rest (r0 == 0: everything) in the fused kernel with G slots per CTA.
+struct SolvePlan {
+    int K, Bc, r0, G, fused_occ;
+    size_t fused_smem;
+};
+
+static int launch_fused(cilqr_handle h, const FusedArgs &F, int work, const SolvePlan &plan, cudaStream_t st)
+{
+    const int grid = std::max(1, std::min((work + F.G - 1) / F.G, h->num_sms * plan.fused_occ));
+    if (h->obs_cv)
+        fused_solve_kernel<true><<<grid, kFusedThreads, plan.fused_smem, st>>>(F);
+    else
+        fused_solve_kernel<false><<<grid, kFusedThreads, plan.fused_smem, st>>>(F);
+    CILQR_LAUNCH_CHECK();
+    return 0;
+}
+
 // The launches of one solve, relative to stream `st` (the caller's stream, or the capture stream when a graph is recorded).
-static int issue_rounds(cilqr_handle h, const SolveArgs &A, const HostIO *io, cudaStream_t st, int K, int Bc)
+static int issue_rounds(cilqr_handle h, const SolveArgs &A, const HostIO *io, cudaStream_t st, const SolvePlan &plan)
 {
     const DevParams &P = h->dp;
-    const int N = P.N, B = A.B, n_obs = h->cur_nobs;
+    const int N = P.N, B = A.B, n_obs = h->cur_nobs, K = plan.K, Bc = plan.Bc, r0 = plan.r0;
     const int n_cnt = P.max_iter + 3;
-    double *hdr = h->bws.as<double>(), *rec = hdr + (size_t)B * kHdrD;
-    int *list0 = reinterpret_cast<int *>(rec + (size_t)B * (N + 1) * kStepD), *list1 = list0 + B, *cnt = list1 + B;
+    const bool rounds = r0 > 0;
+    double *hdr = rounds ? h->bws.as<double>() : nullptr, *rec = rounds ? hdr + (size_t)B * kHdrD : nullptr;
+    int *list0 = rounds ? reinterpret_cast<int *>(rec + (size_t)B * (N + 1) * kStepD) : nullptr, *list1 = rounds ? list0 + B : nullptr;
     const double *ocv = h->obs_b.as<double>(), *oib2 = ocv ? ocv + (size_t)B * n_obs * CV_FIELDS : nullptr, *orec = h->obs.as<double>();
     const size_t trace_per_chunk = (size_t)n_cnt * kTraceKinds * 2;
     if (h->trace_on) CILQR_CUDA(cudaMemsetAsync(h->trace.p, 0xff, (size_t)kMaxChunks * trace_per_chunk * sizeof(unsigned long long), st));
     // Compute token (host buffers, one chunk, direct launches): several handles driven from several host threads would otherwise
-    // interleave their round kernels on the GPU — every solve takes longer and all of them finish, and copy their results back,
+    // interleave their kernels on the GPU — every solve takes longer and all of them finish, and copy their results back,
     // at about the same time.  With the token the solves' kernels run one handle after the other at full speed, and a handle's
     // host<->device copies run under the other handles' kernels.
     const bool token = io && K == 1 && h->exclusive == 1;
@@ -704,13 +695,14 @@ static int issue_rounds(cilqr_handle h, const SolveArgs &A, const HostIO *io, cu
     // back while the later chunks are still iterating.
     for (int c = 0; c < K; ++c) {
         const int o = c * Bc, b = std::min(Bc, B - o);
+        unsigned char *ctl = h->ctl.as<unsigned char>() + (size_t)c * ctl_stride(n_cnt);
         BatchView v;
         v.N = N;
-        v.hdr = hdr + (size_t)o * kHdrD;
-        v.rec = rec + (size_t)o * (N + 1) * kStepD;
-        v.list0 = list0 + o;
-        v.list1 = list1 + o;
-        v.cnt = cnt + (size_t)c * n_cnt;
+        v.hdr = rounds ? hdr + (size_t)o * kHdrD : nullptr;
+        v.rec = rounds ? rec + (size_t)o * (N + 1) * kStepD : nullptr;
+        v.list0 = rounds ? list0 + o : nullptr;
+        v.list1 = rounds ? list1 + o : nullptr;
+        v.cnt = reinterpret_cast<int *>(ctl);
         v.n_obs = n_obs;
         v.cv = h->obs_cv;
         v.ocv = ocv ? ocv + (size_t)o * n_obs * CV_FIELDS : nullptr;
@@ -729,32 +721,64 @@ static int issue_rounds(cilqr_handle h, const SolveArgs &A, const HostIO *io, cu
             CILQR_CUDA(cudaEventSynchronize(h->ev_in));
             compute_token.lock();
         }
-        CILQR_CUDA(cudaMemsetAsync(v.cnt, 0, (size_t)n_cnt * sizeof(int), cs[c]));
-        batch_init_kernel<<<(b + kInitThreads - 1) / kInitThreads, kInitThreads, 0, cs[c]>>>(P, v, b, A.x0 + 4 * so, A.U + 2 * N * so, A.poly + P.npoly * so, A.xlp + 2 * so, MODE_ITERATE);
-        CILQR_LAUNCH_CHECK();
-        const int cost_grid = std::min((b + E - 1) / E, h->num_sms * h->occ_cost);
-        const long long items = (long long)b * N;
-        const int deriv_grid = (int)std::min<long long>((items + kDerivThreads - 1) / kDerivThreads, (long long)h->num_sms * h->occ_deriv);
-        const int sweep_grid = std::min((b + kSweepThreads - 1) / kSweepThreads, h->num_sms * h->occ_sweep);
-        for (int r = 0; r <= P.max_iter; ++r) {
-            batch_cost_kernel<<<cost_grid, kCostThreads, cost_smem, cs[c]>>>(P, v, r);
+        CILQR_CUDA(cudaMemsetAsync(ctl, 0, ctl_stride(n_cnt), cs[c]));
+        FusedArgs F;
+        F.P = P;
+        F.B = b;
+        F.G = plan.G;
+        F.x0 = A.x0 + 4 * so;
+        F.poly = A.poly + P.npoly * so;
+        F.xlp = A.xlp + 2 * so;
+        F.U = A.U + 2 * N * so;
+        F.X = A.X ? A.X + 4 * (N + 1) * so : nullptr;
+        F.J = A.J ? A.J + so : nullptr;
+        F.iters = A.iters ? A.iters + so : nullptr;
+        F.status = A.status ? A.status + so : nullptr;
+        F.n_obs = n_obs;
+        F.ocv = v.ocv;
+        F.oib2 = v.oib2;
+        F.orec = v.orec;
+        F.hand_hdr = F.hand_rec = nullptr;
+        F.hand_list = F.hand_cnt = nullptr;
+        F.counter = v.cnt + n_cnt;
+        F.stats = reinterpret_cast<unsigned long long *>(ctl + ctl_ints(n_cnt) * sizeof(int));
+        if (!rounds) { // the whole solve on chip
+            if (int rc = launch_fused(h, F, b, plan, cs[c])) return rc;
+        } else {
+            batch_init_kernel<<<(b + kInitThreads - 1) / kInitThreads, kInitThreads, 0, cs[c]>>>(P, v, b, F.x0, F.U, F.poly, F.xlp, MODE_ITERATE);
             CILQR_LAUNCH_CHECK();
-            if (r == P.max_iter) break; // the last round only evaluates J of the scenarios that ran out of iterations
-            if (v.cv && staged)
-                batch_derivs_kernel<true, true><<<deriv_grid, kDerivThreads, deriv_stage_bytes(n_obs), cs[c]>>>(P, v, r);
-            else if (v.cv)
-                batch_derivs_kernel<true><<<deriv_grid, kDerivThreads, 0, cs[c]>>>(P, v, r);
-            else
-                batch_derivs_kernel<false><<<deriv_grid, kDerivThreads, 0, cs[c]>>>(P, v, r);
+            const int cost_grid = std::min((b + E - 1) / E, h->num_sms * h->occ_cost);
+            const long long items = (long long)b * N;
+            const int deriv_grid = (int)std::min<long long>((items + kDerivThreads - 1) / kDerivThreads, (long long)h->num_sms * h->occ_deriv);
+            const int sweep_grid = std::min((b + kSweepThreads - 1) / kSweepThreads, h->num_sms * h->occ_sweep);
+            const bool hand = r0 <= P.max_iter;
+            for (int r = 0; r <= P.max_iter && r < r0; ++r) {
+                batch_cost_kernel<<<cost_grid, kCostThreads, cost_smem, cs[c]>>>(P, v, r);
+                CILQR_LAUNCH_CHECK();
+                if (r == P.max_iter) break; // the last round only evaluates J of the scenarios that ran out of iterations
+                if (v.cv && staged)
+                    batch_derivs_kernel<true, true><<<deriv_grid, kDerivThreads, deriv_stage_bytes(n_obs), cs[c]>>>(P, v, r);
+                else if (v.cv)
+                    batch_derivs_kernel<true><<<deriv_grid, kDerivThreads, 0, cs[c]>>>(P, v, r);
+                else
+                    batch_derivs_kernel<false><<<deriv_grid, kDerivThreads, 0, cs[c]>>>(P, v, r);
+                CILQR_LAUNCH_CHECK();
+                batch_sweep_kernel<true><<<sweep_grid, kSweepThreads, 0, cs[c]>>>(P, v, r);
+                CILQR_LAUNCH_CHECK();
+            }
+            const size_t out_items = sb * (N + 1);
+            batch_output_kernel<<<(int)std::min<size_t>((out_items + 255) / 256, (size_t)h->num_sms * 8), 256, 0, cs[c]>>>(
+                P, v, b, F.U, F.X, F.J, F.iters, F.status);
             CILQR_LAUNCH_CHECK();
-            batch_sweep_kernel<true><<<sweep_grid, kSweepThreads, 0, cs[c]>>>(P, v, r);
-            CILQR_LAUNCH_CHECK();
+            if (hand) { // the scenarios still iterating after round r0 - 1 move on chip; their results overwrite the ones just written
+                F.hand_hdr = v.hdr;
+                F.hand_rec = v.rec;
+                F.hand_list = (r0 & 1) ? v.list1 : v.list0;
+                F.hand_cnt = v.cnt + r0;
+                // the list is at most as long as the batch; later rounds leave most CTAs without work, which costs nothing
+                if (int rc = launch_fused(h, F, b, plan, cs[c])) return rc;
+            }
         }
-        const size_t out_items = sb * (N + 1);
-        batch_output_kernel<<<(int)std::min<size_t>((out_items + 255) / 256, (size_t)h->num_sms * 8), 256, 0, cs[c]>>>(
-            P, v, b, A.U + 2 * N * so, A.X ? A.X + 4 * (N + 1) * so : nullptr, A.J ? A.J + so : nullptr, A.iters ? A.iters + so : nullptr,
-            A.status ? A.status + so : nullptr);
-        CILQR_LAUNCH_CHECK();
         if (token) CILQR_CUDA(cudaEventRecord(h->ev_kdone, cs[c]));
         if (io) { // this chunk's results: staging -> host
             CILQR_CUDA(cudaMemcpyAsync(io->U + 2 * N * so, A.U + 2 * N * so, sb * 2 * N * sizeof(double), cudaMemcpyDeviceToHost, cs[c]));
@@ -793,31 +817,58 @@ static void drop_graph(cilqr_handle h)
     h->graph_key.clear();
 }
 
-// One solve = ~60 launches per chunk, most of them a few microseconds long: issued one by one the host's launch rate
-// (~2.5 us per launch) would bound the step as soon as there is more than one chunk.  A call that repeats the previous call's
-// arguments (same buffers, sizes and obstacle form — the receding-horizon loop, the benchmark) records the whole multi-stream
-// sequence once as a CUDA graph and replays it with a single launch afterwards; anything else is issued directly.
+// A call that repeats the previous call's arguments (same buffers, sizes and obstacle form — the receding-horizon loop, the
+// benchmark) records its whole multi-stream sequence of copies and launches once as a CUDA graph and replays it with a single
+// launch afterwards (the round kernels are ~60 launches per chunk, most of them a few microseconds long); anything else is
+// issued directly.
 static int solve_rounds(cilqr_handle h, const SolveArgs &A, const HostIO *io, cudaStream_t st)
 {
     const DevParams &P = h->dp;
     const int N = P.N, B = A.B;
     const int n_cnt = P.max_iter + 3;
-    // chunks pay off when there are transfers to hide; on device buffers the rounds of one chunk already fill the GPU
+    SolvePlan plan;
+    // chunks pay off when there are transfers to hide; on device buffers one chunk already fills the GPU
     int K = io ? (B >= 16384 ? 4 : (B >= 2048 ? 2 : 1)) : 1;
     if (h->force_chunks > 0) K = std::min(h->force_chunks, kMaxChunks);
     if (io && h->exclusive == 1) K = 1;
-    const int Bc = ((B + K - 1) / K + 31) / 32 * 32; // chunk size, a multiple of the warp size
-    K = (B + Bc - 1) / Bc;
-    const size_t n_dbl = (size_t)B * kHdrD + (size_t)B * (N + 1) * kStepD;
-    if (int rc = h->bws.reserve(n_dbl * sizeof(double) + ((size_t)2 * B + (size_t)kMaxChunks * n_cnt) * sizeof(int))) return rc;
+    plan.Bc = ((B + K - 1) / K + 31) / 32 * 32; // chunk size, a multiple of the warp size
+    plan.K = K = (B + plan.Bc - 1) / plan.Bc;
+    // Where the solve runs.  Automatic: on chip from the start (cilqr_fused.cuh) whenever the horizon leaves room for at least
+    // one slot; CILQR_OPT_FUSED_FROM_ROUND = r > 0 keeps rounds 0 .. r - 1 as batch-synchronous round kernels (the first rounds
+    // of a large batch fill every lane of those), r > max_iterations never leaves them.
+    plan.r0 = h->fused_from >= 0 ? h->fused_from : 0;
+    plan.G = 0;
+    plan.fused_occ = 1;
+    plan.fused_smem = 0;
+    if (h->fused_slots_max < 1 || (h->trace_on && plan.r0 == 0)) plan.r0 = P.max_iter + 1; // (the trace is a feature of the round kernels)
+    if (plan.r0 <= P.max_iter) {
+        int G = h->fused_slots > 0 ? std::min(h->fused_slots, h->fused_slots_max) : h->fused_slots_max;
+        if (h->fused_slots == 0) // a small batch is spread over all SMs rather than packed into few CTAs
+            G = std::max(1, std::min(G, (std::min(plan.Bc, B) + 2 * h->num_sms - 1) / (2 * h->num_sms)));
+        plan.G = G;
+        plan.fused_smem = fused_smem_bytes(N, G);
+        int occ = 0;
+        if (h->obs_cv)
+            CILQR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fused_solve_kernel<true>, kFusedThreads, plan.fused_smem));
+        else
+            CILQR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fused_solve_kernel<false>, kFusedThreads, plan.fused_smem));
+        if (occ < 1) return fail(CILQR_E_CUDA, "fused solve kernel does not fit on an SM (%zu B of shared memory)", plan.fused_smem);
+        plan.fused_occ = occ;
+    }
+    if (plan.r0 > 0) {
+        const size_t n_dbl = (size_t)B * kHdrD + (size_t)B * (N + 1) * kStepD;
+        if (int rc = h->bws.reserve(n_dbl * sizeof(double) + (size_t)2 * B * sizeof(int))) return rc;
+    }
+    if (int rc = h->ctl.reserve((size_t)kMaxChunks * ctl_stride(n_cnt))) return rc;
     if (h->trace_on)
         if (int rc = h->trace.reserve((size_t)kMaxChunks * n_cnt * kTraceKinds * 2 * sizeof(unsigned long long))) return rc;
-    h->last_cnt = reinterpret_cast<int *>(h->bws.as<double>() + n_dbl) + 2 * (size_t)B;
     h->last_chunks = K;
+    h->last_r0 = plan.r0;
 
-    std::vector<uintptr_t> key = {(uintptr_t)B, (uintptr_t)h->cur_nobs, (uintptr_t)h->obs_cv, (uintptr_t)K, (uintptr_t)h->bws.p, (uintptr_t)h->obs_b.p,
-                                  (uintptr_t)h->obs.p, (uintptr_t)h->trace.p, (uintptr_t)A.x0, (uintptr_t)A.U, (uintptr_t)A.poly, (uintptr_t)A.xlp, (uintptr_t)A.X,
-                                  (uintptr_t)A.J, (uintptr_t)A.iters, (uintptr_t)A.status};
+    std::vector<uintptr_t> key = {(uintptr_t)B, (uintptr_t)h->cur_nobs, (uintptr_t)h->obs_cv, (uintptr_t)K, (uintptr_t)plan.r0, (uintptr_t)plan.G,
+                                  (uintptr_t)h->bws.p, (uintptr_t)h->ctl.p, (uintptr_t)h->obs_b.p, (uintptr_t)h->obs.p, (uintptr_t)h->trace.p,
+                                  (uintptr_t)A.x0, (uintptr_t)A.U, (uintptr_t)A.poly, (uintptr_t)A.xlp, (uintptr_t)A.X, (uintptr_t)A.J,
+                                  (uintptr_t)A.iters, (uintptr_t)A.status};
     if (io)
         for (const void *q : {(const void *)io->x0, (const void *)io->U, (const void *)io->poly, (const void *)io->xlp, (const void *)io->X,
                               (const void *)io->J, (const void *)io->iters, (const void *)io->status})
@@ -825,24 +876,25 @@ static int solve_rounds(cilqr_handle h, const SolveArgs &A, const HostIO *io, cu
     if (io && h->exclusive == 1) { // the token is taken and released by host code between the launches: no graph
         if (!h->ev_in) CILQR_CUDA(cudaEventCreateWithFlags(&h->ev_in, cudaEventDisableTiming));
         if (!h->ev_kdone) CILQR_CUDA(cudaEventCreateWithFlags(&h->ev_kdone, cudaEventDisableTiming));
-        return issue_rounds(h, A, io, st, K, Bc);
+        return issue_rounds(h, A, io, st, plan);
     }
     if (h->graph_exec && key == h->graph_key) {
         CILQR_CUDA(cudaGraphLaunch(h->graph_exec, st));
         g_launches.fetch_add(h->graph_kernels, std::memory_order_relaxed);
         return 0;
     }
-    bool record = h->use_graph && key == h->seen_key; // second call in a row with these arguments
+    // a graph pays for itself when there is more than one launch to replay: several chunks, or round kernels
+    bool record = h->use_graph && key == h->seen_key && (K > 1 || plan.r0 > 0 || io); // second call in a row with these arguments
     h->seen_key = key;
     if (record && io)
         record = pinned_or_null(io->x0) && pinned_or_null(io->U) && pinned_or_null(io->poly) && pinned_or_null(io->xlp) && pinned_or_null(io->X) &&
                  pinned_or_null(io->J) && pinned_or_null(io->iters) && pinned_or_null(io->status); // pageable copies are not recorded
-    if (!record) return issue_rounds(h, A, io, st, K, Bc);
+    if (!record) return issue_rounds(h, A, io, st, plan);
 
     drop_graph(h);
     const long long before = g_launches.load(std::memory_order_relaxed);
     CILQR_CUDA(cudaStreamBeginCapture(h->cap_stream, cudaStreamCaptureModeRelaxed));
-    const int rc = issue_rounds(h, A, io, h->cap_stream, K, Bc);
+    const int rc = issue_rounds(h, A, io, h->cap_stream, plan);
     cudaGraph_t g = nullptr;
     const cudaError_t e = cudaStreamEndCapture(h->cap_stream, &g);
     const long long recorded = g_launches.load(std::memory_order_relaxed) - before;
@@ -852,7 +904,7 @@ static int solve_rounds(cilqr_handle h, const SolveArgs &A, const HostIO *io, cu
         cudaGetLastError();
         h->use_graph = false; // do not try again on this handle
         if (rc != 0) return rc;
-        return issue_rounds(h, A, io, st, K, Bc);
+        return issue_rounds(h, A, io, st, plan);
     }
     const cudaError_t ei = cudaGraphInstantiate(&h->graph_exec, g, 0);
     cudaGraphDestroy(g);
@@ -860,7 +912,7 @@ static int solve_rounds(cilqr_handle h, const SolveArgs &A, const HostIO *io, cu
         cudaGetLastError();
         h->graph_exec = nullptr;
         h->use_graph = false;
-        return issue_rounds(h, A, io, st, K, Bc);
+        return issue_rounds(h, A, io, st, plan);
     }
     h->graph_key = key;
     h->graph_kernels = recorded;
@@ -877,7 +929,8 @@ static int solve_rounds_ls(cilqr_handle h, const SolveArgs &A, cudaStream_t st)
     const int N = P.N, B = A.B, n_obs = h->cur_nobs, na = A.n_alphas;
     const int n_cnt = P.max_iter + 3;
     const size_t n_dbl = (size_t)B * kHdrD + (size_t)B * (N + 1) * kStepD;
-    if (int rc = h->bws.reserve(n_dbl * sizeof(double) + ((size_t)2 * B + (size_t)kMaxChunks * n_cnt) * sizeof(int))) return rc;
+    if (int rc = h->bws.reserve(n_dbl * sizeof(double) + (size_t)2 * B * sizeof(int))) return rc;
+    if (int rc = h->ctl.reserve((size_t)kMaxChunks * ctl_stride(n_cnt))) return rc;
     const size_t n_cand = (size_t)B * na * (N + 1) * kCandD, n_merit = (size_t)B * na * N;
     if (int rc = h->scratch.reserve((n_cand + n_merit) * sizeof(double) + ((size_t)B + n_cnt) * sizeof(int))) return rc;
     if (h->trace_on)
@@ -888,7 +941,7 @@ static int solve_rounds_ls(cilqr_handle h, const SolveArgs &A, cudaStream_t st)
     v.rec = v.hdr + (size_t)B * kHdrD;
     v.list0 = reinterpret_cast<int *>(v.rec + (size_t)B * (N + 1) * kStepD);
     v.list1 = v.list0 + B;
-    v.cnt = v.list1 + B;
+    v.cnt = h->ctl.as<int>();
     v.n_obs = n_obs;
     v.cv = h->obs_cv;
     v.ocv = h->obs_b.as<double>();
@@ -899,8 +952,8 @@ static int solve_rounds_ls(cilqr_handle h, const SolveArgs &A, cudaStream_t st)
         CILQR_CUDA(cudaMemsetAsync(h->trace.p, 0xff, (size_t)kMaxChunks * n_cnt * kTraceKinds * 2 * sizeof(unsigned long long), st));
         v.trace = h->trace.as<unsigned long long>();
     }
-    h->last_cnt = v.cnt;
     h->last_chunks = 1;
+    h->last_r0 = P.max_iter + 1;
     drop_graph(h);
     h->seen_key.clear();
     LsView L;
@@ -911,7 +964,7 @@ static int solve_rounds_ls(cilqr_handle h, const SolveArgs &A, cudaStream_t st)
     L.n_alphas = na;
     L.merit_total = A.merit == CILQR_MERIT_TOTAL;
 
-    CILQR_CUDA(cudaMemsetAsync(v.cnt, 0, (size_t)n_cnt * sizeof(int), st));
+    CILQR_CUDA(cudaMemsetAsync(v.cnt, 0, ctl_stride(n_cnt), st));
     CILQR_CUDA(cudaMemsetAsync(L.retry_cnt, 0, (size_t)n_cnt * sizeof(int), st));
     batch_init_kernel<<<(B + kInitThreads - 1) / kInitThreads, kInitThreads, 0, st>>>(P, v, B, A.x0, A.U, A.poly, A.xlp, MODE_LS);
     CILQR_LAUNCH_CHECK();
@@ -974,7 +1027,8 @@ static int solve_rounds_ls(cilqr_handle h, const SolveArgs &A, cudaStream_t st)
 int cilqr_solve_trace(cilqr_handle h, uint64_t *out, int capacity, int32_t *chunks, int32_t *rounds, void *stream)
 {
     if (!h || !out) return fail(CILQR_E_ARG, "null argument");
-    if (!h->trace_on || !h->trace.p || !h->last_cnt) return fail(CILQR_E_STATE, "no traced solve on this handle (create it with CILQR_TRACE=1 in the environment)");
+    DeviceScope scope(h->device);
+    if (!h->trace_on || !h->trace.p || !h->last_chunks) return fail(CILQR_E_STATE, "no traced solve on this handle (cilqr_set_option(h, CILQR_OPT_TRACE, 1) before the solve)");
     const int n_cnt = h->dp.max_iter + 3, K = h->last_chunks;
     const size_t n = (size_t)K * n_cnt * kTraceKinds * 2;
     if ((size_t)capacity < n) return fail(CILQR_E_ARG, "trace needs %zu entries, the buffer has %d", n, capacity);
@@ -999,19 +1053,28 @@ int cilqr_set_compute_token(cilqr_handle h, int on)
 int cilqr_solve_stats(cilqr_handle h, int64_t *cost_passes, int64_t *deriv_passes, int32_t *rounds, void *stream)
 {
     if (!h) return fail(CILQR_E_ARG, "null handle");
-    if (!h->last_cnt) return fail(CILQR_E_STATE, "no batch-synchronous solve has run on this handle");
-    const int n_cnt = h->dp.max_iter + 3, K = h->last_chunks;
-    std::vector<int> c((size_t)n_cnt * K);
-    CILQR_CUDA(cudaMemcpyAsync(c.data(), h->last_cnt, c.size() * sizeof(int), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    if (!h->last_chunks || !h->ctl.p) return fail(CILQR_E_STATE, "no solve has run on this handle");
+    DeviceScope scope(h->device);
+    const int n_cnt = h->dp.max_iter + 3, K = h->last_chunks, r0 = h->last_r0;
+    const size_t stride = ctl_stride(n_cnt);
+    std::vector<unsigned char> raw(stride * K);
+    CILQR_CUDA(cudaMemcpyAsync(raw.data(), h->ctl.p, raw.size(), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
     CILQR_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
     int64_t cp = 0, dp = 0;
     int r = 0;
-    for (int k = 0; k < K; ++k)
-        for (int i = 0; i <= h->dp.max_iter; ++i) {
-            cp += c[(size_t)k * n_cnt + i];
-            dp += c[(size_t)k * n_cnt + i + 1];
-            if (c[(size_t)k * n_cnt + i] > 0) r = std::max(r, i + 1);
+    for (int k = 0; k < K; ++k) {
+        const int *c = reinterpret_cast<const int *>(raw.data() + stride * k);
+        const unsigned long long *f = reinterpret_cast<const unsigned long long *>(raw.data() + stride * k + ctl_ints(n_cnt) * sizeof(int));
+        int rk = 0;
+        for (int i = 0; i <= h->dp.max_iter && i < r0; ++i) { // the round kernels' share: work-list lengths
+            cp += c[i];
+            dp += c[i + 1];
+            if (c[i] > 0) rk = i + 1;
         }
+        cp += (int64_t)f[0]; // the fused kernel's share
+        dp += (int64_t)f[1];
+        r = std::max(r, rk + (int)f[2]);
+    }
     if (cost_passes) *cost_passes = cp;
     if (deriv_passes) *deriv_passes = dp;
     if (rounds) *rounds = r;
@@ -1027,6 +1090,7 @@ int cilqr_solve_batch(cilqr_handle h, int B, const double *x0, double *U, const 
     if (merit != CILQR_MERIT_TRACKING && merit != CILQR_MERIT_TOTAL) return fail(CILQR_E_ARG, "unknown merit %d", merit);
     if (int rc = need_obstacles(h, B)) return rc;
     if (B == 0) return 0;
+    DeviceScope scope(h->device);
     cudaStream_t st = (cudaStream_t)stream;
     const int N = h->dp.N;
     SolveArgs A;
@@ -1036,7 +1100,7 @@ int cilqr_solve_batch(cilqr_handle h, int B, const double *x0, double *U, const 
     A.n_alphas = n_alphas;
     A.merit = merit;
     A.obs = nullptr;
-    if (n_alphas == 1 && h->variant == 3) {
+    if (n_alphas == 1) {
         if (mem == CILQR_MEM_DEVICE) {
             A.x0 = x0; A.U = U; A.poly = poly; A.xlp = xlp;
             A.X = X; A.J = J; A.iters = iters; A.status = status;
@@ -1072,44 +1136,11 @@ int cilqr_solve_batch(cilqr_handle h, int B, const double *x0, double *U, const 
     if (int rc = stage_out(h, 8, J, (size_t)B, mem, &A.J)) return rc;
     if (int rc = stage_out(h, 9, iters, (size_t)B, mem, &A.iters)) return rc;
     if (int rc = stage_out(h, 10, status, (size_t)B, mem, &A.status)) return rc;
-    A.counter = h->counter.as<int>();
-
-    if (n_alphas > 1 && h->variant == 3) {
-        if (!h->obs_cv && h->cur_nobs > 0) {
-            if (int rc = ensure_records(h, st)) return rc;
-        }
-        if (int rc = solve_rounds_ls(h, A, st)) return rc;
-        if (int rc = fetch_out(U, A.U, (size_t)B * 2 * N, mem, st)) return rc;
-        if (int rc = fetch_out(X, A.X, (size_t)B * 4 * (N + 1), mem, st)) return rc;
-        if (int rc = fetch_out(J, A.J, (size_t)B, mem, st)) return rc;
-        if (int rc = fetch_out(iters, A.iters, (size_t)B, mem, st)) return rc;
-        if (int rc = fetch_out(status, A.status, (size_t)B, mem, st)) return rc;
-        if (mem == CILQR_MEM_HOST) CILQR_CUDA(cudaStreamSynchronize(st));
-        return 0;
-    }
-    if (h->cur_nobs > 0) {
+    // line-search extension (n_alphas > 1)
+    if (!h->obs_cv && h->cur_nobs > 0) {
         if (int rc = ensure_records(h, st)) return rc;
-        A.obs = h->obs.as<double>();
     }
-    const size_t smem = (size_t)kWarpsPerBlock * warp_smem_doubles(N, h->dp.S) * sizeof(double);
-    int per_sm = 0;
-    if (n_alphas > 1)
-        CILQR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, solve_kernel<true>, kWarpsPerBlock * 32, smem));
-    else
-        CILQR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, solve_kernel<false>, kWarpsPerBlock * 32, smem));
-    if (per_sm < 1) return fail(CILQR_E_CUDA, "solve kernel does not fit on an SM (smem %zu B)", smem);
-    const int grid = std::min((B + kWarpsPerBlock - 1) / kWarpsPerBlock, h->num_sms * per_sm);
-    A.scratch = nullptr;
-    if (n_alphas > 1) {
-        if (int rc = h->scratch.reserve((size_t)grid * kWarpsPerBlock * n_alphas * traj_doubles(N) * sizeof(double))) return rc;
-        A.scratch = h->scratch.as<double>();
-    }
-    CILQR_CUDA(cudaMemsetAsync(A.counter, 0, sizeof(int), st));
-    if (n_alphas > 1)
-        solve_kernel<true><<<grid, kWarpsPerBlock * 32, smem, st>>>(A);
-    else
-        solve_kernel<false><<<grid, kWarpsPerBlock * 32, smem, st>>>(A);
-    CILQR_LAUNCH_CHECK();
+    if (int rc = solve_rounds_ls(h, A, st)) return rc;
     if (int rc = fetch_out(U, A.U, (size_t)B * 2 * N, mem, st)) return rc;
     if (int rc = fetch_out(X, A.X, (size_t)B * 4 * (N + 1), mem, st)) return rc;
     if (int rc = fetch_out(J, A.J, (size_t)B, mem, st)) return rc;
@@ -1149,6 +1180,7 @@ int cilqr_rollout(cilqr_handle h, int B, const double *x0, const double *U, doub
     if (int rc = check_handle(h, B)) return rc;
     if (!x0 || !U || !X) return fail(CILQR_E_ARG, "null argument");
     if (B == 0) return 0;
+    DeviceScope scope(h->device);
     cudaStream_t st = (cudaStream_t)stream;
     const int N = h->dp.N;
     StageArgs A = stage_args(h, B, STAGE_ROLLOUT);
@@ -1168,6 +1200,7 @@ int cilqr_state_cost(cilqr_handle h, int B, const double *X, const double *poly,
     if (!X || !poly || !xlp || !l_x || !l_xx) return fail(CILQR_E_ARG, "null argument");
     if (int rc = need_obstacles(h, B)) return rc;
     if (B == 0) return 0;
+    DeviceScope scope(h->device);
     cudaStream_t st = (cudaStream_t)stream;
     const int N = h->dp.N;
     StageArgs A = stage_args(h, B, STAGE_STATE_COST);
@@ -1188,6 +1221,7 @@ int cilqr_control_cost(cilqr_handle h, int B, const double *X, const double *U, 
     if (int rc = check_handle(h, B)) return rc;
     if (!X || !U || !l_u || !l_uu) return fail(CILQR_E_ARG, "null argument");
     if (B == 0) return 0;
+    DeviceScope scope(h->device);
     cudaStream_t st = (cudaStream_t)stream;
     const int N = h->dp.N;
     StageArgs A = stage_args(h, B, STAGE_CONTROL_COST);
@@ -1208,6 +1242,7 @@ int cilqr_cost(cilqr_handle h, int B, const double *X, const double *U, const do
     if (int rc = check_handle(h, B)) return rc;
     if (!X || !U || !poly || !xlp || !J) return fail(CILQR_E_ARG, "null argument");
     if (B == 0) return 0;
+    DeviceScope scope(h->device);
     cudaStream_t st = (cudaStream_t)stream;
     const int N = h->dp.N;
     StageArgs A = stage_args(h, B, STAGE_COST);
@@ -1229,6 +1264,7 @@ int cilqr_backward(cilqr_handle h, int B, const double *X, const double *U, cons
     if (!X || !U || !poly || !xlp || !lamb || !k || !K) return fail(CILQR_E_ARG, "null argument");
     if (int rc = need_obstacles(h, B)) return rc;
     if (B == 0) return 0;
+    DeviceScope scope(h->device);
     cudaStream_t st = (cudaStream_t)stream;
     const int N = h->dp.N;
     StageArgs A = stage_args(h, B, STAGE_BACKWARD);
@@ -1254,6 +1290,7 @@ int cilqr_forward(cilqr_handle h, int B, const double *X, const double *U, const
     if (int rc = check_handle(h, B)) return rc;
     if (!X || !U || !k || !K || !X_new || !U_new) return fail(CILQR_E_ARG, "null argument");
     if (B == 0) return 0;
+    DeviceScope scope(h->device);
     cudaStream_t st = (cudaStream_t)stream;
     const int N = h->dp.N;
     StageArgs A = stage_args(h, B, STAGE_FORWARD);

@@ -29,6 +29,7 @@
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 
 namespace cilqr
 {
@@ -389,6 +390,9 @@ struct WarpWorkspace { // staging for CILQR_MEM_HOST callers (process-wide, grow
     DevBuf src, poses, bbox, out, idx;
 };
 WarpWorkspace g_ws;
+// Host-buffer calls share g_ws: one at a time, from the first reserve() to the synchronize that ends the call (a second
+// thread's reserve() would free buffers the first thread's kernel is still using).  Device-buffer calls never touch it.
+std::mutex g_ws_mutex;
 } // namespace
 
 extern "C" {
@@ -443,7 +447,9 @@ int costmap_warp_batch(const float *src, const costmap_geom *src_geom, const cos
     const double *d_poses = poses;
     float *d_out = out;
     int32_t *d_idx = idx;
+    std::unique_lock<std::mutex> ws_lock(g_ws_mutex, std::defer_lock);
     if (mem == CILQR_MEM_HOST) {
+        ws_lock.lock();
         if (int rc = g_ws.src.reserve(scells * sizeof(float))) return rc;
         if (int rc = g_ws.poses.reserve((size_t)P * 4 * sizeof(double))) return rc;
         if (int rc = g_ws.out.reserve(P * cells * sizeof(float))) return rc;

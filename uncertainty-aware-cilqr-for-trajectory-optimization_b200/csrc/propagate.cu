@@ -16,6 +16,7 @@
 #include <cfloat>
 #include <climits>
 #include <cmath>
+#include <mutex>
 
 namespace cilqr
 {
@@ -144,9 +145,11 @@ __global__ void __launch_bounds__(kPropThreads) propagate_kernel(const PropGeom 
     const bool maj0 = E.D0 > E.D1;
     const float Dmaj = maj0 ? E.D0 : E.D1, Dmin = maj0 ? E.D1 : E.D0;
     const float Vm0 = maj0 ? E.V00 : E.V10, Vm1 = maj0 ? E.V01 : E.V11; // ROW `major` of V, as the reference takes it
-    double angle = atan2((double)Vm1, (double)Vm0);
+    // The reference's functor calls unqualified atan2 / sqrt on the FLOAT entries of Matrix2f (ARBIT.cuh:91-97; under nvcc these
+    // are CUDA's float overloads, under g++ with `using namespace std` the std:: float overloads): atan2f / sqrtf, widened.
+    double angle = (double)atan2f(Vm1, Vm0);
     if (angle < 0) angle += 6.28318530718;
-    const double half_major = 2.4477 * sqrt((double)Dmaj), half_minor = 2.4477 * sqrt((double)Dmin);
+    const double half_major = 2.4477 * (double)sqrtf(Dmaj), half_minor = 2.4477 * (double)sqrtf(Dmin);
     // W4: EllipseIterator(map, centre, Length(2a, 2b), angle)
     const double len0 = 2 * half_major, len1 = 2 * half_minor;
     const double sas0 = (0.5 * len0) * (0.5 * len0), sas1 = (0.5 * len1) * (0.5 * len1);
@@ -218,6 +221,7 @@ struct PropWorkspace {
     DevBuf map, count, value;
 };
 PropWorkspace g_pw;
+std::mutex g_pw_mutex; // host-buffer calls share g_pw: serialised from the first reserve() to the final synchronize
 } // namespace
 
 extern "C" int costmap_propagate_uncertainty(const float *map, const costmap_geom *geom, double sin_theta, double cos_theta, double sigma_x,
@@ -246,7 +250,9 @@ extern "C" int costmap_propagate_uncertainty(const float *map, const costmap_geo
     const float *d_map = map;
     int32_t *d_count = count;
     double *d_value = value;
+    std::unique_lock<std::mutex> pw_lock(g_pw_mutex, std::defer_lock);
     if (mem == CILQR_MEM_HOST) {
+        pw_lock.lock();
         if (int rc = g_pw.map.reserve((size_t)cells * sizeof(float))) return rc;
         if (int rc = g_pw.count.reserve((size_t)n * sizeof(int32_t))) return rc;
         if (int rc = g_pw.value.reserve((size_t)n * sizeof(double))) return rc;

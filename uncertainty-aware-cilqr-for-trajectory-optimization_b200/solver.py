@@ -128,17 +128,22 @@ class iLQR:
     Result members keep the reference's names: X_result, U_result (plus J_result, iterations, status);
     `control_seq` is the warm start carried between run_step() calls, un-shifted like the reference's."""
 
-    def __init__(self, params, max_batch=1, max_obs=0, stream=None, compute_token=None):
+    def __init__(self, params, max_batch=1, max_obs=0, stream=None, compute_token=None, device=None, options=None):
         """`stream`: CUDA stream for calls with host (numpy) arrays — give every handle its own when several host threads
         drive one GPU, so that one thread's copies and kernels do not queue behind the other's (device arrays always use
         torch's current stream).  `compute_token`: True when several such handles are solving at the same time
-        (cilqr_set_compute_token: their kernels take turns, their copies overlap); None leaves the library's default."""
+        (cilqr_set_compute_token: their kernels take turns, their copies overlap); None leaves the library's default.
+        `device`: CUDA device index of the handle (cilqr_create_on), None = the current device.  `options`: {OPT_*: value}
+        scheduling options (cilqr_set_option; results are bit-identical for every setting)."""
         self.lib = load_library()
         self.stream = stream
         self.params = params.copy()
         self.max_batch, self.max_obs = int(max_batch), int(max_obs)
         self._h = C.c_void_p()
-        _check(self.lib.cilqr_create(C.byref(self.params), C.c_int(self.max_batch), C.c_int(self.max_obs), C.byref(self._h)))
+        _check(self.lib.cilqr_create_on(C.byref(self.params), C.c_int(self.max_batch), C.c_int(self.max_obs),
+                                        C.c_int(-1 if device is None else int(device)), C.byref(self._h)))
+        for k, v in (options or {}).items():
+            self.set_option(k, v)
         if compute_token is not None:
             _check(self.lib.cilqr_set_compute_token(self._h, C.c_int(1 if compute_token else 0)))
         N = self.params.horizon
@@ -149,6 +154,10 @@ class iLQR:
         self.X_result = self.U_result = self.J_result = self.iterations = self.status = None
         self.k = self.K = self.X_new = self.U_new = None
         self.localplanner = None
+
+    def set_option(self, option, value):
+        """cilqr_set_option: OPT_FUSED_FROM_ROUND, OPT_FUSED_SLOTS, OPT_CHUNKS, OPT_GRAPH, OPT_DERIV_STAGED, OPT_TRACE."""
+        _check(self.lib.cilqr_set_option(self._h, C.c_int(int(option)), C.c_int(int(value))))
 
     def close(self):
         if getattr(self, "_h", None) is not None and self._h.value:
@@ -340,7 +349,7 @@ class iLQR:
         return int(cp.value), int(dp.value), int(r.value)
 
     def solve_trace(self):
-        """Timeline of the last solve (handle created with CILQR_TRACE=1): list of (chunk, round, kind, start_ns, end_ns),
+        """Timeline of the last solve (handle with OPT_TRACE set): list of (chunk, round, kind, start_ns, end_ns),
         times relative to the first start, sorted by start; kind in ("cost", "derivs", "sweep", "init", "output")."""
         n_cnt = self.params.max_iterations + 3
         kinds = 4
