@@ -232,6 +232,17 @@ int cilqr_forward(cilqr_handle h, int B, const double *X, const double *U, const
                   const double *K, const double *alpha /*[B] or NULL*/, double *X_new, double *U_new,
                   int mem, void *stream);
 
+/* Constraints::find_closest_point (Constraints.cpp:24-59): state [B][4] (x, y read) -> point [B][2] on the 200-sample polyline. */
+int cilqr_closest_point(cilqr_handle h, int B, const double *state, const double *poly, const double *xlp,
+                        double *point, int mem, void *stream);
+/* Model::get_A_matrix / get_B_matrix (Model.cpp:100-155): velocity, theta, acceleration [B][N] -> the reference's TRANSPOSED
+ * Jacobians as column-major tensors, A_t [B][16*N] = Tensor(4,4,N), B_t [B][8*N] = Tensor(2,4,N). */
+int cilqr_linearize(cilqr_handle h, int B, const double *velocity, const double *theta, const double *acceleration,
+                    double *A_t, double *B_t, int mem, void *stream);
+/* Model::forward_simulate (Model.cpp:17-30), one step: state [B][4], control [B][2] -> next [B][4]. */
+int cilqr_forward_simulate(cilqr_handle h, int B, const double *state, const double *control, double *next,
+                           int mem, void *stream);
+
 /*
  * LocalPlanner (LocalPlanner.cpp:24-116) as iLQR::run_step uses it (iLQR.cpp:247-255), for B ego states on one shared
  * global plan: closest_point_index (:24-41), get_local_wpts (:47-60: the next num_of_local_wpts waypoints),

@@ -261,6 +261,13 @@ class RefOracle(_Base):
                                                 _d(X), _d(J), C.c_int(threads))
         return dict(U=U.reshape(B, -1), X=X, J=J, threads=int(used))
 
+    def linearize(self, p, v, th, acc):
+        """Model::get_A_matrix / get_B_matrix -> (A_t [16 N], B_t [8 N]), the reference's transposed-Jacobian tensors."""
+        v, th, acc = _c64(v), _c64(th), _c64(acc)
+        A, B = np.zeros(16 * p.horizon), np.zeros(8 * p.horizon)
+        self._fn("linearize")(C.byref(p), _d(v), _d(th), _d(acc), _d(A), _d(B))
+        return A, B
+
     def local_plan(self, p, plan, ego):
         plan = np.ascontiguousarray(plan, dtype=np.float64)  # [n][2] == column-major 2 x n
         ego = _c64(ego)

@@ -254,6 +254,17 @@ extern "C"
         for (int i = 0; i < 4; ++i) xn[i] = r(i);
     }
 
+    // Model::get_A_matrix / get_B_matrix (Model.cpp:100-155): the transposed Jacobians as column-major tensors.
+    void ref_linearize(const cilqr_params *c, const double *v, const double *th, const double *acc, double *A_t, double *B_t)
+    {
+        Parameters p = to_ref(*c);
+        Model m(p);
+        Eigen::Tensor<double, 3> A = m.get_A_matrix(vec(v, p.horizon), vec(th, p.horizon), vec(acc, p.horizon));
+        Eigen::Tensor<double, 3> B = m.get_B_matrix(vec(th, p.horizon));
+        std::memcpy(A_t, A.data(), sizeof(double) * 16 * p.horizon);
+        std::memcpy(B_t, B.data(), sizeof(double) * 8 * p.horizon);
+    }
+
     // iLQR::get_nominal_trajectory (iLQR.cpp:51-62)
     void ref_rollout(const cilqr_params *c, const double *x0, const double *U, double *X)
     {

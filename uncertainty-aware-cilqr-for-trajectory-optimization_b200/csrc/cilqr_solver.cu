@@ -79,7 +79,7 @@ __device__ __forceinline__ void store_states(const WarpSmem &W, double *__restri
 }
 
 // ------------------------------------------------------------------------------------------------- stage kernel
-enum { STAGE_ROLLOUT = 0, STAGE_STATE_COST, STAGE_CONTROL_COST, STAGE_COST, STAGE_BACKWARD, STAGE_FORWARD };
+enum { STAGE_ROLLOUT = 0, STAGE_STATE_COST, STAGE_CONTROL_COST, STAGE_COST, STAGE_BACKWARD, STAGE_FORWARD, STAGE_CLOSEST, STAGE_LINEARIZE, STAGE_STEP };
 
 struct StageArgs {
     DevParams P;
@@ -97,6 +97,54 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) stage_kernel(const StageA
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const WarpSmem W = carve(smem + (size_t)warp * warp_smem_doubles(N, P.S), N, P.S);
     for (int b = blockIdx.x * kWarpsPerBlock + warp; b < A.B; b += gridDim.x * kWarpsPerBlock) {
+        if (A.stage == STAGE_LINEARIZE) { // Model::get_A_matrix / get_B_matrix (Model.cpp:100-155): the TRANSPOSED Jacobians, 4x4xN / 2x4xN
+            const double *v = A.X + (size_t)b * N, *th = A.U + (size_t)b * N, *acc = A.k + (size_t)b * N;
+            for (int t = lane; t < N; t += 32) {
+                double s, c;
+                sincos(th[t], &s, &c);
+                const double d = v[t] * P.dt + 0.5 * acc[t] * P.dt * P.dt;
+                double *At = A.o0 + ((size_t)b * N + t) * 16, *Bt = A.o1 + ((size_t)b * N + t) * 8;
+#pragma unroll
+                for (int e = 0; e < 16; ++e)
+                    At[e] = (e % 5 == 0) ? 1.0 : 0.0;
+                At[2] = P.dt * c; At[3] = -1.0 * s * d;  // A(2,0,i), A(3,0,i)
+                At[6] = P.dt * s; At[7] = c * d;         // A(2,1,i), A(3,1,i)
+#pragma unroll
+                for (int e = 0; e < 8; ++e)
+                    Bt[e] = 0.0;
+                Bt[0] = P.dt * P.dt * c / 2.0;           // B(0,0,i)
+                Bt[2] = P.dt * P.dt * s / 2.0;           // B(0,1,i)
+                Bt[4] = P.dt;                            // B(0,2,i)
+                Bt[7] = P.dt;                            // B(1,3,i)
+            }
+            continue;
+        }
+        if (A.stage == STAGE_STEP) { // Model::forward_simulate (Model.cpp:17-30), one step
+            if (lane == 0) {
+                const double *x = A.x0 + 4 * (size_t)b, *u = A.U + 2 * (size_t)b;
+                double s, c, m0, m1, m2, m3;
+                sincos(x[3], &s, &c);
+                dyn_step(P, x[0], x[1], x[2], x[3], c, s, u[0], u[1], m0, m1, m2, m3);
+                double *o = A.o0 + 4 * (size_t)b;
+                o[0] = m0; o[1] = m1; o[2] = m2; o[3] = m3;
+            }
+            continue;
+        }
+        if (A.stage == STAGE_CLOSEST) { // Constraints::find_closest_point (Constraints.cpp:24-59)
+            Polyline pq;
+            pq.x_first = A.xlp[2 * b];
+            pq.dxs = (A.xlp[2 * b + 1] - A.xlp[2 * b]) / P.S;
+            build_polyline(P, A.poly + (size_t)b * P.npoly, pq, W.Y, lane);
+            __syncwarp();
+            if (lane == 0) {
+                double cx, cy;
+                closest_point(P, pq, W.Y, A.x0[4 * (size_t)b], A.x0[4 * (size_t)b + 1], cx, cy);
+                A.o0[2 * (size_t)b] = cx;
+                A.o0[2 * (size_t)b + 1] = cy;
+            }
+            __syncwarp();
+            continue;
+        }
         Polyline pl{0.0, 0.0};
         if (A.poly) {
             pl.x_first = A.xlp[2 * b];
@@ -439,10 +487,14 @@ static int create_impl(cilqr_solver *h, int dev)
         h->occ_sweep = std::max(1, o3);
     }
     { // slots per CTA of the fused kernel: two CTAs per SM (1 KB per CTA is the system's), else one CTA with what fits
-        const size_t per_slot = fused_smem_bytes(h->dp.N, 1) - 16, two = (size_t)h->smem_per_sm / 2 - 1024, one = (size_t)h->smem_optin;
-        size_t g = (two - 16) / per_slot;
-        if (g < 4) g = (one - 16) / per_slot;
-        h->fused_slots_max = (int)std::min<size_t>(g, kFusedMaxSlots);
+        const size_t two = (size_t)h->smem_per_sm / 2 - 1024, one = (size_t)h->smem_optin;
+        int g = kFusedMaxSlots;
+        while (g > 0 && fused_smem_bytes(h->dp.N, g) > two) --g;
+        if (g < 4) {
+            g = kFusedMaxSlots;
+            while (g > 0 && fused_smem_bytes(h->dp.N, g) > one) --g;
+        }
+        h->fused_slots_max = g;
     }
     if (const char *e = getenv("CILQR_EXCLUSIVE")) h->exclusive = atoi(e) != 0; // documented in cilqr.h (cilqr_set_compute_token)
     bool ok = cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming) == cudaSuccess;
@@ -642,13 +694,13 @@ struct HostIO { // caller's host arrays (CILQR_MEM_HOST) — null members when t
 // How one n_alphas == 1 solve is laid out: K chunks of Bc scenarios; rounds 0 .. r0 - 1 as batch-synchronous round kernels,
 // the rest (r0 == 0: everything) in the fused kernel with G slots per CTA.
 struct SolvePlan {
-    int K, Bc, r0, G, fused_occ;
+    int K, Bc, r0, G, fused_grid;
     size_t fused_smem;
 };
 
 static int launch_fused(cilqr_handle h, const FusedArgs &F, int work, const SolvePlan &plan, cudaStream_t st)
 {
-    const int grid = std::max(1, std::min((work + F.G - 1) / F.G, h->num_sms * plan.fused_occ));
+    const int grid = std::max(1, std::min((work + F.G - 1) / F.G, plan.fused_grid));
     if (h->obs_cv)
         fused_solve_kernel<true><<<grid, kFusedThreads, plan.fused_smem, st>>>(F);
     else
@@ -833,12 +885,17 @@ static int solve_rounds(cilqr_handle h, const SolveArgs &A, const HostIO *io, cu
     if (io && h->exclusive == 1) K = 1;
     plan.Bc = ((B + K - 1) / K + 31) / 32 * 32; // chunk size, a multiple of the warp size
     plan.K = K = (B + plan.Bc - 1) / plan.Bc;
-    // Where the solve runs.  Automatic: on chip from the start (cilqr_fused.cuh) whenever the horizon leaves room for at least
-    // one slot; CILQR_OPT_FUSED_FROM_ROUND = r > 0 keeps rounds 0 .. r - 1 as batch-synchronous round kernels (the first rounds
-    // of a large batch fill every lane of those), r > max_iterations never leaves them.
-    plan.r0 = h->fused_from >= 0 ? h->fused_from : 0;
+    // Where the solve runs.  Automatic: a batch of up to kFusedAutoBatch scenarios (one rank's shard of a sharded solve, a
+    // receding-horizon fleet) goes on chip from the start (cilqr_fused.cuh): it is bound by the ~100 us floor of a round, which
+    // the fused kernel does not have (8 192 scenarios x 20 obstacles: 1.3 ms against 1.8 ms).  A larger batch fills every lane of
+    // the round kernels and runs faster there (65 536: 5.2 ms against 6.6 ms — the fused kernel sweeps at 14 of 32 lanes and its
+    // phases are separated by CTA-wide barriers).  CILQR_OPT_FUSED_FROM_ROUND = r forces the choice: 0 = fused from the start,
+    // r > 0 = rounds 0 .. r - 1 as round kernels and the still-active scenarios handed over, r > max_iterations = round
+    // kernels only.
+    constexpr int kFusedAutoBatch = 16384;
+    plan.r0 = h->fused_from >= 0 ? h->fused_from : (B <= kFusedAutoBatch ? 0 : P.max_iter + 1);
     plan.G = 0;
-    plan.fused_occ = 1;
+    plan.fused_grid = 1;
     plan.fused_smem = 0;
     if (h->fused_slots_max < 1 || (h->trace_on && plan.r0 == 0)) plan.r0 = P.max_iter + 1; // (the trace is a feature of the round kernels)
     if (plan.r0 <= P.max_iter) {
@@ -853,7 +910,7 @@ static int solve_rounds(cilqr_handle h, const SolveArgs &A, const HostIO *io, cu
         else
             CILQR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fused_solve_kernel<false>, kFusedThreads, plan.fused_smem));
         if (occ < 1) return fail(CILQR_E_CUDA, "fused solve kernel does not fit on an SM (%zu B of shared memory)", plan.fused_smem);
-        plan.fused_occ = occ;
+        plan.fused_grid = std::max(1, std::min((std::min(plan.Bc, B) + G - 1) / G, h->num_sms * occ));
     }
     if (plan.r0 > 0) {
         const size_t n_dbl = (size_t)B * kHdrD + (size_t)B * (N + 1) * kStepD;
@@ -1308,6 +1365,63 @@ int cilqr_forward(cilqr_handle h, int B, const double *X, const double *U, const
     if (int rc = run_stage(h, A, st)) return rc;
     if (int rc = fetch_out(X_new, A.o0, (size_t)B * 4 * (N + 1), mem, st)) return rc;
     if (int rc = fetch_out(U_new, A.o1, (size_t)B * 2 * N, mem, st)) return rc;
+    if (mem == CILQR_MEM_HOST) CILQR_CUDA(cudaStreamSynchronize(st));
+    return 0;
+}
+
+int cilqr_closest_point(cilqr_handle h, int B, const double *state, const double *poly, const double *xlp, double *point, int mem, void *stream)
+{
+    if (int rc = check_handle(h, B)) return rc;
+    if (!state || !poly || !xlp || !point) return fail(CILQR_E_ARG, "null argument");
+    if (B == 0) return 0;
+    DeviceScope scope(h->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    StageArgs A = stage_args(h, B, STAGE_CLOSEST);
+    if (int rc = stage_in(h, 3, state, (size_t)B * 4, mem, st, &A.x0)) return rc;
+    if (int rc = stage_in(h, 5, poly, (size_t)B * h->dp.npoly, mem, st, &A.poly)) return rc;
+    if (int rc = stage_in(h, 6, xlp, (size_t)B * 2, mem, st, &A.xlp)) return rc;
+    if (int rc = stage_out(h, 7, point, (size_t)B * 2, mem, &A.o0)) return rc;
+    if (int rc = run_stage(h, A, st)) return rc;
+    if (int rc = fetch_out(point, A.o0, (size_t)B * 2, mem, st)) return rc;
+    if (mem == CILQR_MEM_HOST) CILQR_CUDA(cudaStreamSynchronize(st));
+    return 0;
+}
+
+int cilqr_linearize(cilqr_handle h, int B, const double *velocity, const double *theta, const double *acceleration, double *A_t, double *B_t,
+                    int mem, void *stream)
+{
+    if (int rc = check_handle(h, B)) return rc;
+    if (!velocity || !theta || !acceleration || !A_t || !B_t) return fail(CILQR_E_ARG, "null argument");
+    if (B == 0) return 0;
+    DeviceScope scope(h->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    const int N = h->dp.N;
+    StageArgs A = stage_args(h, B, STAGE_LINEARIZE);
+    if (int rc = stage_in(h, 3, velocity, (size_t)B * N, mem, st, &A.X)) return rc;
+    if (int rc = stage_in(h, 4, theta, (size_t)B * N, mem, st, &A.U)) return rc;
+    if (int rc = stage_in(h, 5, acceleration, (size_t)B * N, mem, st, &A.k)) return rc;
+    if (int rc = stage_out(h, 7, A_t, (size_t)B * 16 * N, mem, &A.o0)) return rc;
+    if (int rc = stage_out(h, 8, B_t, (size_t)B * 8 * N, mem, &A.o1)) return rc;
+    if (int rc = run_stage(h, A, st)) return rc;
+    if (int rc = fetch_out(A_t, A.o0, (size_t)B * 16 * N, mem, st)) return rc;
+    if (int rc = fetch_out(B_t, A.o1, (size_t)B * 8 * N, mem, st)) return rc;
+    if (mem == CILQR_MEM_HOST) CILQR_CUDA(cudaStreamSynchronize(st));
+    return 0;
+}
+
+int cilqr_forward_simulate(cilqr_handle h, int B, const double *state, const double *control, double *next, int mem, void *stream)
+{
+    if (int rc = check_handle(h, B)) return rc;
+    if (!state || !control || !next) return fail(CILQR_E_ARG, "null argument");
+    if (B == 0) return 0;
+    DeviceScope scope(h->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    StageArgs A = stage_args(h, B, STAGE_STEP);
+    if (int rc = stage_in(h, 3, state, (size_t)B * 4, mem, st, &A.x0)) return rc;
+    if (int rc = stage_in(h, 4, control, (size_t)B * 2, mem, st, &A.U)) return rc;
+    if (int rc = stage_out(h, 7, next, (size_t)B * 4, mem, &A.o0)) return rc;
+    if (int rc = run_stage(h, A, st)) return rc;
+    if (int rc = fetch_out(next, A.o0, (size_t)B * 4, mem, st)) return rc;
     if (mem == CILQR_MEM_HOST) CILQR_CUDA(cudaStreamSynchronize(st));
     return 0;
 }

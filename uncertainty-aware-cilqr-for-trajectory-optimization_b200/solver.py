@@ -18,7 +18,7 @@ import numpy as np
 from .params import Parameters, MEM_HOST, MEM_DEVICE
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-_LIB_PATH = os.path.join(_HERE, "libcilqr_b200.so")
+_LIB_PATH = os.environ.get("CILQR_B200_LIB") or os.path.join(_HERE, "libcilqr_b200.so")  # (the override loads an instrumented build)
 _lib = None
 
 _dp, _ip, _fp, _vp = C.POINTER(C.c_double), C.POINTER(C.c_int32), C.POINTER(C.c_float), C.c_void_p
