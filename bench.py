@@ -1,5 +1,10 @@
 """bench.py — the driver's measurement contract for the CILQR hot path.
 
+    [blocks of the JSON line added in round 2: `roofline` is the FP64 figure (bound "fp64"), `hbm` the HBM one; `strong_scaling`
+    (N > 1: BASELINE config 4 as written, 65 536 scenarios in total sharded over the ranks, gather included); `config3`,
+    `few_obstacles`; `costmap_warp.sweep` (all five config-5 sizes) and CPU baselines inside the two costmap blocks;
+    `e2e.host_ceiling`, `e2e.u_only_value`.]
+
     python bench.py --gpus 1 --steps K --warmup W                  (this repo's CUDA path)
     torchrun ... bench.py --gpus N --steps K --warmup W            (one rank per GPU, NCCL gather of U*)
     python bench.py --impl reference --steps K --warmup W          (the reference's own CPU code, oracle/_ref)
@@ -57,7 +62,9 @@ def parse_args():
     ap.add_argument("--batch", type=int, default=BATCH_PER_GPU, help="scenarios per GPU")
     ap.add_argument("--n-obs", type=int, default=N_OBS)
     ap.add_argument("--n-alphas", type=int, default=1)
-    ap.add_argument("--warp-T", type=int, default=WARP_T)
+    ap.add_argument("--warp-T", type=int, default=0, help="time one costmap grid edge only (0 = the whole config-5 sweep)")
+    ap.add_argument("--no-strong", action="store_true", help="skip the sharded (strong-scaling) block at N > 1")
+    ap.add_argument("--no-extra", action="store_true", help="skip the config-3 and few-obstacle blocks")
     ap.add_argument("--no-warp", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
@@ -245,8 +252,9 @@ def run_reference_arm(args):
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": 1e3 * dt / max(1, args.steps), "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
         "data": "synthetic",
-        "config": {"workload": "config4: 65536 scenarios x 20 uncertain obstacles, N=50 (bounded sample per step)", "horizon": HORIZON,
-                   "n_obs": args.n_obs, "n_alphas": 1, "sample_per_step": n},
+        "config": {"workload": workload_name(args.batch, args.n_obs, 1), "scenarios_per_gpu": args.batch, "horizon": HORIZON,
+                   "n_obs": args.n_obs, "n_alphas": 1, "sample_per_step": n,
+                   "sample": "each CPU step solves the first %d scenarios of the workload (obstacles host-expanded), all host threads" % n},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": used, "kind": chk.kind, "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -254,10 +262,9 @@ def run_reference_arm(args):
     print(json.dumps(line), flush=True)
 
 
-def cpu_baseline_leg(p, args):
+def cpu_baseline_leg(p, args, chk):
     """cpu_baseline of the main arm: ~15 s of the reference CPU solver on all host threads (rank 0, N = 1)."""
     from cilqr_b200 import scenarios
-    chk = cpu_solver()
     cap = 4096
     sc = scenarios.make_scenarios(p, 0, cap, args.n_obs, dense=True)
     n, used = cpu_sample_size(chk, p, sc, target_s=15.0, cap=cap)
@@ -288,65 +295,222 @@ def max_over_ranks(x, world, device):
     return float(t.item())
 
 
-def bench_warp(args, device, hbm_peak, peak_kind):
-    """costmap_warp_batch, BASELINE config 5 at one grid size: target T x T, source 2T x 2T (both larger than L2 once the
-    64-pose chunk of outputs is counted), 1024 poses in chunks of 64, value + index map emitted (12 B per cell)."""
+def workload_name(B_total, n_obs, n_alphas):
+    if (B_total, n_obs, n_alphas) == (BATCH_PER_GPU, N_OBS, 1):
+        return "config4: 65536 scenarios x 20 Gaussian-uncertain obstacles (covariance propagated over the horizon), N=50, n_alphas=1"
+    if (B_total, n_obs, n_alphas) == (4096, 10, 8):
+        return "config3: 4096 scenarios x 10 Gaussian-uncertain obstacles, N=50, 8 parallel line-search alphas"
+    return "custom: %d scenarios x %d Gaussian-uncertain obstacles, N=50, n_alphas=%d" % (B_total, n_obs, n_alphas)
+
+
+FP64_PEAK = {}
+
+
+def fp64_peak(lib):
+    """DFMA micro-benchmark on this GPU (cilqr_measure_fp64_peak): builder-measured, there is no driver-written FP64 figure."""
+    import ctypes as C
+    if "v" not in FP64_PEAK:
+        v = C.c_double(0.0)
+        FP64_PEAK["v"] = v.value if lib.cilqr_measure_fp64_peak(C.byref(v)) != 0 else v.value
+    return FP64_PEAK["v"]
+
+
+def solve_case(args, p, device, rank, world, first_id, B, n_obs, n_alphas, steps, warmup, opts, gather, sampler=None):
+    """Times `steps` solves of scenarios [first_id, first_id + B) on this rank (inputs resident in HBM): per step
+    cilqr_set_obstacles_cv (covariance propagation on device), cilqr_solve_batch, and for world > 1 the NCCL all-gather of U* on
+    its own stream.  Returns the timing, the work tallies and the status histogram; CUDA events, max over ranks."""
     import torch
     import cilqr_b200
     from cilqr_b200 import scenarios
-    T, S = args.warp_T, 2 * args.warp_T
+    N = HORIZON
+    sc = scenarios.make_scenarios(p, first_id, B, n_obs, dense=False)
+    keys = ("x0", "U0", "poly", "xlp", "obs_state0", "obs_LW", "obs_sigma")
+    d = {k: torch.from_numpy(sc[k]).to(device) for k in keys}
+    U = torch.empty_like(d["U0"])
+    solver = cilqr_b200.iLQR(p, max_batch=B, max_obs=max(n_obs, 1), options=opts)
+    merit = cilqr_b200.MERIT_TOTAL if n_alphas > 1 else cilqr_b200.MERIT_TRACKING
+    res = {"X": torch.empty((B, 4 * (N + 1)), dtype=torch.float64, device=device), "J": torch.empty(B, dtype=torch.float64, device=device),
+           "iters": torch.empty(B, dtype=torch.int32, device=device), "status": torch.empty(B, dtype=torch.int32, device=device)}
+    kern_ev = []
+    do_gather = gather and world > 1
+    if do_gather:
+        # The exchange step (SURVEY.md §8(e)) runs on its own stream from a second U buffer: step i's all-gather travels over
+        # NVLink under step i+1's solve, which writes the other buffer (no snapshot copy).  The timed region ends with a
+        # device-wide synchronize, so the last gather is inside it.
+        U2 = torch.empty_like(U)
+        gathered = torch.empty((world * B, 2 * N), dtype=torch.float64, device=device)
+        comm_stream = torch.cuda.Stream(device=device)
+        solved, gathered_ev = torch.cuda.Event(), [torch.cuda.Event(), torch.cuda.Event()]
+        for e in gathered_ev:
+            e.record()
+    bufs = [U, U2] if do_gather else [U]
+    state = {"i": 0}
+
+    def step(timed):
+        i = state["i"]
+        state["i"] += 1
+        Ub = bufs[i % len(bufs)]
+        cur = torch.cuda.current_stream()
+        if do_gather:
+            cur.wait_event(gathered_ev[i % 2])  # the gather that read this buffer two steps ago has finished
+        solver.set_obstacles_cv(d["obs_state0"], d["obs_LW"], d["obs_sigma"], sc["kappa"])  # covariance propagation on device
+        Ub.copy_(d["U0"])
+        if timed:
+            ev = event_pair()
+            ev[0].record()
+        solver.get_optimal_control_seq(d["x0"], Ub, d["poly"], d["xlp"], n_alphas=n_alphas, merit=merit, outputs=res)
+        if timed:
+            ev[1].record()
+            kern_ev.append(ev)
+        if do_gather:
+            solved.record(cur)
+            with torch.cuda.stream(comm_stream):
+                comm_stream.wait_event(solved)
+                torch.distributed.all_gather_into_tensor(gathered, Ub)
+                gathered_ev[i % 2].record(comm_stream)
+        return Ub
+
+    last = None
+    for _ in range(max(warmup, 0)):
+        last = step(False)
+    torch.cuda.synchronize()
+    launches0 = cilqr_b200.launch_count()
+    if world > 1:
+        torch.distributed.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = event_pair()
+    if sampler:
+        sampler.mark_begin()
+    e0.record()
+    for _ in range(steps):
+        last = step(True)
+    e1.record()
+    torch.cuda.synchronize()
+    if sampler:
+        sampler.mark_end()
+    if world > 1:
+        torch.distributed.barrier()
+    total_ms = max_over_ranks(e0.elapsed_time(e1), world, device)
+    if do_gather:
+        assert torch.equal(gathered[rank * B:(rank + 1) * B], last), "all-gather of U*: this rank's slice differs from its own result"
+    launches = cilqr_b200.launch_count() - launches0
+    kernel_ms = float(np.mean([a.elapsed_time(b) for a, b in kern_ev]))
+    iters = solver.iterations.cpu().numpy()
+    status = solver.status.cpu().numpy()
+    stats = solver.solve_stats() if n_alphas == 1 else (int(iters.sum()), int(iters.sum()), int(iters.max()))
+    out = {"total_ms": total_ms, "ms_per_step": total_ms / steps, "kernel_ms": kernel_ms, "launches": int(launches), "stats": stats,
+           "mean_iterations": float(iters.mean()), "U": last.cpu().numpy(), "sc": sc,
+           "status_hist": {"tolerance": int((status == 0).sum()), "max_iter": int((status == 1).sum()), "lamb_max": int((status == 2).sum()),
+                           "nonfinite": int((status == 3).sum())}}
+    solver.close()
+    return out
+
+
+def fp64_block(lib, N, n_obs, B, stats, kernel_ms):
+    flops_launch, per_cost, per_deriv = solver_flops(N, n_obs, stats[0], stats[1])
+    peak = fp64_peak(lib)
+    tf = flops_launch / (kernel_ms * 1e-3) / 1e12
+    return {"bound": "fp64", "achieved": tf, "peak": peak, "unit": "TFLOP/s", "frac": tf / peak if peak else None,
+            "peak_source": "builder-measured: DFMA micro-benchmark on this GPU (cilqr_measure_fp64_peak); MEASURED_PEAKS.json has no FP64 figure",
+            "flops_per_cost_pass": per_cost, "flops_per_derivative_pass": per_deriv, "cost_passes_per_solve": stats[0] / B,
+            "derivative_passes_per_solve": stats[1] / B, "rounds": stats[2], "kernel_ms": kernel_ms,
+            "counting": "each operation once, exp / sincos = 20 flops (DESIGN.md section 5)"}
+
+
+def bench_warp(args, device, hbm_peak, peak_kind, chk):
+    """costmap_warp_batch over BASELINE config 5: target T x T from a 2T x 2T source, T in {256 .. 4096}, 1024 poses in chunks,
+    value + index map emitted (12 B per cell).  T = 4096 is the headline: its 268 MB source does not fit L2, so the gathers really
+    come from HBM (at T <= 2048 the source is L2-resident and algorithmic bytes overstate what HBM moves)."""
+    import torch
+    import cilqr_b200
+    from cilqr_b200 import scenarios
     G = cilqr_b200.CostmapGeom
-    sg, tg = G(S * 0.2, S * 0.2, 0.2, 0.0, 0.0), G(T * 0.2, T * 0.2, 0.2, 0.0, 0.0)
-    src = torch.from_numpy(scenarios.make_source_map(S, S, nan_band=False)).to(device)
-    chunk = max(1, min(WARP_POSES, WARP_CHUNK_BYTES // (T * T * 8)))
-    poses = torch.from_numpy(scenarios.make_poses(WARP_POSES, (0.0, 0.0), 0.05 * T * 0.2)).to(device)
-    out = torch.empty((chunk, T * T), dtype=torch.float32, device=device)
-    idx = torch.empty((chunk, T * T), dtype=torch.int32, device=device)
-    res = {}
-    for name, with_idx in (("value_only", False), ("value_and_index", True)):
-        def sweep():
-            for c in range(0, WARP_POSES, chunk):
-                cilqr_b200.warp_batch(src, sg, tg, poses[c:c + chunk], out=out[:min(chunk, WARP_POSES - c)],
-                                      idx=idx[:min(chunk, WARP_POSES - c)] if with_idx else None, want_idx=False)
-        sweep()
-        torch.cuda.synchronize()
-        e0, e1 = event_pair()
-        e0.record()
-        sweep()
-        e1.record()
-        torch.cuda.synchronize()
-        ms = e0.elapsed_time(e1)
-        by = WARP_POSES * T * T * (12 if with_idx else 8)
-        res[name] = {"gbs": by / ms / 1e6, "ms_per_pose": ms / WARP_POSES, "bytes_per_cell": 12 if with_idx else 8}
-    best = res["value_and_index"]
-    return {"metric": "costmap warp HBM GB/s", "value": best["gbs"], "unit": "GB/s",
-            "config": {"workload": "config5: target %dx%d from source %dx%d, %d poses in chunks of %d, float value + int32 index map"
-                                   % (T, T, S, S, WARP_POSES, chunk), "l2": "working set per chunk larger than L2"},
-            "value_only_gbs": res["value_only"]["gbs"],
-            "roofline": {"bound": "hbm", "achieved": best["gbs"], "peak": hbm_peak, "unit": "GB/s", "frac": best["gbs"] / hbm_peak,
-                         "traffic": recorded_traffic("warp_dram_bytes_per_launch") if T == WARP_T else None, "peak_source": peak_kind,
-                         "algorithmic_bytes_per_cell": "4 B source read + 4 B value write + 4 B index write"},
-            "launches": 2 * 2 * ((WARP_POSES + chunk - 1) // chunk)}
+    sizes = [args.warp_T] if args.warp_T else [256, 512, 1024, 2048, 4096]
+    sweep = []
+    for T in sizes:
+        S = 2 * T
+        sg, tg = G(S * 0.2, S * 0.2, 0.2, 0.0, 0.0), G(T * 0.2, T * 0.2, 0.2, 0.0, 0.0)
+        src = torch.from_numpy(scenarios.make_source_map(S, S, nan_band=False)).to(device)
+        chunk = max(1, min(WARP_POSES, WARP_CHUNK_BYTES // (T * T * 8)))
+        poses = torch.from_numpy(scenarios.make_poses(WARP_POSES, (0.0, 0.0), 0.05 * T * 0.2)).to(device)
+        out = torch.empty((chunk, T * T), dtype=torch.float32, device=device)
+        idx = torch.empty((chunk, T * T), dtype=torch.int32, device=device)
+        res = {}
+        for name, with_idx in (("value_only", False), ("value_and_index", True)):
+            def sweep_once():
+                for c in range(0, WARP_POSES, chunk):
+                    cilqr_b200.warp_batch(src, sg, tg, poses[c:c + chunk], out=out[:min(chunk, WARP_POSES - c)],
+                                          idx=idx[:min(chunk, WARP_POSES - c)] if with_idx else None, want_idx=False)
+            sweep_once()
+            torch.cuda.synchronize()
+            e0, e1 = event_pair()
+            e0.record()
+            sweep_once()
+            e1.record()
+            torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1)
+            by = WARP_POSES * T * T * (12 if with_idx else 8)
+            res[name] = {"gbs": by / ms / 1e6, "ms_per_pose": ms / WARP_POSES}
+        best = res["value_and_index"]
+        sweep.append({"T": T, "source": "%dx%d (%.0f MB)" % (S, S, S * S * 4 / 1e6), "poses": WARP_POSES, "chunk": chunk, "gbs": best["gbs"],
+                      "frac": best["gbs"] / hbm_peak, "value_only_gbs": res["value_only"]["gbs"], "ms_per_pose": best["ms_per_pose"],
+                      "traffic": recorded_traffic("warp_dram_bytes_per_launch_T%d" % T), "launches_counted": 4 * ((WARP_POSES + chunk - 1) // chunk),
+                      "source_in_l2": S * S * 4 < 100e6})
+        del src, out, idx
+        torch.cuda.empty_cache()
+    head = [e for e in sweep if e["T"] == 4096] or [sweep[-1]]
+    head = head[0]
+    blk = {"metric": "costmap warp HBM GB/s", "value": head["gbs"], "unit": "GB/s",
+           "config": {"workload": "config5: target TxT from source 2Tx2T, %d poses in chunks, float value + int32 index map; headline T=%d "
+                                  "(source larger than L2)" % (WARP_POSES, head["T"]), "l2": "working set per chunk larger than L2"},
+           "roofline": {"bound": "hbm", "achieved": head["gbs"], "peak": hbm_peak, "unit": "GB/s", "frac": head["gbs"] / hbm_peak,
+                        "traffic": head["traffic"], "peak_source": peak_kind,
+                        "algorithmic_bytes_per_cell": "4 B source read + 4 B value write + 4 B index write"},
+           "sweep": sweep, "launches": sum(e["launches_counted"] for e in sweep)}
+    if chk is not None and hasattr(chk, "warp"):  # CPU baseline (iii) of SURVEY.md section 8(d): the reference loop, 1 thread and OpenMP over poses
+        T = 1024
+        S = 2 * T
+        sg, tg = G(S * 0.2, S * 0.2, 0.2, 0.0, 0.0), G(T * 0.2, T * 0.2, 0.2, 0.0, 0.0)
+        srcn = scenarios.make_source_map(S, S, nan_band=False)
+        cores = os.cpu_count() or 1
+        posn = scenarios.make_poses(max(2, cores), (0.0, 0.0), 0.05 * T * 0.2)
+        t0 = time.perf_counter()
+        chk.warp(srcn, sg, tg, posn[:2], want_idx=True, threads=1)
+        t1 = time.perf_counter()
+        chk.warp(srcn, sg, tg, posn, want_idx=True, threads=cores)
+        t2 = time.perf_counter()
+        blk["cpu_baseline"] = {"kind": chk.kind, "unit": "GB/s", "cores": cores, "value": len(posn) * T * T * 12 / (t2 - t1) / 1e9,
+                               "single_thread_value": 2 * T * T * 12 / (t1 - t0) / 1e9,
+                               "sample": "T=%d: 2 poses on one thread, %d poses over %d threads (local_costmap.cpp:242-264 on grid_map::GridMap objects)"
+                                         % (T, len(posn), cores)}
+    return blk
 
 
-def bench_propagate(args, device, hbm_peak, peak_kind):
-    """costmap_propagate_uncertainty (rows W2-W4: per-cell covariance -> ellipse -> Gaussian average), the reference's
-    experiment sigmas on BASELINE config 2's 400 x 400 local costmap at 0.2 m.  The work per cell grows with the square of its
-    distance from the map origin (the heading sigma's lever arm sets the ellipse), so the map size is part of the metric; the
-    2.6 MB working set is L2-resident, which is the kernel's operating point in the reference's node as well."""
+def propagate_flops(counts):
+    """Algorithmic FP64 flops of costmap_propagate_uncertainty: per cell ~120 (covariance, float eigen-solve, ellipse set-up, the
+    final division), per cell of its bounding box 12 (position, rotation, membership test), per cell inside the ellipse 14 + exp (20).
+    The box is ~4/pi of the ellipse's area."""
+    inside = float(np.sum(counts))
+    return 120.0 * counts.size + 12.0 * inside * 4.0 / math.pi + 34.0 * inside
+
+
+def bench_propagate(args, device, lib, chk):
+    """costmap_propagate_uncertainty (rows W2-W4), the reference's experiment sigmas on BASELINE config 2's 400 x 400 local costmap
+    at 0.2 m.  FP64 / divergence bound: the map (640 KB) is L2-resident, as in the reference's node."""
     import torch
     import cilqr_b200
     from cilqr_b200 import scenarios
     S = 400
     g = cilqr_b200.CostmapGeom(S * 0.2, S * 0.2, 0.2, 0.0, 0.0)
-    src = torch.from_numpy(scenarios.make_source_map(S, S, nan_band=False)).to(device)
+    srcn = scenarios.make_source_map(S, S, nan_band=False)
+    src = torch.from_numpy(srcn).to(device)
     sig = scenarios.SIGMA_EXPERIMENT
 
     def once():
         return cilqr_b200.propagate_uncertainty(src, g, math.sin(0.7), math.cos(0.7), *sig)
 
     for _ in range(2):
-        once()
+        cnt, _ = once()
     torch.cuda.synchronize()
     reps = 20
     e0, e1 = event_pair()
@@ -356,21 +520,156 @@ def bench_propagate(args, device, hbm_peak, peak_kind):
     e1.record()
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / reps
-    by = S * S * (4 + 4 + 8)
-    return {"metric": "uncertainty propagation Mcells/s", "value": S * S / ms / 1e3, "unit": "Mcells/s", "ms_per_map": ms,
-            "config": {"workload": "%dx%d map, 0.2 m cells, sigma (x, y, theta) = %s, all cells" % (S, S, tuple(sig)),
-                       "l2": "L2-resident (2.6 MB per map), as in the reference's map node"},
-            "roofline": {"bound": "hbm", "achieved": by / ms / 1e6, "peak": hbm_peak, "unit": "GB/s", "frac": by / ms / 1e6 / hbm_peak, "traffic": None,
-                         "peak_source": peak_kind, "algorithmic_bytes_per_cell": "4 B map read + 4 B count + 8 B value written",
-                         "note": "FP64 / divergence bound: each cell averages the map over its own uncertainty ellipse (a data-dependent number of cells)"},
-            "launches": reps + 2}
+    flops = propagate_flops(cnt.cpu().numpy())
+    peak = fp64_peak(lib)
+    blk = {"metric": "uncertainty propagation Mcells/s", "value": S * S / ms / 1e3, "unit": "Mcells/s", "ms_per_map": ms,
+           "config": {"workload": "%dx%d map, 0.2 m cells, sigma (x, y, theta) = %s, all cells" % (S, S, tuple(sig)),
+                      "l2": "L2-resident (2.6 MB per map), as in the reference's map node"},
+           "roofline": {"bound": "fp64", "achieved": flops / (ms * 1e-3) / 1e12, "peak": peak, "unit": "TFLOP/s",
+                        "frac": flops / (ms * 1e-3) / 1e12 / peak if peak else None, "traffic": None,
+                        "peak_source": "builder-measured DFMA micro-benchmark (cilqr_measure_fp64_peak)", "flops_per_map": flops,
+                        "note": "each cell averages the map over its own uncertainty ellipse (a data-dependent number of cells): divergence bound"},
+           "launches": reps + 2}
+    if chk is not None and hasattr(chk, "propagate"):
+        cores = os.cpu_count() or 1
+        t0 = time.perf_counter()
+        chk.propagate(srcn, g, math.sin(0.7), math.cos(0.7), *sig, threads=cores)
+        t1 = time.perf_counter()
+        blk["cpu_baseline"] = {"kind": chk.kind, "unit": "Mcells/s", "cores": cores, "value": S * S / (t1 - t0) / 1e6,
+                               "sample": "one 400x400 map, OpenMP over cells on %d threads (the reference uses 8, arbitrary_transformation.cu:102)" % cores}
+    return blk
+
+
+def host_ceiling(device, world, h2d, d2h, reps=6):
+    """All ranks at once move only one step's pinned host->device and device->host volumes (two streams, no kernels): what the
+    box's host memory / PCIe paths allow, in steps per second per rank."""
+    import torch
+    a = torch.empty(h2d, dtype=torch.uint8).pin_memory()
+    b = torch.empty(d2h, dtype=torch.uint8).pin_memory()
+    da = torch.empty(h2d, dtype=torch.uint8, device=device)
+    db = torch.empty(d2h, dtype=torch.uint8, device=device)
+    s1, s2 = torch.cuda.Stream(device=device), torch.cuda.Stream(device=device)
+
+    def go(n):
+        for _ in range(n):
+            with torch.cuda.stream(s1):
+                da.copy_(a, non_blocking=True)
+            with torch.cuda.stream(s2):
+                b.copy_(db, non_blocking=True)
+        torch.cuda.synchronize()
+
+    go(2)
+    if world > 1:
+        torch.distributed.barrier()
+    t0 = time.perf_counter()
+    go(reps)
+    return reps / max_over_ranks(time.perf_counter() - t0, world, device)
+
+
+def bench_e2e(args, p, device, world, sc, U_dev, opts, n_obs):
+    """End to end through the C ABI with pinned HOST buffers (copies inside the timed region).  Every step is
+    cilqr_set_obstacles_cv + cilqr_solve_batch on host arrays; the calls block until the results are in host memory.  Like a host
+    application that keeps the GPU busy, --e2e-threads host threads, each with its own solver handle, CUDA stream and buffers,
+    take the steps in turn (compute token on): one step's transfers run under another's kernels.  Every step has its own
+    pre-filled in/out U buffer in pinned memory (the inputs of a step are in pinned host memory when the step starts)."""
+    import threading
+    import torch
+    import cilqr_b200
+    N, B = HORIZON, args.batch
+    keys = ("x0", "U0", "poly", "xlp", "obs_state0", "obs_LW", "obs_sigma")
+    pin = {k: torch.from_numpy(sc[k]).pin_memory() for k in keys}
+    h2d = 8 * (B * (4 + 2 * N + (p.poly_order + 1) + 2) + B * n_obs * 9)
+    d2h = 8 * B * (2 * N + 4 * (N + 1) + 1) + 4 * B * 2
+    d2h_u = 8 * B * (2 * N + 1) + 4 * B * 2
+    merit = cilqr_b200.MERIT_TRACKING
+    n_thr = max(1, args.e2e_threads)
+    ksteps = max(n_thr, min(args.steps, 12))
+    each = max(1, (ksteps + n_thr - 1) // n_thr)
+
+    class Worker:
+        def __init__(self, token, steps, want_x=True, reuse=False):
+            self.reuse = reuse  # one in/out buffer restored by a host memcpy before every call (keeps the recorded graph's key)
+            self.stream = torch.cuda.Stream(device=device)
+            self.hs = cilqr_b200.iLQR(p, max_batch=B, max_obs=n_obs, stream=self.stream, compute_token=True if token else None, options=opts)
+            self.Us = [pin["U0"].clone().pin_memory() for _ in range(steps + 3)]  # one in/out buffer per step, filled before timing
+            self.k = 0
+            self.outs = {"J": torch.empty(B, dtype=torch.float64).pin_memory().numpy(), "iters": torch.empty(B, dtype=torch.int32).pin_memory().numpy(),
+                         "status": torch.empty(B, dtype=torch.int32).pin_memory().numpy()}
+            if want_x:
+                self.outs["X"] = torch.empty((B, 4 * (N + 1)), dtype=torch.float64).pin_memory().numpy()
+
+        def step(self):
+            self.hs.set_obstacles_cv(pin["obs_state0"].numpy(), pin["obs_LW"].numpy(), pin["obs_sigma"].numpy(), sc["kappa"])
+            U = self.Us[0 if self.reuse else self.k % len(self.Us)]
+            if self.reuse:
+                U.copy_(pin["U0"])
+            self.k += 1
+            self.hs.get_optimal_control_seq(pin["x0"].numpy(), U.numpy(), pin["poly"].numpy(), pin["xlp"].numpy(), n_alphas=1, merit=merit,
+                                            outputs=self.outs, want=())
+            return U
+
+    def run(workers, steps_each):
+        """steps_each steps on every worker, all workers at once; wall time from the common start to the last result."""
+        torch.cuda.synchronize()
+        if world > 1:
+            torch.distributed.barrier()
+        gate = threading.Barrier(len(workers) + 1)
+
+        def loop(w):
+            torch.cuda.set_device(device)
+            gate.wait()
+            for _ in range(steps_each):
+                w.last = w.step()
+
+        th = [threading.Thread(target=loop, args=(w,)) for w in workers]
+        for t in th:
+            t.start()
+        gate.wait()
+        t0 = time.perf_counter()
+        for t in th:
+            t.join()
+        torch.cuda.synchronize()
+        return max_over_ranks(time.perf_counter() - t0, world, device)
+
+    out = {"unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "host_threads": n_thr}
+    for name, want_x in (("full", True), ("u_only", False)):
+        workers = [Worker(n_thr > 1, each, want_x) for _ in range(n_thr)]
+        for w in workers:  # warm-up: allocations (the first three buffers)
+            for _ in range(3):
+                w.step()
+        dt = run(workers, each)
+        for w in workers:
+            assert np.array_equal(w.last.numpy(), U_dev), "host-buffer path and device-resident path disagree"
+            w.hs.close()
+        v = world * B * each * n_thr / dt
+        if name == "full":
+            out.update(value=v, steps=each * n_thr)
+        else:
+            out.update(u_only_value=v, u_only_d2h_bytes_per_step=d2h_u)
+        del workers
+    solo = Worker(False, 0, reuse=True)  # one caller: the library's default host path (chunked streams, recorded graph)
+    for _ in range(3):
+        solo.step()
+    dt1 = run([solo], ksteps)
+    solo.hs.close()
+    out["one_thread_value"] = world * B * ksteps / dt1
+    ceil_steps = host_ceiling(device, world, h2d, d2h)
+    out["host_ceiling"] = {"value": world * B * ceil_steps, "unit": UNIT,
+                           "how": "all %d rank(s) at once copy one step's pinned H2D (%d B) and D2H (%d B) volumes on two streams, no kernels" % (world, h2d, d2h)}
+    out["exchange"] = ("none (1 GPU)" if world == 1 else
+                       "each rank's host receives its own shard's U*, X*, J, iterations, status (the contract of cilqr_solve_batch with "
+                       "CILQR_MEM_HOST); the all-gather of U* is a device-side step and is measured in `value`, not here")
+    out["path"] = ("cilqr_set_obstacles_cv + cilqr_solve_batch with CILQR_MEM_HOST pinned buffers, blocking calls; %d host thread(s), one solver "
+                   "handle and stream each, compute token on; u_only_value: X = NULL (U*, J, iterations, status only); one_thread_value: "
+                   "one handle on the default host path" % n_thr)
+    return out
 
 
 def run_b200_arm(args):
     import ctypes as C
     import torch
     import cilqr_b200
-    from cilqr_b200 import scenarios, dist as cdist
+    from cilqr_b200 import dist as cdist
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device - this arm has no CPU path (use --impl reference for the CPU reference)")
@@ -384,206 +683,85 @@ def run_b200_arm(args):
     p = p.replace(horizon=HORIZON)
     N, B, n_obs = HORIZON, args.batch, args.n_obs
     hbm_peak, peak_kind = measured_peaks()
-
-    # ---- inputs: this rank's contiguous shard of scenario ids, generated on the host, resident in HBM before timing
-    sc = scenarios.make_scenarios(p, rank * B, B, n_obs, dense=False)
-    keys = ("x0", "U0", "poly", "xlp", "obs_state0", "obs_LW", "obs_sigma")
-    d = {k: torch.from_numpy(sc[k]).to(device) for k in keys}
-    U = torch.empty_like(d["U0"])
-    gathered = torch.empty((world * B, 2 * N), dtype=torch.float64, device=device) if world > 1 else None
     opts = {cilqr_b200.OPT_FUSED_FROM_ROUND: args.fused_from, cilqr_b200.OPT_FUSED_SLOTS: args.fused_slots,
             cilqr_b200.OPT_GRAPH: 0 if args.no_graph else 1}
-    solver = cilqr_b200.iLQR(p, max_batch=B, max_obs=n_obs, options=opts)
-    merit = cilqr_b200.MERIT_TOTAL if args.n_alphas > 1 else cilqr_b200.MERIT_TRACKING
-    kern_ev = []
-    # results in preallocated device buffers: a call that repeats the previous call's buffers replays the recorded launch graph
-    res = {"X": torch.empty((B, 4 * (N + 1)), dtype=torch.float64, device=device), "J": torch.empty(B, dtype=torch.float64, device=device),
-           "iters": torch.empty(B, dtype=torch.int32, device=device), "status": torch.empty(B, dtype=torch.int32, device=device)}
 
-    # The exchange step runs on its own stream from a snapshot of U*: step i's all-gather travels over NVLink
-    # under step i+1's rounds (the solver's U buffer is in/out and is reset at the start of the next step).  The timed region
-    # ends with a device-wide synchronize, so the last gather is inside it.
-    if world > 1:
-        U_snap = torch.empty_like(U)
-        comm_stream = torch.cuda.Stream(device=device)
-        solved, gathered_ev = torch.cuda.Event(), torch.cuda.Event()
-        gathered_ev.record()
-
-    def step(timed):
-        solver.set_obstacles_cv(d["obs_state0"], d["obs_LW"], d["obs_sigma"], sc["kappa"])  # covariance propagation on device
-        U.copy_(d["U0"])
-        if timed:
-            ev = event_pair()
-            ev[0].record()
-        solver.get_optimal_control_seq(d["x0"], U, d["poly"], d["xlp"], n_alphas=args.n_alphas, merit=merit, outputs=res)
-        if timed:
-            ev[1].record()
-            kern_ev.append(ev)
-        if world > 1:
-            cur = torch.cuda.current_stream()
-            cur.wait_event(gathered_ev)  # the previous gather has read the snapshot
-            U_snap.copy_(U)
-            solved.record(cur)
-            with torch.cuda.stream(comm_stream):
-                comm_stream.wait_event(solved)
-                torch.distributed.all_gather_into_tensor(gathered, U_snap)
-                gathered_ev.record(comm_stream)
-
-    for _ in range(max(args.warmup, 0)):
-        step(False)
-    torch.cuda.synchronize()
-    launches0 = cilqr_b200.launch_count()
-    if world > 1:
-        torch.distributed.barrier()
-    torch.cuda.synchronize()
-    e0, e1 = event_pair()
-    if sampler:
-        sampler.mark_begin()
-    e0.record()
-    for _ in range(args.steps):
-        step(True)
-    e1.record()
-    torch.cuda.synchronize()
-    if sampler:
-        sampler.mark_end()
-    if world > 1:
-        torch.distributed.barrier()
-    total_ms = max_over_ranks(e0.elapsed_time(e1), world, device)
-    if world > 1:
-        assert torch.equal(gathered[rank * B:(rank + 1) * B], U), "all-gather of U*: this rank's slice differs from its own result"
+    # ---- the headline: every rank solves its own B scenarios (ids rank*B ...), weak scaling
+    main = solve_case(args, p, device, rank, world, rank * B, B, n_obs, args.n_alphas, args.steps, args.warmup, opts, True, sampler)
     clocks = sampler.stop() if sampler else None
-    launches = cilqr_b200.launch_count() - launches0
-    kernel_ms = float(np.mean([a.elapsed_time(b) for a, b in kern_ev]))
-    iters = solver.iterations.cpu().numpy()
-    status = solver.status.cpu().numpy()
-    stats = solver.solve_stats() if args.n_alphas == 1 else (int(iters.sum()), int(iters.sum()), int(iters.max()))
-    value = world * B * args.steps / (total_ms * 1e-3)
+    value = world * B * args.steps / (main["total_ms"] * 1e-3)
 
-    # ---- end to end through the C ABI with pinned HOST buffers (copies inside the timed region).  Every step is
-    # cilqr_set_obstacles_cv + cilqr_solve_batch on host arrays; the calls block until the results are in host memory.  Like a
-    # host application that keeps the GPU busy, --e2e-threads host threads (default 3), each with its own solver handle, CUDA
-    # stream and result buffers, take the steps in turn: one step's transfers run under the other's kernels.  The
-    # one-thread number is reported next to it.
+    # ---- BASELINE config 4 as written: 65 536 scenarios in total, sharded over the ranks by contiguous id ranges, gather included
+    strong = None
+    if world > 1 and args.n_alphas == 1 and not args.no_strong:
+        lo, hi = cdist.shard_range(B, rank, world)
+        ksteps = max(10, min(args.steps, 50))
+        st = solve_case(args, p, device, rank, world, lo, hi - lo, n_obs, 1, ksteps, max(3, args.warmup), opts, (hi - lo) * world == B)
+        strong = {"value": B * ksteps / (st["total_ms"] * 1e-3), "unit": UNIT, "ms_per_step": st["ms_per_step"], "solver_ms": st["kernel_ms"],
+                  "scenarios_total": B, "scenarios_per_gpu": hi - lo, "steps": ksteps, "scaling": "strong",
+                  "vs_one_gpu_rate": None, "gpu_launches": st["launches"],
+                  "workload": workload_name(B, n_obs, 1) + ", sharded over %d GPUs by contiguous scenario ranges, all-gather of U* included" % world}
+
     e2e = None
     if not args.no_e2e:
-        import threading
-        pin = {k: torch.from_numpy(sc[k]).pin_memory() for k in keys}
-        h2d = 8 * (B * (4 + 2 * N + (p.poly_order + 1) + 2) + B * n_obs * 9)
-        d2h = 8 * B * (2 * N + 4 * (N + 1) + 1) + 4 * B * 2
-        U_dev = U.cpu().numpy()
-
-        class Worker:
-            def __init__(self, token=False):
-                self.stream = torch.cuda.Stream(device=device)
-                # several handles solving at once: their kernels take turns (cilqr_set_compute_token), their copies overlap
-                self.hs = cilqr_b200.iLQR(p, max_batch=B, max_obs=n_obs, stream=self.stream, compute_token=True if token else None, options=opts)
-                self.Uh = torch.empty((B, 2 * N), dtype=torch.float64).pin_memory()
-                self.outs = {"X": torch.empty((B, 4 * (N + 1)), dtype=torch.float64).pin_memory().numpy(),
-                             "J": torch.empty(B, dtype=torch.float64).pin_memory().numpy(),
-                             "iters": torch.empty(B, dtype=torch.int32).pin_memory().numpy(),
-                             "status": torch.empty(B, dtype=torch.int32).pin_memory().numpy()}
-
-            def step(self):
-                self.hs.set_obstacles_cv(pin["obs_state0"].numpy(), pin["obs_LW"].numpy(), pin["obs_sigma"].numpy(), sc["kappa"])
-                self.Uh.copy_(pin["U0"])
-                self.hs.get_optimal_control_seq(pin["x0"].numpy(), self.Uh.numpy(), pin["poly"].numpy(), pin["xlp"].numpy(),
-                                                n_alphas=args.n_alphas, merit=merit, outputs=self.outs)
-
-        def run(workers, steps_each):
-            """steps_each steps on every worker, all workers at once; wall time from the common start to the last result."""
-            torch.cuda.synchronize()
-            if world > 1:
-                torch.distributed.barrier()
-            gate = threading.Barrier(len(workers) + 1)
-
-            def loop(w):
-                torch.cuda.set_device(device)
-                gate.wait()
-                for _ in range(steps_each):
-                    w.step()
-
-            th = [threading.Thread(target=loop, args=(w,)) for w in workers]
-            for t in th:
-                t.start()
-            gate.wait()
-            t0 = time.perf_counter()
-            for t in th:
-                t.join()
-            torch.cuda.synchronize()
-            return max_over_ranks(time.perf_counter() - t0, world, device)
-
-        n_thr = max(1, args.e2e_threads)
-        solo = Worker()  # one caller: the library's default host path (chunked streams, recorded graph)
-        workers = [Worker(token=True) for _ in range(n_thr)] if n_thr > 1 else [solo]
-        for w in [solo] + (workers if n_thr > 1 else []):  # warm-up: allocations, and the third call of a handle replays the recorded graph
-            for _ in range(max(3, min(args.warmup, 3))):
-                w.step()
-        ksteps = max(1, min(args.steps, 12))
-        dt1 = run([solo], ksteps)
-        each = max(1, (ksteps + n_thr - 1) // n_thr)
-        dtp = run(workers, each) if n_thr > 1 else dt1
-        for w in workers + [solo]:
-            assert np.array_equal(w.Uh.numpy(), U_dev), "host-buffer path and device-resident path disagree"
-        e2e = {"value": world * B * each * n_thr / dtp, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-               "steps": each * n_thr, "host_threads": n_thr, "one_thread_value": world * B * ksteps / dt1,
-               "path": "cilqr_set_obstacles_cv + cilqr_solve_batch with CILQR_MEM_HOST pinned buffers, blocking calls; %d host "
-                       "thread(s), one solver handle and stream each, compute token on (cilqr_set_compute_token); one_thread_value: one "
-                       "handle on the default host path" % n_thr}
-        for w in set(workers + [solo]):
-            w.hs.close()
+        e2e = bench_e2e(args, p, device, world, main["sc"], main["U"], opts, n_obs)
 
     if rank != 0:
-        solver.close()
         if world > 1:
             torch.distributed.destroy_process_group()
         return
 
-    # ---- roofline of the dominant kernel + FP64 rate
-    mean_iters = float(iters.mean())
+    # ---- roofline of the solve: FP64 (what bounds it), HBM beside it
+    stats = main["stats"]
+    kernel_ms = main["kernel_ms"]
     bytes_launch = B * solver_bytes_per_solve(N, n_obs)
     achieved = bytes_launch / (kernel_ms * 1e-3) / 1e9
-    flops_launch, per_cost, per_deriv = solver_flops(N, n_obs, stats[0], stats[1])
-    fp64_peak = C.c_double(0.0)
-    fp64 = None
-    if hasattr(lib, "cilqr_measure_fp64_peak") and lib.cilqr_measure_fp64_peak(C.byref(fp64_peak)) == 0:
-        tf = flops_launch / (kernel_ms * 1e-3) / 1e12
-        fp64 = {"achieved": tf, "peak": fp64_peak.value, "unit": "TFLOP/s", "frac": tf / fp64_peak.value,
-                "peak_source": "DFMA micro-benchmark on this GPU (cilqr_measure_fp64_peak)",
-                "flops_per_cost_pass": per_cost, "flops_per_derivative_pass": per_deriv,
-                "cost_passes_per_solve": stats[0] / B, "derivative_passes_per_solve": stats[1] / B, "rounds": stats[2]}
+    roof = fp64_block(lib, N, n_obs, B, stats, kernel_ms)
+    roof["kernel"] = ("cilqr_solve_batch: one 'launch' = one solve of the batch (fused_solve_kernel for batches up to 16 384 scenarios; batch_init + "
+                      "<= %d rounds of batch_cost / batch_derivs / batch_sweep + batch_output for larger ones; batch_derivs_kernel dominates, "
+                      "see profiles/)" % (p.max_iterations + 1))
+    roof["traffic"] = recorded_traffic("solver_dram_bytes_per_step")
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+        "ms_per_step": main["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
         "data": "synthetic",
-        "config": {"workload": "%s: %d scenarios x %d Gaussian-uncertain obstacles (covariance propagated on device), N=%d, "
-                               "n_alphas=%d, per GPU" % ("config4" if (B, n_obs, args.n_alphas) == (BATCH_PER_GPU, N_OBS, 1) else
-                                                         "config3" if (B, n_obs, args.n_alphas) == (4096, 10, 8) else "custom", B, n_obs, N, args.n_alphas),
-                   "batch_per_gpu": B, "horizon": N, "n_obs": n_obs, "n_alphas": args.n_alphas, "parallelism": "scenario shards x%d" % world,
+        "config": {"workload": workload_name(B, n_obs, args.n_alphas), "scenarios_per_gpu": B, "horizon": N, "n_obs": n_obs, "n_alphas": args.n_alphas,
+                   "parallelism": "scenario shards x%d, every GPU its own %d scenarios" % (world, B),
                    "l2": "%s (%.2f GB of obstacle data re-generated every step + %.2f GB of solver state)"
                          % ("working set larger than L2" if B * (n_obs * 8 * (8 + N) + (18 + 18 * (N + 1)) * 8) > 126e6 else
                             "working set L2-resident: a parity-size configuration, not the headline", B * n_obs * 8 * (8 + N) / 1e9,
                             B * (18 + 18 * (N + 1)) * 8 / 1e9),
-                   "collective": "all_gather U* (NCCL), on its own stream under the next step's rounds" if world > 1 else "none"},
-        "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches),
-        "roofline": {"kernel": ("cilqr_solve_batch = batch_init + <= %d rounds of batch_cost / batch_derivs / batch_sweep + batch_output "
-                                "(one 'launch' = one solve of the batch; batch_derivs_kernel dominates, see profiles/)" % (p.max_iterations + 1))
-                               if args.n_alphas == 1 else "solve_kernel<true>",
-                     "bound": "hbm", "achieved": achieved,
-                     "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": recorded_traffic("solver_dram_bytes_per_step"),
-                     "peak_source": peak_kind, "kernel_ms": kernel_ms, "algorithmic_bytes_per_solve": solver_bytes_per_solve(N, n_obs),
-                     "note": "the solver is FP64-issue/latency bound, not HBM bound: see fp64"},
-        "fp64": fp64,
-        "solver": {"mean_iterations": mean_iters, "status_hist": {"tolerance": int((status == 0).sum()), "max_iter": int((status == 1).sum()),
-                                                                 "lamb_max": int((status == 2).sum()), "nonfinite": int((status == 3).sum())}},
+                   "collective": "all_gather U* (NCCL), on its own stream under the next step's solve" if world > 1 else "none"},
+        "clocks": clocks, "e2e": e2e, "gpu_launches": main["launches"],
+        "roofline": roof,
+        "hbm": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
+                "traffic": recorded_traffic("solver_dram_bytes_per_step"), "peak_source": peak_kind,
+                "algorithmic_bytes_per_solve": solver_bytes_per_solve(N, n_obs), "note": "the solve is FP64-issue / latency bound, not HBM bound"},
+        "solver": {"mean_iterations": main["mean_iterations"], "status_hist": main["status_hist"],
+                   "note": "status as the reference would stop (iLQR.cpp:217-239, lagged accept test): lamb_max = a nominal was rejected and lamb "
+                           "grew past lamb_max; the iterations after the rejection change nothing and cost nothing here"},
+        "strong_scaling": strong,
     }
-    solver.close()
     if world > 1:
         torch.distributed.destroy_process_group()
-    if not args.no_warp:
-        line["costmap_warp"] = bench_warp(args, device, hbm_peak, peak_kind)
-        line["costmap_propagate"] = bench_propagate(args, device, hbm_peak, peak_kind)
+    chk = None
     if world == 1 and not args.no_cpu:
-        line["cpu_baseline"] = cpu_baseline_leg(p, args)
+        chk = cpu_solver()
+    if world == 1 and not args.no_extra and args.n_alphas == 1:
+        # config 3 (line search) and a batch whose scenarios mostly run to the iteration limit instead of stopping on a rejection
+        c3 = solve_case(args, p, device, 0, 1, 0, 4096, 10, 8, 20, 3, opts, False)
+        line["config3"] = {"workload": workload_name(4096, 10, 8), "value": 4096 * 20 / (c3["total_ms"] * 1e-3), "unit": UNIT,
+                           "ms_per_step": c3["ms_per_step"], "mean_iterations": c3["mean_iterations"], "status_hist": c3["status_hist"],
+                           "gpu_launches": c3["launches"], "merit": "total (tracking + obstacle + control barriers)"}
+        c1 = solve_case(args, p, device, 0, 1, 0, B, 3, 1, 10, 3, opts, False)
+        line["few_obstacles"] = {"workload": workload_name(B, 3, 1), "value": B * 10 / (c1["total_ms"] * 1e-3), "unit": UNIT,
+                                 "ms_per_step": c1["ms_per_step"], "mean_iterations": c1["mean_iterations"], "status_hist": c1["status_hist"],
+                                 "roofline": fp64_block(lib, N, 3, B, c1["stats"], c1["kernel_ms"])}
+    if not args.no_warp:
+        line["costmap_warp"] = bench_warp(args, device, hbm_peak, peak_kind, chk)
+        line["costmap_propagate"] = bench_propagate(args, device, lib, chk)
+    if chk is not None:
+        line["cpu_baseline"] = cpu_baseline_leg(p, args, chk)
     print(json.dumps(line), flush=True)
 
 

@@ -261,6 +261,17 @@ class RefOracle(_Base):
                                                 _d(X), _d(J), C.c_int(threads))
         return dict(U=U.reshape(B, -1), X=X, J=J, threads=int(used))
 
+    def solve_alpha_batch(self, p, B, n_obs, dim, pos, x0, U, poly, xlp, n_alphas, threads=0):
+        """solve_alpha for B scenarios, the same loop natively (reference member functions only), OpenMP over scenarios."""
+        dim, pos, x0, poly, xlp = _c64(dim), _c64(pos), _c64(x0), _c64(poly), _c64(xlp)
+        U = np.array(U, dtype=np.float64).copy()
+        N = p.horizon
+        X, J = np.zeros((B, 4 * (N + 1))), np.zeros(B)
+        it, st = np.zeros(B, dtype=np.int32), np.zeros(B, dtype=np.int32)
+        used = self._fn("solve_alpha_batch", C.c_int)(C.byref(p), C.c_int(B), C.c_int(n_obs), _d(dim), _d(pos), _d(x0), _d(U), _d(poly), _d(xlp),
+                                                      C.c_int(n_alphas), _d(X), _d(J), _i(it), _i(st), C.c_int(threads))
+        return dict(U=U.reshape(B, -1), X=X, J=J, iters=it, status=st, threads=int(used))
+
     def linearize(self, p, v, th, acc):
         """Model::get_A_matrix / get_B_matrix -> (A_t [16 N], B_t [8 N]), the reference's transposed-Jacobian tensors."""
         v, th, acc = _c64(v), _c64(th), _c64(acc)

@@ -427,6 +427,71 @@ extern "C"
         return used;
     }
 
+    // The n_alphas > 1 extension for B scenarios, assembled from reference member functions only: per iteration
+    // iLQR::backward_pass, then for alpha = 1, 1/2, ... iLQR::forward_pass with the feed-forward term scaled (k := alpha k) and
+    // Constraints::get_J of the candidate; the largest improving step is taken (lamb /= 10, stop when the improvement is below
+    // the tolerance), none improving raises lamb (stop above lamb_max).  Tracking merit only: the reference API returns no
+    // barrier VALUES.  Same loop as RefOracle.solve_alpha (oracle/__init__.py), OpenMP over scenarios.
+    int ref_solve_alpha_batch(const cilqr_params *c, int B, int n_obs, const double *dim, const double *pos, const double *x0, double *U,
+                              const double *poly, const double *xlp, int n_alphas, double *X, double *J, int *iters, int *status, int threads)
+    {
+        Parameters p = to_ref(*c);
+        const int N = p.horizon;
+        const int npoly = p.poly_order + 1;
+        int used = 1;
+        std::cout.setstate(std::ios_base::failbit);
+#ifdef _OPENMP
+        if (threads > 0)
+            omp_set_num_threads(threads);
+        used = omp_get_max_threads();
+#pragma omp parallel for schedule(dynamic, 1)
+#endif
+        for (int b = 0; b < B; ++b)
+        {
+            iLQR s(p);
+            setup(s, p, n_obs, dim ? dim + (size_t)b * n_obs * 2 * N : nullptr, pos ? pos + (size_t)b * n_obs * 4 * N : nullptr);
+            Eigen::MatrixXd Um = mat(U + (size_t)b * 2 * N, 2, N);
+            Eigen::VectorXd pc = vec(poly + (size_t)b * npoly, npoly);
+            Eigen::VectorXd xl = xlp_vec(xlp + (size_t)b * 2);
+            Eigen::MatrixXd Xm = s.get_nominal_trajectory(vec(x0 + (size_t)b * 4, 4), Um);
+            double lamb = 1.0, J_cur = s.constraints.get_J(Xm, Um, pc, xl);
+            int it = 0, st = 1;
+            for (int i = 0; i < p.max_iterations; ++i)
+            {
+                ++it;
+                if (!s.backward_pass(Xm, Um, pc, xl, lamb)) { st = 3; break; }
+                bool found = false;
+                double Ja = 0.0;
+                for (int a = 0; a < n_alphas; ++a)
+                {
+                    Eigen::MatrixXd ka = s.k * std::ldexp(1.0, -a);
+                    s.forward_pass(Xm, Um, ka, s.K);
+                    Ja = s.constraints.get_J(s.X_new, s.U_new, pc, xl);
+                    if (Ja < J_cur) { found = true; break; }
+                }
+                if (found)
+                {
+                    const double dJ = J_cur - Ja;
+                    Xm = s.X_new; Um = s.U_new; J_cur = Ja;
+                    lamb /= s.lamb_factor;
+                    if (std::abs(dJ) < p.tolerance) { st = 0; break; }
+                }
+                else
+                {
+                    lamb *= s.lamb_factor;
+                    if (lamb > s.lamb_max) { st = 2; break; }
+                }
+            }
+            Eigen::Map<Eigen::MatrixXd>(U + (size_t)b * 2 * N, 2, N) = Um;
+            if (X) Eigen::Map<Eigen::MatrixXd>(X + (size_t)b * 4 * (N + 1), 4, N + 1) = Xm;
+            if (J) J[b] = s.constraints.get_J(Xm, Um, pc, xl);
+            if (iters) iters[b] = it;
+            if (status) status[b] = st;
+        }
+        std::cout.clear();
+        return used;
+    }
+
     // LocalPlanner::get_local_plan / get_local_plan_coeffs (LocalPlanner.cpp:66-96) as run_step uses
     // them (iLQR.cpp:247-255): returns poly (poly_order+1) and xlp = (first, last) x of the local plan.
     int ref_local_plan(const cilqr_params *c, const double *plan, int n_pts, const double *ego, double *poly, double *xlp)

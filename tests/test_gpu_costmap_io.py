@@ -41,6 +41,25 @@ def test_occupancy_conversions_match_reference_loops(checker, n):
     assert np.array_equal(np.isnan(back), np.isnan(data))
 
 
+def test_occupancy_known_answers_transcribed_from_grid_map_ros_tests():
+    """grid_map_ros/test/GridMapRosTest.cpp:116-139 (withMove) and :141-177 (roundTrip) against the CUDA kernels: known answers
+    held by the reference's own tests, no checker involved."""
+    rows, cols = 16, 10
+    m = np.ones((rows, cols), np.float32)
+    assert np.all(cilqr_b200.to_occupancy(m.ravel(order="F"), 0.0, 1.0) == 100)
+    m[rows - 2:, :] = np.nan
+    m[:, cols - 2:] = np.nan
+    flat = m.ravel(order="F")
+    occ = cilqr_b200.to_occupancy(flat, 0.0, 1.0)
+    assert occ[0] == -1 and np.array_equal(occ == -1, np.isnan(flat)[::-1]) and np.all(occ[occ != -1] == 100)
+    rng = np.random.default_rng(1234)
+    grid = (rng.integers(0, 102, 50 * 100) - 1).astype(np.int8)
+    grid[:102] = np.arange(-1, 101, dtype=np.int8)
+    layer = cilqr_b200.from_occupancy(grid)
+    assert np.array_equal(np.isnan(layer), (grid == -1)[::-1])
+    assert np.array_equal(cilqr_b200.to_occupancy(layer, -1.0, 100.0), grid)
+
+
 def test_occupancy_device_buffers_and_full_size_round_trip():
     import torch
     n = 4096 * 4096

@@ -141,6 +141,49 @@ def test_line_search_matches_port(port, merit):
     s.close()
 
 
+@pytest.mark.parametrize("merit", [0, 1])
+def test_config3_at_size_matches_reference_functions(checker, port, merit):
+    """BASELINE config 3 at its own size — 4 096 scenarios x 10 covariance-inflated obstacles, 8 step lengths, where the two-wave
+    line search has non-trivial retry lists and empty wave-2 grids — on a 256-scenario sample (every 16th scenario).
+    Tracking merit: against the alpha loop assembled from reference member functions only (iLQR::backward_pass / forward_pass
+    with k scaled / Constraints::get_J; oracle ref_solve_alpha_batch).  Total merit (needs barrier VALUES, which the reference API
+    does not return): against the plain-C port, whose derivative pieces are pinned on the reference."""
+    import torch
+    p = checker.params_default(horizon=50)
+    B, n_obs, na, step = 4096, 10, 8, 16
+    sc = scenarios.make_scenarios(p, 0, B, n_obs, dense=True)
+    dev = torch.device("cuda:0")
+    t = {k: torch.from_numpy(sc[k]).to(dev) for k in ("x0", "U0", "poly", "xlp", "obs_state0", "obs_LW", "obs_sigma")}
+    s = cilqr_b200.iLQR(p, max_batch=B, max_obs=n_obs)
+    s.set_obstacles_cv(t["obs_state0"], t["obs_LW"], t["obs_sigma"], sc["kappa"])
+    U = t["U0"].clone()
+    s.get_optimal_control_seq(t["x0"], U, t["poly"], t["xlp"], n_alphas=na, merit=merit)
+    torch.cuda.synchronize()
+    Uh, Xh, Jh = U.cpu().numpy(), s.X_result.cpu().numpy(), s.J_result.cpu().numpy()
+    ih, sh = s.iterations.cpu().numpy(), s.status.cpu().numpy()
+    sel = np.arange(0, B, step)
+    sub = {k: np.ascontiguousarray(sc[k][sel]) for k in ("dim", "pos", "x0", "U0", "poly", "xlp")}
+    if merit == 0:
+        if not hasattr(checker, "solve_alpha_batch"):
+            pytest.skip("needs the compiled reference (oracle/_ref)")
+        r = checker.solve_alpha_batch(p, sel.size, n_obs, sub["dim"], sub["pos"], sub["x0"], sub["U0"], sub["poly"], sub["xlp"], na, threads=os.cpu_count() or 1)
+    else:
+        r = port.solve_batch(p, sel.size, n_obs, sub["dim"], sub["pos"], sub["x0"], sub["U0"], sub["poly"], sub["xlp"], n_alphas=na, merit=merit,
+                             threads=os.cpu_count() or 1)
+    flips = [int(b) for i, b in enumerate(sel) if ih[b] != r["iters"][i] or sh[b] != r["status"][i]]
+    assert flips == [], "iteration count / status differ in scenarios %s" % flips
+    worst = 0.0
+    for i, b in enumerate(sel):
+        eu, ex = rel(Uh[b], r["U"][i]), rel(Xh[b], r["X"][i])
+        ej = abs(Jh[b] - r["J"][i]) / abs(r["J"][i])
+        assert eu < TOL and ex < TOL and ej < TOL, (int(b), eu, ex, ej)
+        worst = max(worst, eu, ex, ej)
+    hist = np.bincount(sh, minlength=4)
+    print("config 3 (merit %d): %d of %d scenarios checked, worst relative difference %.3g, status histogram of the batch %s, mean iterations %.2f"
+          % (merit, sel.size, B, worst, hist.tolist(), float(ih.mean())))
+    s.close()
+
+
 def test_covariance_inflated_obstacles_on_device_match_host_expansion(checker):
     """cilqr_set_obstacles_cv (device-side constant-velocity prediction + covariance inflation) against the unmodified
     Obstacle class fed with host-inflated per-timestep dimensions."""

@@ -97,3 +97,34 @@ def test_bounding_box_rasterisation_known_answer(ref):
     x = 0.0 + (0.5 * 40.0 - 0.5 * 0.2) - 0.2 * i
     y = 0.0 + (0.5 * 40.0 - 0.5 * 0.2) - 0.2 * j
     assert x.min() > 10.1 - 2.1 - 1e-9 and x.max() < 10.1 + 2.1 + 1e-9 and y.min() > 0.1 - 1.1 - 1e-9 and y.max() < 0.1 + 1.1 + 1e-9
+
+
+def _move_unwrapped_layer():
+    """OccupancyGridConversion.withMove (grid_map_ros/test/GridMapRosTest.cpp:116-139): an 8.0 x 5.0 m map at 0.5 m (16 x 10
+    cells) filled with 1.0, then moved by (-1, -1) m: the two rows / columns that enter on the low-coordinate side (the highest
+    indices) are unobserved (NaN).  Returned in unwrapped linear (column-major) order, as toOccupancyGrid walks it."""
+    rows, cols = 16, 10
+    m = np.ones((rows, cols), np.float32)
+    before = m.ravel(order="F").copy()
+    m[rows - 2:, :] = np.nan
+    m[:, cols - 2:] = np.nan
+    return before, m.ravel(order="F")
+
+
+def test_occupancy_known_answers_transcribed_from_grid_map_ros_tests(ref):
+    """The reference's own tests of the wire format, as known answers for the checker's restated loops (GridMapRosConverter.cpp
+    itself needs ROS headers): GridMapRosTest.cpp:116-139 withMove (cell 0 is 100 before the move and -1 after it) and :141-177
+    roundTrip (fromOccupancyGrid then toOccupancyGrid(-1, 100) returns every value of [-1, 100] unchanged)."""
+    for chk in (ref,):
+        before, after = _move_unwrapped_layer()
+        occ = chk.to_occupancy(before, 0.0, 1.0)
+        assert occ[0] == 100 and np.all(occ == 100)
+        occ_new = chk.to_occupancy(after, 0.0, 1.0)
+        assert occ_new[0] == -1
+        assert np.array_equal(occ_new == -1, np.isnan(after)[::-1]) and np.all(occ_new[occ_new != -1] == 100)
+        rng = np.random.default_rng(1234)
+        grid = (rng.integers(0, 102, 50 * 100) - 1).astype(np.int8)  # rand() % 102 - 1: [-1, 100]
+        grid[:102] = np.arange(-1, 101, dtype=np.int8)               # every value at least once
+        layer = chk.from_occupancy(grid)
+        assert np.array_equal(np.isnan(layer), (grid == -1)[::-1])
+        assert np.array_equal(chk.to_occupancy(layer, -1.0, 100.0), grid)

@@ -3,8 +3,8 @@
 CPU: the plain-C restatement (incl. its restatement of Eigen 3.2.10's EigenSolver<Matrix2f> for symmetric 2x2 input) is pinned
 bit-for-bit on the compiled reference (real Eigen, real grid_map::EllipseIterator), on the committed golden vectors, and on the
 known-answer test transcribed from grid_map_core/test/EllipseIteratorTest.cpp:28-60.
-GPU: the fused kernel behind costmap_propagate_uncertainty against the checker: identical visit counts (a cell centre within an
-ulp of an ellipse border may flip, so a 1e-4 fraction is tolerated and reported), values within 1e-12 relative."""
+GPU: the fused kernel behind costmap_propagate_uncertainty against the checker: identical visit counts (0 flips in every
+committed case, reported per case), values within 1e-12 relative."""
 import os
 
 import numpy as np
@@ -67,7 +67,11 @@ def check_gpu(checker, g, m, theta, sigma, index):
     c, v = cilqr_b200.propagate_uncertainty(m, g, np.sin(theta), np.cos(theta), *sigma, index=index)
     cr, vr = checker.propagate(m, g, np.sin(theta), np.cos(theta), *sigma, index=index)
     flips = int(np.sum(c != cr))
-    assert flips <= 1e-4 * c.size, "%d of %d visit counts differ" % (flips, c.size)
+    print("propagate: %d of %d visit counts differ from the checker" % (flips, c.size))
+    # The ellipse angle goes through atan2f (CUDA's on the device, glibc's in the checker: up to 2 float ulp apart), so a cell
+    # centre within ~1e-7 of an ellipse border could in principle flip.  Measured on B200 (round 2): 0 of 15 000 / 15 000 / 9 566 /
+    # 6 400 / 160 000 cells in the committed cases — asserted as such.
+    assert flips == 0, "%d of %d visit counts differ" % (flips, c.size)
     same = c == cr
     assert np.array_equal(np.isnan(v[same]), np.isnan(vr[same]))
     ok = same & np.isfinite(vr)
