@@ -69,7 +69,7 @@ def parse_args():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--e2e-threads", type=int, default=4, help="host threads (one solver handle each) in the end-to-end measurement")
-    ap.add_argument("--fused-from", type=int, default=-1, help="CILQR_OPT_FUSED_FROM_ROUND (-1 automatic, 0 fused from the start, 99 round kernels only)")
+    ap.add_argument("--fused", type=int, default=-1, help="CILQR_OPT_FUSED (-1 automatic, 1 fused on-chip kernel, 0 round kernels)")
     ap.add_argument("--fused-slots", type=int, default=0, help="CILQR_OPT_FUSED_SLOTS (0 automatic)")
     ap.add_argument("--no-graph", action="store_true", help="CILQR_OPT_GRAPH = 0: direct launches (for ncu launch lists)")
     return ap.parse_args()
@@ -683,7 +683,7 @@ def run_b200_arm(args):
     p = p.replace(horizon=HORIZON)
     N, B, n_obs = HORIZON, args.batch, args.n_obs
     hbm_peak, peak_kind = measured_peaks()
-    opts = {cilqr_b200.OPT_FUSED_FROM_ROUND: args.fused_from, cilqr_b200.OPT_FUSED_SLOTS: args.fused_slots,
+    opts = {cilqr_b200.OPT_FUSED: args.fused, cilqr_b200.OPT_FUSED_SLOTS: args.fused_slots,
             cilqr_b200.OPT_GRAPH: 0 if args.no_graph else 1}
 
     # ---- the headline: every rank solves its own B scenarios (ids rank*B ...), weak scaling

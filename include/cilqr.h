@@ -119,9 +119,9 @@ int cilqr_create_on(const cilqr_params *p, int max_batch, int max_obs, int devic
 int cilqr_destroy(cilqr_handle h);
 
 /* Scheduling options of a handle (no reference counterpart; results are bit-identical for every setting).
- *   CILQR_OPT_FUSED_FROM_ROUND  r: cilqr_solve_batch (n_alphas = 1) runs solver rounds 0 .. r-1 as batch-synchronous
- *                               round kernels and the rest in the fused on-chip kernel; 0 = fused from the start,
- *                               r > max_iterations = round kernels only, -1 = automatic (default).
+ *   CILQR_OPT_FUSED             where cilqr_solve_batch (n_alphas = 1) runs: 1 = the fused on-chip kernel (scenario groups
+ *                               resident in shared memory from rollout to result), 0 = batch-synchronous round kernels,
+ *                               -1 = automatic (default: fused up to 16 384 scenarios per call).
  *   CILQR_OPT_FUSED_SLOTS       scenario slots per CTA of the fused kernel (0 = automatic).
  *   CILQR_OPT_CHUNKS            number of stream chunks of a host-buffer solve (0 = automatic).
  *   CILQR_OPT_GRAPH             0 = never record repeated solves as a CUDA graph (default 1).
@@ -129,7 +129,7 @@ int cilqr_destroy(cilqr_handle h);
  *   CILQR_OPT_TRACE             1 = the round kernels record their start/end times for cilqr_solve_trace (default 0;
  *                               implies round kernels only). */
 enum {
-    CILQR_OPT_FUSED_FROM_ROUND = 1,
+    CILQR_OPT_FUSED = 1,
     CILQR_OPT_FUSED_SLOTS = 2,
     CILQR_OPT_CHUNKS = 3,
     CILQR_OPT_GRAPH = 4,

@@ -255,7 +255,7 @@ def test_device_resident_and_host_buffers_give_identical_bits():
 def test_fused_kernel_gives_the_bits_of_the_round_kernels(B, n_obs, cv, horizon):
     """cilqr_fused.cuh (scenario groups resident in shared memory from rollout to result) against the batch-synchronous round
     kernels: the same per-step device functions in the same order, so U*, X*, J, iteration counts, status and the pass tallies are
-    identical — fused from the start, taking over after round 1 or 3, with 1 / 5 / automatic slots per CTA."""
+    identical — with 1 / 5 / 14 / automatic slots per CTA."""
     import torch
     p = cilqr_b200.Parameters()
     cilqr_b200.load_library().cilqr_params_default(__import__("ctypes").byref(p))
@@ -265,8 +265,8 @@ def test_fused_kernel_gives_the_bits_of_the_round_kernels(B, n_obs, cv, horizon)
     keys = ("x0", "U0", "poly", "xlp") + (("obs_state0", "obs_LW", "obs_sigma") if cv else ("dim", "pos"))
     t = {k: torch.from_numpy(sc[k]).to(dev) for k in keys if n_obs or not k.startswith(("obs", "dim", "pos"))}
     ref = None
-    for r0, slots in [(99, 0), (0, 0), (0, 1), (0, 5), (1, 0), (3, 3)]:
-        s = cilqr_b200.iLQR(p, max_batch=B, max_obs=max(n_obs, 1), options={cilqr_b200.OPT_FUSED_FROM_ROUND: r0, cilqr_b200.OPT_FUSED_SLOTS: slots})
+    for r0, slots in [(0, 0), (1, 0), (1, 1), (1, 5), (1, 14)]:  # (CILQR_OPT_FUSED, CILQR_OPT_FUSED_SLOTS): round kernels first
+        s = cilqr_b200.iLQR(p, max_batch=B, max_obs=max(n_obs, 1), options={cilqr_b200.OPT_FUSED: r0, cilqr_b200.OPT_FUSED_SLOTS: slots})
         if n_obs:
             if cv:
                 s.set_obstacles_cv(t["obs_state0"], t["obs_LW"], t["obs_sigma"], sc["kappa"])
@@ -330,7 +330,7 @@ def test_chunked_streams_give_the_bits_of_one_stream(chunks):
     sc = scenarios.make_scenarios(p, 11, B, n_obs, curved=True, dense=False)
     out = {}
     for k in (1, chunks):
-        s = cilqr_b200.iLQR(p, max_batch=B, max_obs=n_obs, options={cilqr_b200.OPT_CHUNKS: k, cilqr_b200.OPT_FUSED_FROM_ROUND: 99 if k == chunks else 2})
+        s = cilqr_b200.iLQR(p, max_batch=B, max_obs=n_obs, options={cilqr_b200.OPT_CHUNKS: k, cilqr_b200.OPT_FUSED: 0 if k == chunks else 1})
         s.set_obstacles_cv(sc["obs_state0"], sc["obs_LW"], sc["obs_sigma"], sc["kappa"])
         U = sc["U0"].copy()
         s.get_optimal_control_seq(sc["x0"], U, sc["poly"], sc["xlp"])

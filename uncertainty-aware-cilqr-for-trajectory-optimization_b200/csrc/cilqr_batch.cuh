@@ -102,6 +102,27 @@ __device__ __forceinline__ int2 &hdr_ints(double *h, int which) { return *reinte
 __device__ __forceinline__ double2 ld2(const double *p) { return *reinterpret_cast<const double2 *>(p); }
 __device__ __forceinline__ void st2(double *p, double a, double b) { *reinterpret_cast<double2 *>(p) = make_double2(a, b); }
 
+// iLQR.cpp:217-239 for a scenario whose current nominal costs J (iteration number `iters`, already counted): the
+// one-iteration-lagged accept test.  Rejected: J_new is the cost of the CURRENT nominal (:217), which never changes again, so
+// every later iteration rejects too — only lamb and the iteration counter advance until lamb > lamb_max or the iterations run
+// out; the scenario retires with that status.  Accepted: returns true, `converged` says whether this iteration's improvement
+// was below the tolerance (:225; the backward / forward pass of this iteration still runs).
+__device__ __forceinline__ bool lagged_accept(const DevParams &P, double J, double J_old, double lamb, int &iters, int &status, bool &converged)
+{
+    if (!(J < J_old)) {
+        lamb = lamb * P.lamb_factor;
+        for (;;) {
+            if (lamb > P.lamb_max) { status = CILQR_ST_LAMB_MAX; break; }
+            if (iters >= P.max_iter) { status = CILQR_ST_MAX_ITER; break; }
+            ++iters;
+            lamb = lamb * P.lamb_factor;
+        }
+        return false;
+    }
+    converged = fabs(J - J_old) < P.tol;
+    return true;
+}
+
 // ------------------------------------------------------------------------------------------------- obstacle records
 // Obstacle.cpp:39-48 per (obstacle, t): (x, y, cos, sin, 1/a^2, 1/b^2).
 __device__ __forceinline__ void ellipse_axes(const DevParams &P, double vo, double co, double so, double dim0, double dim1, double &ia2, double &ib2)
@@ -443,27 +464,15 @@ __global__ void __launch_bounds__(kCostThreads) batch_cost_kernel(DevParams P, B
                         h[H_JRES] = J;
                         im.y = MODE_DONE;
                     } else {
-                        int iters = im.x + 1;
-                        double lamb = lamb_sel;
-                        const double J_old = jold_sel;
-                        if (!(J < J_old)) {
-                            // rejected (iLQR.cpp:229-236): J_new is the cost of the CURRENT nominal (:217), which never changes again,
-                            // so every later iteration rejects too — only lamb and the iteration counter advance
-                            int status;
-                            lamb = lamb * P.lamb_factor;
-                            for (;;) {
-                                if (lamb > P.lamb_max) { status = CILQR_ST_LAMB_MAX; break; }
-                                if (iters >= P.max_iter) { status = CILQR_ST_MAX_ITER; break; }
-                                ++iters;
-                                lamb = lamb * P.lamb_factor;
-                            }
-                            hdr_ints(h, H_CONV_STATUS) = make_int2(0, status);
+                        int iters = im.x + 1, status = CILQR_ST_MAX_ITER;
+                        bool converged = false;
+                        accepted = lagged_accept(P, J, jold_sel, lamb_sel, iters, status, converged);
+                        hdr_ints(h, H_CONV_STATUS) = make_int2(converged ? 1 : 0, status);
+                        if (accepted) {
+                            h[H_JNEW] = J;
+                        } else {
                             h[H_JRES] = J;
                             im.y = MODE_DONE;
-                        } else {
-                            hdr_ints(h, H_CONV_STATUS) = make_int2(fabs(J - J_old) < P.tol ? 1 : 0, CILQR_ST_MAX_ITER); // iLQR.cpp:225
-                            h[H_JNEW] = J;
-                            accepted = true;
                         }
                         im.x = iters;
                     }

@@ -263,7 +263,7 @@ struct cilqr_solver {
     DevBuf ctl;                  // per chunk: work-list lengths, the fused kernel's scenario counter and pass tallies
     int last_chunks = 0;         // chunks of the last n_alphas == 1 solve (0: none yet)
     int last_r0 = 0;             // ... and the round from which the fused kernel ran it
-    int fused_from = -1;         // CILQR_OPT_FUSED_FROM_ROUND (-1 = automatic)
+    int fused_from = -1;         // CILQR_OPT_FUSED: 1 = fused kernel, 0 = round kernels, -1 = automatic
     int fused_slots = 0;         // CILQR_OPT_FUSED_SLOTS (0 = automatic)
     int fused_slots_max = 0;     // slots per CTA that fit shared memory with two CTAs per SM (0: the horizon is too long for the fused kernel)
     int force_chunks = 0;        // CILQR_OPT_CHUNKS: override the number of chunks
@@ -578,7 +578,7 @@ int cilqr_set_option(cilqr_handle h, int option, int value)
 {
     if (!h) return fail(CILQR_E_ARG, "null handle");
     switch (option) {
-    case CILQR_OPT_FUSED_FROM_ROUND: h->fused_from = value < 0 ? -1 : value; break;
+    case CILQR_OPT_FUSED: h->fused_from = value < 0 ? -1 : (value != 0); break;
     case CILQR_OPT_FUSED_SLOTS:
         if (value < 0 || value > kFusedMaxSlots) return fail(CILQR_E_ARG, "fused slots %d outside [0, %d]", value, kFusedMaxSlots);
         h->fused_slots = value;
@@ -691,8 +691,8 @@ struct HostIO { // caller's host arrays (CILQR_MEM_HOST) — null members when t
     int32_t *iters = nullptr, *status = nullptr;
 };
 
-// How one n_alphas == 1 solve is laid out: K chunks of Bc scenarios; rounds 0 .. r0 - 1 as batch-synchronous round kernels,
-// the rest (r0 == 0: everything) in the fused kernel with G slots per CTA.
+// How one n_alphas == 1 solve is laid out: K chunks of Bc scenarios; r0 == 0: in the fused kernel with G slots per CTA, else as
+// batch-synchronous round kernels.
 struct SolvePlan {
     int K, Bc, r0, G, fused_grid;
     size_t fused_smem;
@@ -790,8 +790,6 @@ static int issue_rounds(cilqr_handle h, const SolveArgs &A, const HostIO *io, cu
         F.ocv = v.ocv;
         F.oib2 = v.oib2;
         F.orec = v.orec;
-        F.hand_hdr = F.hand_rec = nullptr;
-        F.hand_list = F.hand_cnt = nullptr;
         F.counter = v.cnt + n_cnt;
         F.stats = reinterpret_cast<unsigned long long *>(ctl + ctl_ints(n_cnt) * sizeof(int));
         if (!rounds) { // the whole solve on chip
@@ -803,8 +801,7 @@ static int issue_rounds(cilqr_handle h, const SolveArgs &A, const HostIO *io, cu
             const long long items = (long long)b * N;
             const int deriv_grid = (int)std::min<long long>((items + kDerivThreads - 1) / kDerivThreads, (long long)h->num_sms * h->occ_deriv);
             const int sweep_grid = std::min((b + kSweepThreads - 1) / kSweepThreads, h->num_sms * h->occ_sweep);
-            const bool hand = r0 <= P.max_iter;
-            for (int r = 0; r <= P.max_iter && r < r0; ++r) {
+            for (int r = 0; r <= P.max_iter; ++r) {
                 batch_cost_kernel<<<cost_grid, kCostThreads, cost_smem, cs[c]>>>(P, v, r);
                 CILQR_LAUNCH_CHECK();
                 if (r == P.max_iter) break; // the last round only evaluates J of the scenarios that ran out of iterations
@@ -822,14 +819,6 @@ static int issue_rounds(cilqr_handle h, const SolveArgs &A, const HostIO *io, cu
             batch_output_kernel<<<(int)std::min<size_t>((out_items + 255) / 256, (size_t)h->num_sms * 8), 256, 0, cs[c]>>>(
                 P, v, b, F.U, F.X, F.J, F.iters, F.status);
             CILQR_LAUNCH_CHECK();
-            if (hand) { // the scenarios still iterating after round r0 - 1 move on chip; their results overwrite the ones just written
-                F.hand_hdr = v.hdr;
-                F.hand_rec = v.rec;
-                F.hand_list = (r0 & 1) ? v.list1 : v.list0;
-                F.hand_cnt = v.cnt + r0;
-                // the list is at most as long as the batch; later rounds leave most CTAs without work, which costs nothing
-                if (int rc = launch_fused(h, F, b, plan, cs[c])) return rc;
-            }
         }
         if (token) CILQR_CUDA(cudaEventRecord(h->ev_kdone, cs[c]));
         if (io) { // this chunk's results: staging -> host
@@ -886,14 +875,12 @@ static int solve_rounds(cilqr_handle h, const SolveArgs &A, const HostIO *io, cu
     plan.Bc = ((B + K - 1) / K + 31) / 32 * 32; // chunk size, a multiple of the warp size
     plan.K = K = (B + plan.Bc - 1) / plan.Bc;
     // Where the solve runs.  Automatic: a batch of up to kFusedAutoBatch scenarios (one rank's shard of a sharded solve, a
-    // receding-horizon fleet) goes on chip from the start (cilqr_fused.cuh): it is bound by the ~100 us floor of a round, which
-    // the fused kernel does not have (8 192 scenarios x 20 obstacles: 1.3 ms against 1.8 ms).  A larger batch fills every lane of
-    // the round kernels and runs faster there (65 536: 5.2 ms against 6.6 ms — the fused kernel sweeps at 14 of 32 lanes and its
-    // phases are separated by CTA-wide barriers).  CILQR_OPT_FUSED_FROM_ROUND = r forces the choice: 0 = fused from the start,
-    // r > 0 = rounds 0 .. r - 1 as round kernels and the still-active scenarios handed over, r > max_iterations = round
-    // kernels only.
+    // receding-horizon fleet) goes on chip (cilqr_fused.cuh): it is bound by the latency floor of a round, which the fused kernel
+    // does not have (8 192 scenarios x 20 obstacles: 1.3 ms against 1.8 ms).  A larger batch fills every lane of the round
+    // kernels and runs faster there (65 536: 5.2 ms against 6.6 ms — the fused kernel sweeps at 14 of 32 lanes and its phases are
+    // separated by CTA-wide barriers).  CILQR_OPT_FUSED forces the choice (1 = fused, 0 = round kernels).
     constexpr int kFusedAutoBatch = 16384;
-    plan.r0 = h->fused_from >= 0 ? h->fused_from : (B <= kFusedAutoBatch ? 0 : P.max_iter + 1);
+    plan.r0 = (h->fused_from >= 0 ? h->fused_from != 0 : B <= kFusedAutoBatch) ? 0 : P.max_iter + 1;
     plan.G = 0;
     plan.fused_grid = 1;
     plan.fused_smem = 0;
@@ -1123,7 +1110,7 @@ int cilqr_solve_stats(cilqr_handle h, int64_t *cost_passes, int64_t *deriv_passe
         const int *c = reinterpret_cast<const int *>(raw.data() + stride * k);
         const unsigned long long *f = reinterpret_cast<const unsigned long long *>(raw.data() + stride * k + ctl_ints(n_cnt) * sizeof(int));
         int rk = 0;
-        for (int i = 0; i <= h->dp.max_iter && i < r0; ++i) { // the round kernels' share: work-list lengths
+        for (int i = 0; i <= h->dp.max_iter && r0 > 0; ++i) { // the round kernels' share: work-list lengths
             cp += c[i];
             dp += c[i + 1];
             if (c[i] > 0) rk = i + 1;

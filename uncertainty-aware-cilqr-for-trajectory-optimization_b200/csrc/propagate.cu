@@ -116,21 +116,17 @@ __device__ __forceinline__ bool index_from_position(const PropGeom &G, double x,
     return qx >= 0.0 && qy >= 0.0 && qx < G.Lx && qy < G.Ly && i0 >= 0 && i1 >= 0 && i0 < G.rows && i1 < G.cols;
 }
 
-constexpr int kPropThreads = 64; // small blocks: the per-cell work varies by two orders of magnitude across the map
-__global__ void __launch_bounds__(kPropThreads) propagate_kernel(const PropGeom G, const float *__restrict__ map, double sn, double cn, double sigma_x,
-                                                        double sigma_y, double sigma_theta, int index, int n, int32_t *__restrict__ count,
-                                                        double *__restrict__ value)
+// Everything a cell's ellipse walk needs, produced by the owning lane (rows W2, W3 and the SubmapIterator set-up of W4).
+struct CellWalk {
+    double Cx, Cy, cosR, sinR, sas0, sas1, inv_sas0, inv_sas1, pref, ecoef, two_rho, isxx, isxy, isyy;
+    int s0, s1, n0, n1;
+};
+static_assert(sizeof(CellWalk) % 16 == 0, "staged with 128-bit accesses");
+
+__device__ __forceinline__ CellWalk cell_walk(const PropGeom &G, int l, double sn, double cn, double sigma_x, double sigma_y, double sigma_theta)
 {
-    // The work of a cell grows with the square of its distance from the map origin (the heading sigma's lever arm sets the
-    // ellipse), so in linear cell order both ends of the grid are heavy and the middle is light.  Blocks are dealt from the two
-    // ends inwards — even block ids from the front, odd ones from the back — so the heavy cells start first and the light ones
-    // fill the tail; the cells a block owns and everything computed for them are unchanged.
-    const int half = blockIdx.x >> 1;
-    const int blk = (blockIdx.x & 1) ? (int)gridDim.x - 1 - half : half;
-    const int k = blk * blockDim.x + threadIdx.x;
-    if (k >= n)
-        return;
-    const int l = index + k, ci = l % G.rows, cj = l / G.rows; // GridMapIterator order: linear, column-major
+    CellWalk W;
+    const int ci = l % G.rows, cj = l / G.rows; // GridMapIterator order: linear, column-major
     const double Cx = (G.Px + G.offx) + G.r * (double)(-ci), Cy = (G.Py + G.offy) + G.r * (double)(-cj);
     // W2: uncertainty_error_functor + abc_functor (ARBIT.cuh:58-79)
     const double u = (-sn * Cx - cn * Cy) * (-sn * Cx - cn * Cy);
@@ -152,64 +148,143 @@ __global__ void __launch_bounds__(kPropThreads) propagate_kernel(const PropGeom 
     const double half_major = 2.4477 * (double)sqrtf(Dmaj), half_minor = 2.4477 * (double)sqrtf(Dmin);
     // W4: EllipseIterator(map, centre, Length(2a, 2b), angle)
     const double len0 = 2 * half_major, len1 = 2 * half_minor;
-    const double sas0 = (0.5 * len0) * (0.5 * len0), sas1 = (0.5 * len1) * (0.5 * len1);
-    double sinR, cosR;
-    sincos(angle, &sinR, &cosR);
-    const double u0 = cosR * len0 + (-sinR) * 0.0, u1 = sinR * len0 + cosR * 0.0;
-    const double v0 = cosR * 0.0 + (-sinR) * len1, v1 = sinR * 0.0 + cosR * len1;
+    W.sas0 = (0.5 * len0) * (0.5 * len0);
+    W.sas1 = (0.5 * len1) * (0.5 * len1);
+    sincos(angle, &W.sinR, &W.cosR);
+    const double u0 = W.cosR * len0 + (-W.sinR) * 0.0, u1 = W.sinR * len0 + W.cosR * 0.0;
+    const double v0 = W.cosR * 0.0 + (-W.sinR) * len1, v1 = W.sinR * 0.0 + W.cosR * len1;
     const double bb0 = sqrt(u0 * u0 + v0 * v0), bb1 = sqrt(u1 * u1 + v1 * v1);
     const double tlx = bound_to_range(Cx + bb0, G.Lx, G.Px), tly = bound_to_range(Cy + bb1, G.Ly, G.Py);
     const double brx = bound_to_range(Cx - bb0, G.Lx, G.Px), bry = bound_to_range(Cy - bb1, G.Ly, G.Py);
-    int s0, s1, e0, e1;
-    index_from_position(G, tlx, tly, s0, s1);
+    int e0, e1;
+    index_from_position(G, tlx, tly, W.s0, W.s1);
     index_from_position(G, brx, bry, e0, e1);
-    int n0 = e0 - s0 + 1, n1 = e1 - s1 + 1;
-    if (n0 <= 0 || n1 <= 0) { n0 = 1; n1 = 1; } // a degenerate SubmapIterator still yields its first index
+    W.n0 = e0 - W.s0 + 1;
+    W.n1 = e1 - W.s1 + 1;
+    if (W.n0 <= 0 || W.n1 <= 0) { W.n0 = 1; W.n1 = 1; } // a degenerate SubmapIterator still yields its first index
     const double omr = 1 - rho * rho;
-    const double pref = 1.0 / (sqrt(omr) * (2 * 3.14159265358979323846 * sxi * syi));
-    const double ecoef = -1 / (2 * omr);
-    const double sxx = sxi * sxi, sxy = sxi * syi, syy = syi * syi;
-    double numerator = 0, denominator = 0;
-    int cnt = 0;
-    const double inv_sas0 = 1.0 / sas0, inv_sas1 = 1.0 / sas1;
+    W.pref = 1.0 / (sqrt(omr) * (2 * 3.14159265358979323846 * sxi * syi));
+    W.ecoef = -1 / (2 * omr);
+    // nomal2's three quotients (ARBIT.cuh:103-107) become products with reciprocals taken once per cell: the weight f moves by
+    // ~1e-16 relative, far inside the 1e-12 the values are checked to; which cells are visited is decided separately, exactly.
+    W.isxx = 1.0 / (sxi * sxi);
+    W.isxy = 1.0 / (sxi * syi);
+    W.isyy = 1.0 / (syi * syi);
+    W.two_rho = 2 * rho;
+    W.inv_sas0 = 1.0 / W.sas0;
+    W.inv_sas1 = 1.0 / W.sas1;
+    W.Cx = Cx;
+    W.Cy = Cy;
+    return W;
+}
+
+// One cell (a0, a1) of a bounding box: membership (EllipseIterator::isInside, EllipseIterator.cpp:80-86), weight, map value.
+__device__ __forceinline__ void walk_cell(const PropGeom &G, const CellWalk &W, const float *__restrict__ map, bool centre_exact, int a0, int a1,
+                                          double &numerator, double &denominator, int &cnt)
+{
+    const int i0 = W.s0 + a0, i1 = W.s1 + a1;
+    if (i0 < 0 || i0 >= G.rows || i1 < 0 || i1 >= G.cols)
+        return;
+    const double px = (G.Px + G.offx) + G.r * (double)(-i0), py = (G.Py + G.offy) + G.r * (double)(-i1);
+    const double dx = px - W.Cx, dy = py - W.Cy;
+    const double q0 = W.cosR * dx + W.sinR * dy, q1 = W.sinR * dx + (-W.cosR) * dy; // transformMatrix_ (EllipseIterator.cpp:25)
+    // q0^2/sas0 + q1^2/sas1 <= 1.  The two IEEE divisions are only needed when the sum is within 1e-9 of the threshold;
+    // everywhere else a reciprocal-multiply estimate (off by a few ulp) gives the same decision.
+    const double est = q0 * q0 * W.inv_sas0 + q1 * q1 * W.inv_sas1;
+    bool inside = est <= 1.0;
+    if (!(fabs(est - 1.0) > 1e-9)) // near the border, or NaN
+        inside = q0 * q0 / W.sas0 + q1 * q1 / W.sas1 <= 1;
+    if (!inside)
+        return;
+    const double f = W.pref * exp(W.ecoef * ((dx * dx * W.isxx - W.two_rho * dx * dy * W.isxy) + dy * dy * W.isyy)); // nomal2
+    // atPosition (GridMap.cpp:160-166) of a cell CENTRE: the reference's position -> index chain lands half a cell away from
+    // every border, so for any geometry whose coordinates stay below 2^40 cells its result is (i0, i1) itself (rounding moves it
+    // by < 2^-10 cell); beyond that the chain is evaluated as written.
+    float mv;
+    if (centre_exact) {
+        mv = __ldg(map + i0 + G.rows * i1);
+    } else {
+        int j0, j1;
+        mv = __int_as_float(0x7fc00000);
+        if (index_from_position(G, px, py, j0, j1)) mv = __ldg(map + j0 + G.rows * j1);
+    }
+    numerator += f * mv; // float promoted to double, as in the reference expression
+    denominator += f;
+    cnt++;
+}
+
+// A warp owns 32 consecutive cells.  Every lane prepares its own cell's ellipse (the float eigen-solve chain is per cell), then
+// the walks are shared out by size: a cell whose bounding box has fewer than kPropHeavy cells is walked by its own lane; the
+// others — the work of a cell grows with the square of its distance from the map origin, up to ~500 cells at the experiment's
+// sigmas — are walked by the whole warp, one cell after the other: lanes stride the flattened box, the three sums meet in a
+// fixed shuffle tree (deterministic; the sum's association differs from the reference's sequential one by ~1e-16 relative) and
+// the owner stores.  The one-thread-per-cell version ran 22 of 32 lanes and kept the FP64 pipe 36 % busy (profiles/r01h).
+constexpr int kPropThreads = 128;
+constexpr int kPropHeavy = 48;
+__global__ void __launch_bounds__(kPropThreads) propagate_kernel(const PropGeom G, const float *__restrict__ map, double sn, double cn, double sigma_x,
+                                                        double sigma_y, double sigma_theta, int index, int n, int32_t *__restrict__ count,
+                                                        double *__restrict__ value)
+{
+    __shared__ __align__(16) CellWalk staged[kPropThreads];
+    // The work of a cell grows with the square of its distance from the map origin, so neighbouring cells are equally heavy: a
+    // warp that owned 32 consecutive cells of the far corner would walk ~16 000 box cells while most warps walk a few hundred
+    // (measured: no faster than one thread per cell, the heaviest warp is the whole run time).  Cells are dealt to warps
+    // interleaved instead — lane l of warp w owns cell l * (number of warps) + w — so every warp gets the same mix.
+    const int lane = threadIdx.x & 31;
+    const int warp_global = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, n_warps = (gridDim.x * blockDim.x) >> 5;
+    const int k = lane * n_warps + warp_global;
+    const bool valid = k < n;
     const bool centre_exact = (fabs(G.Px) + G.Lx) < 1.0995e12 * G.r && (fabs(G.Py) + G.Ly) < 1.0995e12 * G.r; // 2^40 cells
-    for (int a0 = 0; a0 < n0; ++a0) { // SubmapIterator order: index 1 fastest (GridMapMath.cpp:459-488)
-        const int i0 = s0 + a0;
-        if (i0 < 0 || i0 >= G.rows) continue;
-        const double px = (G.Px + G.offx) + G.r * (double)(-i0);
-        const double dx = px - Cx;
-        for (int a1 = 0; a1 < n1; ++a1) {
-            const int i1 = s1 + a1;
-            if (i1 < 0 || i1 >= G.cols) continue;
-            const double py = (G.Py + G.offy) + G.r * (double)(-i1);
-            const double dy = py - Cy;
-            const double q0 = cosR * dx + sinR * dy, q1 = sinR * dx + (-cosR) * dy; // transformMatrix_ (EllipseIterator.cpp:25)
-            // isInside (:80-86): q0^2/sas0 + q1^2/sas1 <= 1.  The two IEEE divisions are only needed when the sum is within
-            // 1e-9 of the threshold; everywhere else a reciprocal-multiply estimate (off by a few ulp) gives the same decision.
-            const double est = q0 * q0 * inv_sas0 + q1 * q1 * inv_sas1;
-            bool inside = est <= 1.0;
-            if (!(fabs(est - 1.0) > 1e-9)) // near the border, or NaN
-                inside = q0 * q0 / sas0 + q1 * q1 / sas1 <= 1;
-            if (!inside) continue;
-            const double f = pref * exp(ecoef * ((dx * dx / sxx - 2 * rho * dx * dy / sxy) + dy * dy / syy)); // nomal2
-            // atPosition (GridMap.cpp:160-166) of a cell CENTRE: the reference's position -> index chain lands half a cell
-            // away from every border, so for any geometry whose coordinates stay below 2^40 cells its result is (i0, i1)
-            // itself (rounding moves it by < 2^-10 cell); beyond that the chain is evaluated as written.
-            float mv;
-            if (centre_exact) {
-                mv = __ldg(map + i0 + G.rows * i1);
+    CellWalk W = cell_walk(G, index + (valid ? k : 0), sn, cn, sigma_x, sigma_y, sigma_theta);
+    const long long area = (long long)W.n0 * W.n1;
+    const bool heavy = valid && area >= kPropHeavy;
+    if (valid && !heavy) {
+        double numerator = 0, denominator = 0;
+        int cnt = 0;
+        for (int a0 = 0; a0 < W.n0; ++a0) // SubmapIterator order: index 1 fastest (GridMapMath.cpp:459-488)
+            for (int a1 = 0; a1 < W.n1; ++a1)
+                walk_cell(G, W, map, centre_exact, a0, a1, numerator, denominator, cnt);
+        count[k] = cnt;
+        value[k] = numerator / denominator;
+    }
+    unsigned todo = __ballot_sync(0xffffffffu, heavy);
+    if (!todo)
+        return;
+    staged[threadIdx.x] = W;
+    __syncwarp();
+    const CellWalk *mine = staged + (threadIdx.x & ~31);
+    while (todo) {
+        const int src = __ffs(todo) - 1;
+        todo &= todo - 1;
+        const CellWalk C = mine[src]; // broadcast read
+        const long long cells = (long long)C.n0 * C.n1;
+        const float inv_n1 = 1.0f / (float)C.n1;
+        double numerator = 0, denominator = 0;
+        int cnt = 0;
+        for (long long q = lane; q < cells; q += 32) {
+            int a0, a1;
+            if (cells < (1 << 22)) { // quotient by a float reciprocal, corrected by at most one
+                a0 = __float2int_rz(((float)q + 0.5f) * inv_n1);
+                a1 = (int)q - a0 * C.n1;
+                if (a1 < 0) { --a0; a1 += C.n1; }
+                else if (a1 >= C.n1) { ++a0; a1 -= C.n1; }
             } else {
-                int j0, j1;
-                mv = __int_as_float(0x7fc00000);
-                if (index_from_position(G, px, py, j0, j1)) mv = __ldg(map + j0 + G.rows * j1);
+                a0 = (int)(q / C.n1);
+                a1 = (int)(q - (long long)a0 * C.n1);
             }
-            numerator += f * mv; // float promoted to double, as in the reference expression
-            denominator += f;
-            cnt++;
+            walk_cell(G, C, map, centre_exact, a0, a1, numerator, denominator, cnt);
+        }
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) {
+            numerator += __shfl_xor_sync(0xffffffffu, numerator, d);
+            denominator += __shfl_xor_sync(0xffffffffu, denominator, d);
+            cnt += __shfl_xor_sync(0xffffffffu, cnt, d);
+        }
+        if (lane == src) {
+            count[k] = cnt;
+            value[k] = numerator / denominator;
         }
     }
-    count[k] = cnt;
-    value[k] = numerator / denominator;
 }
 } // namespace cilqr
 

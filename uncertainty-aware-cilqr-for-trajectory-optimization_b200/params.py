@@ -61,4 +61,4 @@ MEM_HOST, MEM_DEVICE = 0, 1
 ST_TOLERANCE, ST_MAX_ITER, ST_LAMB_MAX, ST_NONFINITE = 0, 1, 2, 3
 MERIT_TRACKING, MERIT_TOTAL = 0, 1
 # cilqr_set_option keys (include/cilqr.h)
-OPT_FUSED_FROM_ROUND, OPT_FUSED_SLOTS, OPT_CHUNKS, OPT_GRAPH, OPT_DERIV_STAGED, OPT_TRACE = 1, 2, 3, 4, 5, 6
+OPT_FUSED, OPT_FUSED_SLOTS, OPT_CHUNKS, OPT_GRAPH, OPT_DERIV_STAGED, OPT_TRACE = 1, 2, 3, 4, 5, 6

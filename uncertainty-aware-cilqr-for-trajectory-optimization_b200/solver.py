@@ -156,7 +156,7 @@ class iLQR:
         self.localplanner = None
 
     def set_option(self, option, value):
-        """cilqr_set_option: OPT_FUSED_FROM_ROUND, OPT_FUSED_SLOTS, OPT_CHUNKS, OPT_GRAPH, OPT_DERIV_STAGED, OPT_TRACE."""
+        """cilqr_set_option: OPT_FUSED, OPT_FUSED_SLOTS, OPT_CHUNKS, OPT_GRAPH, OPT_DERIV_STAGED, OPT_TRACE."""
         _check(self.lib.cilqr_set_option(self._h, C.c_int(int(option)), C.c_int(int(value))))
 
     def close(self):
