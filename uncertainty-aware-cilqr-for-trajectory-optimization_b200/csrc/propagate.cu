@@ -118,8 +118,11 @@ __device__ __forceinline__ bool index_from_position(const PropGeom &G, double x,
 
 // Everything a cell's ellipse walk needs, produced by the owning lane (rows W2, W3 and the SubmapIterator set-up of W4).
 struct CellWalk {
-    double Cx, Cy, cosR, sinR, sas0, sas1, inv_sas0, inv_sas1, pref, ecoef, two_rho, isxx, isxy, isyy;
-    int s0, s1, n0, n1;
+    double Cx, Cy, cosR, sinR, sas0, sas1; // centre; EllipseIterator's transform and squared semi-axes (the exact membership test)
+    double qa, qb, qc, inv2c;              // the same test as a quadratic form in (dx, dy): qa dx^2 + qb dx dy + qc dy^2 <= 1
+    double ga, gb, gc, pref;               // nomal2 (ARBIT.cuh:103-107): pref * exp(ga dx^2 + gb dx dy + gc dy^2)
+    int s0, s1, n0, n1;                    // the SubmapIterator's box
+    int est_cells, pad[3];                 // ~ cells inside the ellipse (area / cell area)
 };
 static_assert(sizeof(CellWalk) % 16 == 0, "staged with 128-bit accesses");
 
@@ -162,88 +165,114 @@ __device__ __forceinline__ CellWalk cell_walk(const PropGeom &G, int l, double s
     W.n0 = e0 - W.s0 + 1;
     W.n1 = e1 - W.s1 + 1;
     if (W.n0 <= 0 || W.n1 <= 0) { W.n0 = 1; W.n1 = 1; } // a degenerate SubmapIterator still yields its first index
-    const double omr = 1 - rho * rho;
-    W.pref = 1.0 / (sqrt(omr) * (2 * 3.14159265358979323846 * sxi * syi));
-    W.ecoef = -1 / (2 * omr);
-    // nomal2's three quotients (ARBIT.cuh:103-107) become products with reciprocals taken once per cell: the weight f moves by
-    // ~1e-16 relative, far inside the 1e-12 the values are checked to; which cells are visited is decided separately, exactly.
-    W.isxx = 1.0 / (sxi * sxi);
-    W.isxy = 1.0 / (sxi * syi);
-    W.isyy = 1.0 / (syi * syi);
-    W.two_rho = 2 * rho;
-    W.inv_sas0 = 1.0 / W.sas0;
-    W.inv_sas1 = 1.0 / W.sas1;
+    // Everything below only steers the walk or weights the cells; none of it decides which cells the ellipse admits (the exact
+    // test does), and the weights move by ~1e-16 relative against the reference's quotients — the values are checked to 1e-12.
+    const double i0 = 1.0 / W.sas0, i1 = 1.0 / W.sas1;
+    // q0 = c dx + s dy, q1 = s dx - c dy (EllipseIterator.cpp:25): q0^2 / sas0 + q1^2 / sas1 as a form in (dx, dy)
+    W.qa = W.cosR * W.cosR * i0 + W.sinR * W.sinR * i1;
+    W.qb = 2.0 * W.cosR * W.sinR * (i0 - i1);
+    W.qc = W.sinR * W.sinR * i0 + W.cosR * W.cosR * i1;
+    W.inv2c = 0.5 / W.qc;
+    const double rx = 1.0 / sxi, ry = 1.0 / syi, omr = 1 - rho * rho, rs = rsqrt(omr);
+    const double ecoef = -0.5 * rs * rs; // -1 / (2 (1 - rho^2))
+    W.pref = rs * rx * ry * (1.0 / (2 * 3.14159265358979323846));
+    W.ga = ecoef * rx * rx;
+    W.gb = ecoef * (-2.0 * rho) * rx * ry;
+    W.gc = ecoef * ry * ry;
+    const double cells = 3.14159265358979323846 * half_major * half_minor / (G.r * G.r);
+    W.est_cells = cells < 1e9 ? (int)cells : 1000000000;
+    W.pad[0] = W.pad[1] = W.pad[2] = 0;
     W.Cx = Cx;
     W.Cy = Cy;
     return W;
 }
 
-// One cell (a0, a1) of a bounding box: membership (EllipseIterator::isInside, EllipseIterator.cpp:80-86), weight, map value.
-__device__ __forceinline__ void walk_cell(const PropGeom &G, const CellWalk &W, const float *__restrict__ map, bool centre_exact, int a0, int a1,
-                                          double &numerator, double &denominator, int &cnt)
+// One row (fixed index 0) of a cell's box: the cells the ellipse admits, in SubmapIterator order (index 1 ascending).
+// For a fixed dx membership is a quadratic inequality in dy, so the candidates are one interval of index 1; it is taken with
+// margins (1e-8 in the discriminant, 1e-6 cell at either end — the form's own rounding error is ~1e-15) and every candidate is
+// then decided like EllipseIterator::isInside decides it (EllipseIterator.cpp:80-86): by the form when it is further than 1e-9
+// from the threshold, by the reference's own expression with its two IEEE divisions otherwise.  The ellipses of this map are
+// thin and rotated: their axis-aligned boxes are ~8x larger than they are (first version: 44 M box cells tested for 5 M
+// admitted, 7 of 32 lanes active in the weighting code).
+__device__ __forceinline__ void walk_row(const PropGeom &G, const CellWalk &W, const float *__restrict__ map, bool centre_exact, int a0,
+                                         double &numerator, double &denominator, int &cnt)
 {
-    const int i0 = W.s0 + a0, i1 = W.s1 + a1;
-    if (i0 < 0 || i0 >= G.rows || i1 < 0 || i1 >= G.cols)
+    const int i0 = W.s0 + a0;
+    if (i0 < 0 || i0 >= G.rows)
         return;
-    const double px = (G.Px + G.offx) + G.r * (double)(-i0), py = (G.Py + G.offy) + G.r * (double)(-i1);
-    const double dx = px - W.Cx, dy = py - W.Cy;
-    const double q0 = W.cosR * dx + W.sinR * dy, q1 = W.sinR * dx + (-W.cosR) * dy; // transformMatrix_ (EllipseIterator.cpp:25)
-    // q0^2/sas0 + q1^2/sas1 <= 1.  The two IEEE divisions are only needed when the sum is within 1e-9 of the threshold;
-    // everywhere else a reciprocal-multiply estimate (off by a few ulp) gives the same decision.
-    const double est = q0 * q0 * W.inv_sas0 + q1 * q1 * W.inv_sas1;
-    bool inside = est <= 1.0;
-    if (!(fabs(est - 1.0) > 1e-9)) // near the border, or NaN
-        inside = q0 * q0 / W.sas0 + q1 * q1 / W.sas1 <= 1;
-    if (!inside)
-        return;
-    const double f = W.pref * exp(W.ecoef * ((dx * dx * W.isxx - W.two_rho * dx * dy * W.isxy) + dy * dy * W.isyy)); // nomal2
-    // atPosition (GridMap.cpp:160-166) of a cell CENTRE: the reference's position -> index chain lands half a cell away from
-    // every border, so for any geometry whose coordinates stay below 2^40 cells its result is (i0, i1) itself (rounding moves it
-    // by < 2^-10 cell); beyond that the chain is evaluated as written.
-    float mv;
-    if (centre_exact) {
-        mv = __ldg(map + i0 + G.rows * i1);
-    } else {
-        int j0, j1;
-        mv = __int_as_float(0x7fc00000);
-        if (index_from_position(G, px, py, j0, j1)) mv = __ldg(map + j0 + G.rows * j1);
+    const double px = (G.Px + G.offx) + G.r * (double)(-i0);
+    const double dx = px - W.Cx, dx2 = dx * dx;
+    int j_lo = max(W.s1, 0), j_hi = min(W.s1 + W.n1 - 1, G.cols - 1);
+    const double bdx = W.qb * dx;
+    const double D = fma(bdx, bdx, -4.0 * W.qc * fma(W.qa, dx2, -1.0)) + 4e-8 * W.qc;
+    bool by_form = false;
+    if (fabs(D) <= 1.7976931348623157e308 && fabs(W.inv2c) <= 1.7976931348623157e308) { // else: a degenerate ellipse, every box cell is a candidate
+        if (D < 0.0)
+            return;
+        by_form = true;
+        const double sq = sqrt(D), rinv = 1.0 / G.r, by = (G.Py + G.offy) - W.Cy;
+        const double dy_a = (-bdx - sq) * W.inv2c, dy_b = (-bdx + sq) * W.inv2c; // dy = py - Cy, py = (Py + offy) - r i1
+        const double t_lo = (by - fmax(dy_a, dy_b)) * rinv - 1e-6, t_hi = (by - fmin(dy_a, dy_b)) * rinv + 1e-6;
+        if (t_lo > (double)j_lo) j_lo = t_lo < 2.0e9 ? (int)ceil(t_lo) : j_hi + 1;
+        if (t_hi < (double)j_hi) j_hi = t_hi > -2.0e9 ? (int)floor(t_hi) : j_lo - 1;
     }
-    numerator += f * mv; // float promoted to double, as in the reference expression
-    denominator += f;
-    cnt++;
+    for (int i1 = j_lo; i1 <= j_hi; ++i1) {
+        const double py = (G.Py + G.offy) + G.r * (double)(-i1);
+        const double dy = py - W.Cy, dxy = dx * dy, dy2 = dy * dy;
+        const double est = fma(W.qa, dx2, fma(W.qb, dxy, W.qc * dy2));
+        bool inside = est <= 1.0;
+        if (!by_form || !(fabs(est - 1.0) > 1e-9)) { // near the border (or NaN): the reference's expression decides
+            const double q0 = W.cosR * dx + W.sinR * dy, q1 = W.sinR * dx + (-W.cosR) * dy; // transformMatrix_ (EllipseIterator.cpp:25)
+            inside = q0 * q0 / W.sas0 + q1 * q1 / W.sas1 <= 1;
+        }
+        if (!inside)
+            continue;
+        const double f = W.pref * exp(fma(W.ga, dx2, fma(W.gb, dxy, W.gc * dy2))); // nomal2
+        // atPosition (GridMap.cpp:160-166) of a cell CENTRE: the reference's position -> index chain lands half a cell away from
+        // every border, so for any geometry whose coordinates stay below 2^40 cells its result is (i0, i1) itself (rounding moves
+        // it by < 2^-10 cell); beyond that the chain is evaluated as written.
+        float mv;
+        if (centre_exact) {
+            mv = __ldg(map + i0 + G.rows * i1);
+        } else {
+            int j0, j1;
+            mv = __int_as_float(0x7fc00000);
+            if (index_from_position(G, px, py, j0, j1)) mv = __ldg(map + j0 + G.rows * j1);
+        }
+        numerator += f * mv; // float promoted to double, as in the reference expression
+        denominator += f;
+        cnt++;
+    }
 }
 
-// A warp owns 32 consecutive cells.  Every lane prepares its own cell's ellipse (the float eigen-solve chain is per cell), then
-// the walks are shared out by size: a cell whose bounding box has fewer than kPropHeavy cells is walked by its own lane; the
-// others — the work of a cell grows with the square of its distance from the map origin, up to ~500 cells at the experiment's
-// sigmas — are walked by the whole warp, one cell after the other: lanes stride the flattened box, the three sums meet in a
-// fixed shuffle tree (deterministic; the sum's association differs from the reference's sequential one by ~1e-16 relative) and
-// the owner stores.  The one-thread-per-cell version ran 22 of 32 lanes and kept the FP64 pipe 36 % busy (profiles/r01h).
-constexpr int kPropThreads = 128;
-constexpr int kPropHeavy = 48;
+// A warp owns 32 consecutive cells — neighbours have nearly the same ellipse, so the lanes of a warp carry nearly the same
+// work.  A cell of up to kPropHeavy admitted cells is walked by its own lane, row after row, i.e. summed in exactly the
+// reference's order.  The few larger ones (the far corners of the map: up to ~500 cells at the experiment's sigmas) would be the
+// run time of the whole launch as single threads; they are walked by the whole warp afterwards, one lane per row, and the three
+// sums meet in a fixed shuffle tree (deterministic; the association differs from the sequential one by ~1e-16 relative).
+constexpr int kPropThreads = 64;
+constexpr int kPropHeavy = 160;
 __global__ void __launch_bounds__(kPropThreads) propagate_kernel(const PropGeom G, const float *__restrict__ map, double sn, double cn, double sigma_x,
                                                         double sigma_y, double sigma_theta, int index, int n, int32_t *__restrict__ count,
                                                         double *__restrict__ value)
 {
     __shared__ __align__(16) CellWalk staged[kPropThreads];
-    // The work of a cell grows with the square of its distance from the map origin, so neighbouring cells are equally heavy: a
-    // warp that owned 32 consecutive cells of the far corner would walk ~16 000 box cells while most warps walk a few hundred
-    // (measured: no faster than one thread per cell, the heaviest warp is the whole run time).  Cells are dealt to warps
-    // interleaved instead — lane l of warp w owns cell l * (number of warps) + w — so every warp gets the same mix.
-    const int lane = threadIdx.x & 31;
-    const int warp_global = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, n_warps = (gridDim.x * blockDim.x) >> 5;
-    const int k = lane * n_warps + warp_global;
+    // The work of a cell grows with the square of its distance from the map origin (the heading sigma's lever arm sets the
+    // ellipse), so in linear cell order both ends of the grid are heavy and the middle is light.  Blocks are dealt from the two
+    // ends inwards — even block ids from the front, odd ones from the back — so the heavy cells start first and the light ones
+    // fill the tail.
+    const int half = blockIdx.x >> 1;
+    const int blk = (blockIdx.x & 1) ? (int)gridDim.x - 1 - half : half;
+    const int k = blk * blockDim.x + threadIdx.x, lane = threadIdx.x & 31;
     const bool valid = k < n;
     const bool centre_exact = (fabs(G.Px) + G.Lx) < 1.0995e12 * G.r && (fabs(G.Py) + G.Ly) < 1.0995e12 * G.r; // 2^40 cells
     CellWalk W = cell_walk(G, index + (valid ? k : 0), sn, cn, sigma_x, sigma_y, sigma_theta);
-    const long long area = (long long)W.n0 * W.n1;
-    const bool heavy = valid && area >= kPropHeavy;
+    const bool heavy = valid && W.est_cells > kPropHeavy && W.n0 >= 8;
     if (valid && !heavy) {
         double numerator = 0, denominator = 0;
         int cnt = 0;
-        for (int a0 = 0; a0 < W.n0; ++a0) // SubmapIterator order: index 1 fastest (GridMapMath.cpp:459-488)
-            for (int a1 = 0; a1 < W.n1; ++a1)
-                walk_cell(G, W, map, centre_exact, a0, a1, numerator, denominator, cnt);
+        for (int a0 = 0; a0 < W.n0; ++a0) // SubmapIterator order: index 0 outer, index 1 fastest (GridMapMath.cpp:459-488)
+            walk_row(G, W, map, centre_exact, a0, numerator, denominator, cnt);
         count[k] = cnt;
         value[k] = numerator / denominator;
     }
@@ -257,23 +286,10 @@ __global__ void __launch_bounds__(kPropThreads) propagate_kernel(const PropGeom 
         const int src = __ffs(todo) - 1;
         todo &= todo - 1;
         const CellWalk C = mine[src]; // broadcast read
-        const long long cells = (long long)C.n0 * C.n1;
-        const float inv_n1 = 1.0f / (float)C.n1;
         double numerator = 0, denominator = 0;
         int cnt = 0;
-        for (long long q = lane; q < cells; q += 32) {
-            int a0, a1;
-            if (cells < (1 << 22)) { // quotient by a float reciprocal, corrected by at most one
-                a0 = __float2int_rz(((float)q + 0.5f) * inv_n1);
-                a1 = (int)q - a0 * C.n1;
-                if (a1 < 0) { --a0; a1 += C.n1; }
-                else if (a1 >= C.n1) { ++a0; a1 -= C.n1; }
-            } else {
-                a0 = (int)(q / C.n1);
-                a1 = (int)(q - (long long)a0 * C.n1);
-            }
-            walk_cell(G, C, map, centre_exact, a0, a1, numerator, denominator, cnt);
-        }
+        for (int a0 = lane; a0 < C.n0; a0 += 32)
+            walk_row(G, C, map, centre_exact, a0, numerator, denominator, cnt);
 #pragma unroll
         for (int d = 16; d > 0; d >>= 1) {
             numerator += __shfl_xor_sync(0xffffffffu, numerator, d);
