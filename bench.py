@@ -437,7 +437,10 @@ def bench_warp(args, device, hbm_peak, peak_kind, chk):
         idx = torch.empty((chunk, T * T), dtype=torch.int32, device=device)
         res = {}
         for name, with_idx in (("value_only", False), ("value_and_index", True)):
+            reps = max(1, 2048 // T)  # small grids: several sweeps back to back, so that one launch's latency is not the measurement
+
             def sweep_once():
+              for _ in range(reps):
                 for c in range(0, WARP_POSES, chunk):
                     cilqr_b200.warp_batch(src, sg, tg, poses[c:c + chunk], out=out[:min(chunk, WARP_POSES - c)],
                                           idx=idx[:min(chunk, WARP_POSES - c)] if with_idx else None, want_idx=False)
@@ -448,13 +451,13 @@ def bench_warp(args, device, hbm_peak, peak_kind, chk):
             sweep_once()
             e1.record()
             torch.cuda.synchronize()
-            ms = e0.elapsed_time(e1)
+            ms = e0.elapsed_time(e1) / reps
             by = WARP_POSES * T * T * (12 if with_idx else 8)
             res[name] = {"gbs": by / ms / 1e6, "ms_per_pose": ms / WARP_POSES}
         best = res["value_and_index"]
         sweep.append({"T": T, "source": "%dx%d (%.0f MB)" % (S, S, S * S * 4 / 1e6), "poses": WARP_POSES, "chunk": chunk, "gbs": best["gbs"],
                       "frac": best["gbs"] / hbm_peak, "value_only_gbs": res["value_only"]["gbs"], "ms_per_pose": best["ms_per_pose"],
-                      "traffic": recorded_traffic("warp_dram_bytes_per_launch_T%d" % T), "launches_counted": 4 * ((WARP_POSES + chunk - 1) // chunk),
+                      "traffic": recorded_traffic("warp_dram_bytes_per_launch_T%d" % T), "launches_counted": 4 * reps * ((WARP_POSES + chunk - 1) // chunk),
                       "source_in_l2": S * S * 4 < 100e6})
         del src, out, idx
         torch.cuda.empty_cache()
@@ -467,6 +470,34 @@ def bench_warp(args, device, hbm_peak, peak_kind, chk):
                         "traffic": head["traffic"], "peak_source": peak_kind,
                         "algorithmic_bytes_per_cell": "4 B source read + 4 B value write + 4 B index write"},
            "sweep": sweep, "launches": sum(e["launches_counted"] for e in sweep)}
+    # the same frame on the wire format (int8 occupancy data in and out, N2 fused into the warp): 1 B + 1 B (+ 4 B index) per cell
+    occ_blk = []
+    for T in ([args.warp_T] if args.warp_T else [1024, 4096]):
+        S = 2 * T
+        sg, tg = G(S * 0.2, S * 0.2, 0.2, 0.0, 0.0), G(T * 0.2, T * 0.2, 0.2, 0.0, 0.0)
+        occ = torch.randint(-1, 101, (S * S,), device=device, dtype=torch.int32).to(torch.int8)
+        chunk = max(1, min(WARP_POSES, WARP_CHUNK_BYTES // (T * T * 8)))
+        poses = torch.from_numpy(scenarios.make_poses(WARP_POSES, (0.0, 0.0), 0.05 * T * 0.2)).to(device)
+        out8 = torch.empty((chunk, T * T), dtype=torch.int8, device=device)
+
+        def sweep8():
+            for c in range(0, WARP_POSES, chunk):
+                cilqr_b200.warp_occupancy_batch(occ, sg, tg, poses[c:c + chunk], out=out8[:min(chunk, WARP_POSES - c)])
+        sweep8()
+        torch.cuda.synchronize()
+        e0, e1 = event_pair()
+        e0.record()
+        sweep8()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1)
+        occ_blk.append({"T": T, "ms_per_pose": ms / WARP_POSES, "gbs": WARP_POSES * T * T * 2 / ms / 1e6, "frac": WARP_POSES * T * T * 2 / ms / 1e6 / hbm_peak,
+                        "cells_per_s": WARP_POSES * T * T / (ms * 1e-3), "bytes_per_cell": "1 B int8 read + 1 B int8 written"})
+        del occ, out8
+        torch.cuda.empty_cache()
+    blk["occupancy_in_out"] = {"what": "costmap_warp_occupancy_batch: fromOccupancyGrid + warp + toOccupancyGrid in one gather", "sweep": occ_blk,
+                               "float_path_ms_per_pose": {e["T"]: e["ms_per_pose"] for e in sweep},
+                               "bound": "gather instruction rate (8 byte loads per thread), not HBM: 2 B per cell are algorithmic"}
     if chk is not None and hasattr(chk, "warp"):  # CPU baseline (iii) of SURVEY.md section 8(d): the reference loop, 1 thread and OpenMP over poses
         T = 1024
         S = 2 * T

@@ -184,6 +184,16 @@ int cilqr_solve_batch(cilqr_handle h, int B, const double *x0, double *U, const 
                       const double *xlp, int n_alphas, int merit, double *X, double *J,
                       int32_t *iters, int32_t *status, int mem, void *stream);
 
+/*
+ * The one exchange step of a sharded solve (the reference has no counterpart): NCCL all-gather of this
+ * rank's `count` doubles (its shard of U*, X* or J, device memory) into `gathered` (count x ranks doubles, device memory, the
+ * same on every rank, shards in rank order), enqueued on `stream` — give it the solve's stream and it follows the last kernel.
+ * `nccl_comm` is the caller's ncclComm_t (one per rank / device; inside ncclGroupStart / ncclGroupEnd when one thread drives
+ * several devices).  NCCL is bound at run time: the library shares the NCCL already loaded into the process, else loads
+ * libnccl.so.2; CILQR_E_STATE when there is none.
+ */
+int cilqr_gather(cilqr_handle h, void *nccl_comm, const double *local, int64_t count, double *gathered, void *stream);
+
 /* Work done by the last cilqr_solve_batch call with n_alphas == 1 (measurement helper, no reference counterpart): how many
  * times the cost (Constraints::get_J) and the derivative pass + backward/forward pass ran, summed over the scenarios, and
  * the number of solver rounds that had work (round kernels) plus the largest number of iterations any CTA of the fused kernel made.  The reference's own iteration counter (`iters`) also counts the iterations in
@@ -311,6 +321,18 @@ int costmap_propagate_uncertainty(const float *map, const costmap_geom *geom, do
 int costmap_from_occupancy(const int8_t *occ, int64_t n, float *data, int mem, void *stream);
 int costmap_to_occupancy(const float *data, int64_t n, float data_min, float data_max, int8_t *occ,
                          int mem, void *stream);
+
+/*
+ * The warp of a frame on the wire format (row N2 fused into row W1): fromOccupancyGrid (local_costmap.cpp:169) -> warp loop
+ * (:242-264) -> toOccupancyGrid(data_min, data_max) (:298) as ONE gather over int8 data — 1 B read + 1 B written per cell.
+ *   occ_src [rows_s*cols_s] int8  nav_msgs/OccupancyGrid data of the global map (-1 = unknown), in the message's order
+ *   occ_out [P][rows_t*cols_t] int8  the ego-frame maps as OccupancyGrid data (unknown / out-of-map cells: -1)
+ *   bbox, idx, poses as in costmap_warp_batch (bbox is a float layer in grid_map order; idx in grid_map order)
+ * Identical, byte for byte, to costmap_to_occupancy(costmap_warp_batch(costmap_from_occupancy(occ_src))).
+ */
+int costmap_warp_occupancy_batch(const int8_t *occ_src, const costmap_geom *src_geom, const costmap_geom *tgt_geom,
+                                 const double *poses, int P, const float *bbox, float data_min, float data_max,
+                                 int8_t *occ_out, int32_t *idx, int mem, void *stream);
 
 /*
  * LocalCostmap::bondingBoxHandle (CILQR/src/map_engine/src/local_costmap.cpp:860-922), the producer of the warp's

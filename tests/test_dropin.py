@@ -13,6 +13,7 @@ BUILD = os.path.join(ROOT, "build")
 DEMO = os.path.join(BUILD, "dropin_demo")
 STAGES = os.path.join(BUILD, "dropin_stages")
 MAPDEMO = os.path.join(BUILD, "map_dropin_demo")
+GATHER = os.path.join(BUILD, "gather_demo")
 EIGEN = "/root/reference/CILQR/src/map_engine/include/map_engine"
 GMC = "/root/reference/CILQR/src/grid_map/grid_map_core"
 PKG = "uncertainty-aware-cilqr-for-trajectory-optimization_b200"
@@ -30,6 +31,11 @@ def build_demo():
     link = ["-L" + os.path.join(ROOT, PKG), "-l:libcilqr_b200.so", "-Wl,-rpath,$ORIGIN/../" + PKG]
     for src, out in (("dropin_demo.cpp", DEMO), ("dropin_stages.cpp", STAGES)):
         subprocess.run(common + [os.path.join(ROOT, "tests", "cpp", src), "-o", out] + link, check=True)
+    nvcc = "/usr/local/cuda/bin/nvcc"
+    if os.path.exists(nvcc) and os.path.exists("/usr/include/nccl.h"):  # one host thread, one handle per GPU, cilqr_gather on the application's NCCL communicators
+        subprocess.run([nvcc, "-ccbin", cxx, "-O2", "-std=c++17", "-Wno-deprecated-gpu-targets", "-I" + os.path.join(ROOT, "include"),
+                        os.path.join(ROOT, "tests", "cpp", "gather_demo.cpp"), "-o", GATHER, "-L" + os.path.join(ROOT, PKG), "-l:libcilqr_b200.so", "-lnccl",
+                        "-Xlinker", "-rpath", "-Xlinker", "$ORIGIN/../" + PKG], check=True)
     oracle.build(("ref",))
     objs = sorted(glob.glob(os.path.join(ROOT, "oracle", "_ref", "obj", "gmc*_*.o")))
     subprocess.run(common + ["-I" + os.path.join(GMC, "include"), "-I" + os.path.join(ROOT, "oracle", "_ref", "inc"),
@@ -178,3 +184,17 @@ def test_map_dropin_matches_reference(checker, index):
     same = d["count"].astype(np.int64) == cr
     ok = same & np.isfinite(vr)
     assert np.max(np.abs(d["value"][ok] - vr[ok]) / np.maximum(np.abs(vr[ok]), 1e-300)) < 1e-12
+
+
+@pytest.mark.gpu
+def test_one_thread_drives_a_handle_per_gpu_and_gathers_over_nccl():
+    """cilqr_create_on + cilqr_gather from a C++ host (tests/cpp/gather_demo.cpp): shards solved on every device of the box, the
+    all-gathered U* identical on every device and bit-identical to the one-device solve.  Needs at least two GPUs."""
+    import torch
+    if not os.path.exists(GATHER):
+        pytest.skip("build/gather_demo was not built")
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs at least two GPUs (run under gpurun --gpus 2)")
+    r = subprocess.run([GATHER], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "0 mismatching devices" in r.stdout

@@ -60,6 +60,42 @@ def test_occupancy_known_answers_transcribed_from_grid_map_ros_tests():
     assert np.array_equal(cilqr_b200.to_occupancy(layer, -1.0, 100.0), grid)
 
 
+@pytest.mark.parametrize("rows_t,cols_t,with_bbox", [(400, 400, True), (64, 40, False), (150, 100, True), (37, 21, False)])
+def test_warp_on_the_wire_format_equals_the_three_step_frame(checker, rows_t, cols_t, with_bbox):
+    """costmap_warp_occupancy_batch (N2 fused into W1: int8 in, int8 out) against the reference's frame assembled from its
+    pieces — fromOccupancyGrid, the warp loop on grid_map::GridMap objects, toOccupancyGrid — byte for byte, index map int for
+    int; sizes with and without 8-cell alignment, poses that leave the global map (unknown cells: -1)."""
+    need_ref(checker)
+    import torch
+    sg = G(60.0, 48.0, 0.2, 10.0, -5.0)
+    tg = G(rows_t * 0.2, cols_t * 0.2, 0.2, 2.0, 0.0)
+    rs, cs = checker.geom_size(sg)
+    rng = np.random.default_rng(rows_t * 1000 + cols_t)
+    occ = rng.integers(-1, 101, rs * cs).astype(np.int8)
+    poses = np.array([[12.0, -4.0, np.sin(0.7), np.cos(0.7)], [30.0, 10.0, np.sin(2.9), np.cos(2.9)], [10.0, -5.0, 0.0, 1.0],
+                      [-15.0, -25.0, np.sin(5.5), np.cos(5.5)]])
+    bbox = None
+    if with_bbox:
+        bbox = np.zeros((len(poses), rows_t * cols_t), np.float32)
+        bbox[:, rng.integers(0, rows_t * cols_t, 50)] = 100.0
+    layer = checker.from_occupancy(occ)
+    val, idx_ref = checker.warp(layer, sg, tg, poses, bbox=bbox)
+    want = np.stack([checker.to_occupancy(v, 0.0, 100.0) for v in val])
+    got, idx = cilqr_b200.warp_occupancy_batch(occ, sg, tg, poses, bbox=bbox, want_idx=True)
+    assert np.array_equal(idx, idx_ref)
+    assert np.array_equal(got, want)
+    assert (got == -1).any() and (got >= 0).any()
+    # device buffers, other scaling
+    want2 = np.stack([checker.to_occupancy(v, -5.0, 37.5) for v in val])
+    got2, _ = cilqr_b200.warp_occupancy_batch(torch.from_numpy(occ).cuda(), sg, tg, torch.from_numpy(poses).cuda(),
+                                              bbox=None if bbox is None else torch.from_numpy(bbox).cuda(), data_min=-5.0, data_max=37.5)
+    assert np.array_equal(got2.cpu().numpy(), want2)
+    # and against this library's own three kernels
+    three = cilqr_b200.to_occupancy(cilqr_b200.warp_batch(cilqr_b200.from_occupancy(occ), sg, tg, poses[:1], bbox=None if bbox is None else bbox[:1],
+                                                          want_idx=False)[0][0], 0.0, 100.0)
+    assert np.array_equal(three, got[0])
+
+
 def test_occupancy_device_buffers_and_full_size_round_trip():
     import torch
     n = 4096 * 4096

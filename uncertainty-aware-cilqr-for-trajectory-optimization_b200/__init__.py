@@ -5,6 +5,6 @@ from . import params, scenarios, solver, costmap, local_planner, receding_horizo
 from .params import Parameters, CostmapGeom, MEM_HOST, MEM_DEVICE, MERIT_TRACKING, MERIT_TOTAL  # noqa: F401
 from .params import OPT_FUSED, OPT_FUSED_SLOTS, OPT_CHUNKS, OPT_GRAPH, OPT_DERIV_STAGED, OPT_TRACE  # noqa: F401
 from .solver import iLQR, Obstacle, load_library, LibraryMissing, CilqrError, launch_count  # noqa: F401
-from .costmap import warp_batch, propagate_uncertainty, geom_size, from_occupancy, to_occupancy, rasterize_boxes  # noqa: F401
+from .costmap import warp_batch, warp_occupancy_batch, propagate_uncertainty, geom_size, from_occupancy, to_occupancy, rasterize_boxes  # noqa: F401
 from .local_planner import LocalPlanner  # noqa: F401
 from .receding_horizon import RecedingHorizon, ExperimentLog, read_log  # noqa: F401

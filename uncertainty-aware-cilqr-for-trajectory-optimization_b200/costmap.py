@@ -48,6 +48,47 @@ def warp_batch(src, src_geom, tgt_geom, poses, bbox=None, want_idx=True, variant
     return out, idx
 
 
+def warp_occupancy_batch(occ_src, src_geom, tgt_geom, poses, bbox=None, data_min=0.0, data_max=100.0, want_idx=False, out=None, idx=None):
+    """The frame on the wire format in one gather (costmap_warp_occupancy_batch): int8 OccupancyGrid data of the global map in,
+    int8 OccupancyGrid data of the P ego-frame maps out; equals to_occupancy(warp_batch(from_occupancy(occ_src))) byte for byte.
+    Returns (occ_out [P, rows*cols] int8, idx or None)."""
+    lib = load_library()
+    a = _Arg()
+    if hasattr(occ_src, "is_cuda"):
+        import torch
+        if not (occ_src.is_cuda and occ_src.dtype == torch.int8 and occ_src.is_contiguous()):
+            raise ValueError("occ_src must be a contiguous int8 CUDA tensor")
+        a._set_mem(MEM_DEVICE)
+        a.keep.append(occ_src)
+        ps = C.c_void_p(occ_src.data_ptr())
+    else:
+        occ_src = np.ascontiguousarray(occ_src, dtype=np.int8)
+        a._set_mem(MEM_HOST)
+        a.keep.append(occ_src)
+        ps = C.c_void_p(occ_src.ctypes.data)
+    pp = a.inp(poses)
+    P = int(poses.shape[0])
+    pb = a.inp(bbox, np.float32) if bbox is not None else None
+    rt, ct = geom_size(tgt_geom)
+    dev = a.mem == MEM_DEVICE
+    if out is None:
+        if dev:
+            import torch
+            out = torch.empty((P, rt * ct), dtype=torch.int8, device=occ_src.device)
+        else:
+            out = np.empty((P, rt * ct), dtype=np.int8)
+    po = C.c_void_p(out.data_ptr()) if dev else C.c_void_p(out.ctypes.data)
+    a.keep.append(out)
+    pi = None
+    if idx is not None:
+        pi = a.inp(idx, np.int32) if dev else C.c_void_p(idx.ctypes.data)
+    elif want_idx:
+        idx, pi = a.out((P, rt * ct), np.int32, dev, getattr(occ_src, "device", None))
+    _check(lib.costmap_warp_occupancy_batch(ps, C.byref(src_geom), C.byref(tgt_geom), pp, C.c_int(P), pb, C.c_float(data_min), C.c_float(data_max),
+                                            po, pi, C.c_int(a.mem), a.stream_ptr()))
+    return out, idx
+
+
 def propagate_uncertainty(vmap, geom, sin_theta, cos_theta, sigma_x, sigma_y, sigma_theta, index=0):
     """Returns (count int32 [cells-index], value float64 [cells-index]) — the vector<pair<int,double>> of
     thrust_propagateUncertainty."""

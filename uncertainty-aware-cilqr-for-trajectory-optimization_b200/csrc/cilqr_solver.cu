@@ -16,6 +16,7 @@
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
+#include <dlfcn.h>
 #include <new>
 #include <mutex>
 #include <vector>
@@ -1410,6 +1411,44 @@ int cilqr_forward_simulate(cilqr_handle h, int B, const double *state, const dou
     if (int rc = run_stage(h, A, st)) return rc;
     if (int rc = fetch_out(next, A.o0, (size_t)B * 4, mem, st)) return rc;
     if (mem == CILQR_MEM_HOST) CILQR_CUDA(cudaStreamSynchronize(st));
+    return 0;
+}
+
+// ---- multi-GPU exchange ---------------------------------------------------------------------------------------
+// NCCL is bound at run time (dlopen): the library has no link-time dependency on it, and a process that already carries an
+// NCCL (torch's, the system's) shares that one.
+typedef int (*NcclAllGatherFn)(const void *, void *, size_t, int, void *, cudaStream_t);
+static NcclAllGatherFn nccl_all_gather_fn()
+{
+    static NcclAllGatherFn fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void *sym = dlsym(RTLD_DEFAULT, "ncclAllGather"); // an NCCL already loaded into the process
+        if (!sym) {
+            for (const char *name : {"libnccl.so.2", "libnccl.so"}) {
+                if (void *lib = dlopen(name, RTLD_NOW | RTLD_GLOBAL)) {
+                    sym = dlsym(lib, "ncclAllGather");
+                    if (sym) break;
+                }
+            }
+        }
+        fn = reinterpret_cast<NcclAllGatherFn>(sym);
+    });
+    return fn;
+}
+
+int cilqr_gather(cilqr_handle h, void *nccl_comm, const double *local, int64_t count, double *gathered, void *stream)
+{
+    if (!h || !nccl_comm || !local || !gathered) return fail(CILQR_E_ARG, "null argument");
+    if (count < 0) return fail(CILQR_E_ARG, "negative count");
+    if (count == 0) return 0;
+    NcclAllGatherFn fn = nccl_all_gather_fn();
+    if (!fn) return fail(CILQR_E_STATE, "NCCL is not available in this process (libnccl.so.2 could not be loaded)");
+    DeviceScope scope(h->device);
+    constexpr int kNcclFloat64 = 8; // ncclDataType_t: ncclFloat64 / ncclDouble
+    const int rc = fn(local, gathered, (size_t)count, kNcclFloat64, nccl_comm, (cudaStream_t)stream);
+    if (rc != 0) return fail(CILQR_E_CUDA, "ncclAllGather failed (ncclResult_t %d)", rc);
+    g_launches.fetch_add(1, std::memory_order_relaxed);
     return 0;
 }
 

@@ -37,6 +37,20 @@ inline int fail(int code, const char *fmt, ...)
             return ::cilqr::fail(CILQR_E_CUDA, "kernel launch failed: %s (%s:%d)", cudaGetErrorString(e__), __FILE__, __LINE__); \
     } while (0)
 
+#ifdef __CUDACC__
+// GridMapRosConverter::toOccupancyGrid, one cell (grid_map_ros/src/GridMapRosConverter.cpp:297-302):
+// value = isnan(v) ? -1 : 0 + min(max(0, v), 1) * 100 with v = (data - min) / (max - min), assigned to an int8 (truncation).
+__device__ __forceinline__ int8_t occupancy_cell(float d, float dmin, float dmax)
+{
+    float value = __fdiv_rn(__fsub_rn(d, dmin), __fsub_rn(dmax, dmin));
+    if (isnan(value))
+        value = -1.0f;
+    else
+        value = __fadd_rn(0.0f, __fmul_rn(fminf(fmaxf(0.0f, value), 1.0f), 100.0f));
+    return (int8_t)(int)value; // float -> integer conversion truncates, like the reference's assignment to int8_t
+}
+#endif
+
 // Device buffer that is only ever grown (workspaces live as long as the handle).
 struct DevBuf {
     void *p = nullptr;

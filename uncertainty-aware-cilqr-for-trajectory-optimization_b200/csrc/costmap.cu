@@ -349,6 +349,211 @@ __global__ void __launch_bounds__(kWarpThreads, 5) warp_tma_kernel(const __grid_
         warp_tile_body<true, false>(G, T, src, sbox, Vx, Vy, sn, cn, i0, j0, bb, out + pose * cells, ix, tid);
 }
 
+// ---- the warp on the wire format (row N2 fused into W1) ---------------------------------------------------------------
+// The reference's frame is fromOccupancyGrid (int8 -> float layer, reversed order, -1 -> NaN; GridMapRosConverter.cpp:259-266,
+// call site local_costmap.cpp:169) -> warp loop (local_costmap.cpp:242-264) -> toOccupancyGrid (float -> int8 0..100, NaN ->
+// -1, reversed; :291-306, call site local_costmap.cpp:298).  The two conversions are a reversal and a per-cell map, so they
+// fold into the gather's load and store: this kernel reads the global map as int8 occupancy data and writes the ego-frame map
+// as int8 occupancy data — 1 B read + 1 B written per cell instead of 4 + 4 (plus the two conversion passes) — with the same
+// index arithmetic (tile_setup, fixed-point predictor, exact chain on border cells), so the index map stays bit-identical.
+// Thread = 8 consecutive cells along index 0: eight byte gathers through the read-only path (a 4096^2 source is 16.7 MB of
+// int8: L2-resident), one 64-bit store of the reversed bytes, two 128-bit stores of the optional index map.
+struct OccTile {
+    const float *bb;
+    int32_t *ix_out;
+    int8_t *out;
+    const int8_t *occ_src;
+    const uint8_t *sbox;
+    const int8_t *lut;
+    int a0, a1;
+    float dmin, dmax;
+};
+constexpr int kOccBoxWc = 144, kOccBoxHc = kBoxH; // (= kOccBoxW / kOccBoxH below)
+
+// Thread = 8 consecutive cells along index 0, two rows of the 64 x 64 tile per thread.  FAST: the tile's whole source box lies
+// inside the map and is staged — index prediction, one shared-memory byte, one table look-up per cell.  The cells within 2^-17
+// cell of a source-cell border (about 3e-5 of all) are redone afterwards with the reference's own chain, outside the hot loop.
+template <bool FAST>
+__device__ __forceinline__ void occupancy_tile_body(const WarpGeom &G, const TileShared &T, const OccTile &O, double Vx, double Vy, double sn, double cn,
+                                                    int i0, int j0, int tid, bool staged = true)
+{
+    const long long cells = (long long)G.rows_t * G.cols_t, ns = (long long)G.rows_s * G.cols_s;
+    const bool vec_ok = (G.rows_t & 7) == 0 && (reinterpret_cast<uintptr_t>(O.out) & 7) == 0;
+    const bool bb_vec = O.bb && vec_ok && (reinterpret_cast<uintptr_t>(O.bb) & 15) == 0;
+    const bool ix_vec = O.ix_out && vec_ok && (reinterpret_cast<uintptr_t>(O.ix_out) & 15) == 0;
+    const double sc = G.ratio * (double)(1u << kFrac);
+    const unsigned Axi = (unsigned)__double2int_rn(sc * cn), Axj = (unsigned)__double2int_rn(-sc * sn);
+    const unsigned Ayi = (unsigned)__double2int_rn(sc * sn), Ayj = Axi;
+    const int org0 = T.org0, org1 = T.org1, gbase = org1 * G.rows_s + org0;
+    const bool exact_only = !FAST && T.exact_only != 0;
+    const int8_t unknown = O.lut[255]; // the conversion of an unknown (-1) / out-of-map cell
+    const int lq = tid & 7;
+#pragma unroll 1
+    for (int pass = 0; pass < 2; ++pass) {
+        const int lj = (tid >> 3) + 32 * pass;
+        const int i = i0 + 8 * lq, j = j0 + lj;
+        if (j >= G.cols_t || i >= G.rows_t)
+            continue;
+        unsigned tx = T.Tx0 + (unsigned)(8 * lq) * Axi + (unsigned)lj * Axj;
+        unsigned ty = T.Ty0 + (unsigned)(8 * lq) * Ayi + (unsigned)lj * Ayj;
+        int gidx[8];
+        int8_t o[8];
+        unsigned unc = exact_only ? 0xffu : 0u;
+        const size_t l = (size_t)j * G.rows_t + i;
+        if (!exact_only) {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+                const int ixs = (int)(tx >> kFrac), iys = (int)(ty >> kFrac);
+                if (((tx + kDelta) & kFracMask) < 2 * kDelta || ((ty + kDelta) & kFracMask) < 2 * kDelta) // within 2^-17 cell of a border
+                    unc |= 1u << e;
+                const int g = iys * G.rows_s + ixs + gbase;
+                if (FAST) {
+                    gidx[e] = g;
+                    // (a predicted coordinate a hair below the box origin wraps around: such a cell is flagged and redone below, the
+                    // clamp only keeps this read inside the staged box)
+                    o[e] = O.lut[O.sbox[(O.a1 - min(iys, kOccBoxHc - 1)) * kOccBoxWc + (O.a0 - min(ixs, kBoxW - 1))]];
+                } else {
+                    const bool ok = (unsigned)(ixs + org0) < (unsigned)G.rows_s && (unsigned)(iys + org1) < (unsigned)G.cols_s;
+                    gidx[e] = ok ? g : -1;
+                    uint8_t byte = 255;
+                    if (ok) {
+                        if (staged && (unsigned)ixs < (unsigned)kBoxW && (unsigned)iys < (unsigned)kOccBoxHc)
+                            byte = O.sbox[(O.a1 - iys) * kOccBoxWc + (O.a0 - ixs)];
+                        else
+                            byte = (uint8_t)__ldg(O.occ_src + (ns - 1 - (long long)g));
+                    }
+                    o[e] = ok ? O.lut[byte] : unknown; // the reference throws for out-of-map cells (GridMap.cpp:160-166): unknown here
+                }
+                tx += Axi;
+                ty += Ayi;
+            }
+        }
+        if (unc) { // the reference's own chain for the flagged cells
+#pragma unroll 1
+            for (int e = 0; e < 8; ++e) {
+                if (!((unc >> e) & 1u))
+                    continue;
+                double px, py;
+                cell_position(T, 8 * lq + e, lj, Vx, Vy, px, py);
+                const int g0 = source_index_exact(px, G.hLx, G.Psx, G.r_s), g1 = source_index_exact(py, G.hLy, G.Psy, G.r_s);
+                const bool ok = source_valid_exact(G, px, py, g0, g1);
+                const int g = g0 + G.rows_s * g1;
+                const int8_t v = ok ? O.lut[(uint8_t)__ldg(O.occ_src + (ns - 1 - (long long)g))] : unknown;
+#pragma unroll
+                for (int q = 0; q < 8; ++q) // (constant indices keep the arrays in registers)
+                    if (q == e) { gidx[q] = ok ? g : -1; o[q] = v; }
+            }
+        }
+        if (O.bb) { // local_costmap.cpp:260-263: bounding-box layer wins when > 90
+            float bbv[8];
+            if (bb_vec) {
+                const float4 b0 = __ldcs(reinterpret_cast<const float4 *>(O.bb + l)), b1 = __ldcs(reinterpret_cast<const float4 *>(O.bb + l + 4));
+                bbv[0] = b0.x; bbv[1] = b0.y; bbv[2] = b0.z; bbv[3] = b0.w; bbv[4] = b1.x; bbv[5] = b1.y; bbv[6] = b1.z; bbv[7] = b1.w;
+            } else {
+#pragma unroll
+                for (int e = 0; e < 8; ++e)
+                    bbv[e] = i + e < G.rows_t ? O.bb[l + e] : 0.0f;
+            }
+#pragma unroll
+            for (int e = 0; e < 8; ++e)
+                if (bbv[e] > 90.f) o[e] = occupancy_cell(bbv[e], O.dmin, O.dmax);
+        }
+        if (vec_ok) { // occ[n - 1 - (l + e)]: the eight bytes in reverse, one 64-bit store
+            const unsigned lo = (unsigned)(uint8_t)o[7] | ((unsigned)(uint8_t)o[6] << 8) | ((unsigned)(uint8_t)o[5] << 16) | ((unsigned)(uint8_t)o[4] << 24);
+            const unsigned hi = (unsigned)(uint8_t)o[3] | ((unsigned)(uint8_t)o[2] << 8) | ((unsigned)(uint8_t)o[1] << 16) | ((unsigned)(uint8_t)o[0] << 24);
+            __stcs(reinterpret_cast<uint2 *>(O.out + (cells - 8 - (long long)l)), make_uint2(lo, hi));
+        } else {
+#pragma unroll
+            for (int e = 0; e < 8; ++e)
+                if (i + e < G.rows_t) O.out[cells - 1 - (long long)(l + e)] = o[e];
+        }
+        if (O.ix_out) {
+            if (ix_vec) {
+                __stcs(reinterpret_cast<int4 *>(O.ix_out + l), make_int4(gidx[0], gidx[1], gidx[2], gidx[3]));
+                __stcs(reinterpret_cast<int4 *>(O.ix_out + l + 4), make_int4(gidx[4], gidx[5], gidx[6], gidx[7]));
+            } else {
+#pragma unroll
+                for (int e = 0; e < 8; ++e)
+                    if (i + e < G.rows_t) O.ix_out[l + e] = gidx[e];
+            }
+        }
+    }
+}
+
+constexpr int kOccBoxW = 144; // staged box, index-0 extent in bytes: the 108 source cells a tile can span + up to 15 of alignment (TMA
+                              // needs the innermost start coordinate on a 16-byte boundary), a multiple of 16; 144 B = 36 words keeps
+                              // consecutive box rows 4 banks apart (128 would put every row on the same banks)
+constexpr int kOccBoxH = kBoxH;
+static_assert(kOccBoxW == kOccBoxWc && kOccBoxH == kOccBoxHc, "one box size");
+
+// STAGED: the tile's source box arrives through the TMA unit (uint8 tensor map over the occupancy data, whose order is the
+// layer's reversed: layer cell (i, j) is occ[(rows - 1 - i) + rows (cols - 1 - j)]), and the int8 -> float -> int8 conversion
+// of a cell that no bounding box overrides is one look-up in a 256-entry table that the CTA fills with occupancy_cell itself.
+// !STAGED (source rows not a multiple of 16 bytes, or an unaligned buffer): byte gathers through the read-only path.
+template <bool STAGED>
+__global__ void __launch_bounds__(kWarpThreads, 3) warp_occupancy_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ WarpGeom G,
+                                                                       const int8_t *__restrict__ occ_src, const double *__restrict__ poses,
+                                                                       const float *__restrict__ bbox, float dmin, float dmax,
+                                                                       int8_t *__restrict__ occ_out, int32_t *__restrict__ idx)
+{
+    __shared__ __align__(128) uint8_t sbox[STAGED ? kOccBoxW * kOccBoxH : 16];
+    __shared__ int8_t lut[256];
+    __shared__ TileShared T;
+    __shared__ __align__(8) unsigned long long bar;
+    const int tid = threadIdx.x;
+    const int tile = blockIdx.x, pose = blockIdx.y;
+    const int i0 = (tile % G.tiles_i) * kTile, j0 = (tile / G.tiles_i) * kTile;
+    const double Vx = poses[4 * pose], Vy = poses[4 * pose + 1], sn = poses[4 * pose + 2], cn = poses[4 * pose + 3];
+    if (STAGED && tid == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&bar)));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    { // toOccupancyGrid(fromOccupancyGrid(b)) for every byte value (GridMapRosConverter.cpp:263, 297-302)
+        const int8_t b = (int8_t)tid;
+        lut[tid & 255] = occupancy_cell(b != -1 ? (float)b : __int_as_float(0x7fc00000), dmin, dmax);
+    }
+    tile_setup(G, T, i0, j0, Vx, Vy, sn, cn, tid); // ends with __syncthreads()
+    const bool staged = STAGED && !T.exact_only;
+    // occ coordinates of the box: index 0 runs backwards, so layer column org0 + ix sits at c0 + (a0 - ix)
+    const int c0 = (G.rows_s - T.org0 - kBoxW) & ~15, a0 = (G.rows_s - 1 - T.org0) - c0;
+    const int c1 = G.cols_s - T.org1 - kOccBoxH, a1 = (G.cols_s - 1 - T.org1) - c1;
+    if (STAGED) {
+        if (staged && tid == 0) {
+            const unsigned bytes = kOccBoxW * kOccBoxH;
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(&bar)), "r"(bytes) : "memory");
+            asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                         ::"r"(smem_u32(sbox)), "l"(&tmap), "r"(c0), "r"(c1), "r"(smem_u32(&bar))
+                         : "memory");
+        }
+        if (staged) {
+            unsigned done = 0;
+            while (!done) {
+                asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                             : "=r"(done)
+                             : "r"(smem_u32(&bar))
+                             : "memory");
+            }
+        }
+    }
+    const long long cells = (long long)G.rows_t * G.cols_t;
+    OccTile O;
+    O.bb = bbox ? bbox + pose * cells : nullptr;
+    O.ix_out = idx ? idx + pose * cells : nullptr;
+    O.out = occ_out + pose * cells;
+    O.occ_src = occ_src;
+    O.sbox = sbox;
+    O.lut = lut;
+    O.a0 = a0;
+    O.a1 = a1;
+    O.dmin = dmin;
+    O.dmax = dmax;
+    // whole box inside the map and staged: no validity tests, every gather comes from shared memory
+    if (staged && T.inside)
+        occupancy_tile_body<true>(G, T, O, Vx, Vy, sn, cn, i0, j0, tid);
+    else
+        occupancy_tile_body<false>(G, T, O, Vx, Vy, sn, cn, i0, j0, tid, staged);
+}
+
 // ------------------------------------------------------------------------------------------------- host helpers
 static int geom_size_host(const costmap_geom *g, int *rows, int *cols)
 {
@@ -358,6 +563,32 @@ static int geom_size_host(const costmap_geom *g, int *rows, int *cols)
     *cols = (int)std::round(g->length_y / g->resolution);
     if (*rows < 1 || *cols < 1)
         return fail(CILQR_E_ARG, "costmap geometry has no cells");
+    return 0;
+}
+
+// setGeometry (GridMap.cpp:45-62) of both maps and the constants of the index chain.
+static int make_warp_geom(const costmap_geom *src_geom, const costmap_geom *tgt_geom, WarpGeom &G)
+{
+    if (int rc = geom_size_host(src_geom, &G.rows_s, &G.cols_s)) return rc;
+    if (int rc = geom_size_host(tgt_geom, &G.rows_t, &G.cols_t)) return rc;
+    if ((long long)G.rows_s * G.cols_s > 2147483647LL) return fail(CILQR_E_ARG, "source map has more than 2^31-1 cells");
+    // setGeometry (GridMap.cpp:57-58): length_ = size * resolution; getVectorToFirstCell (GridMapMath.cpp:41-52)
+    const double Ltx = G.rows_t * tgt_geom->resolution, Lty = G.cols_t * tgt_geom->resolution;
+    G.r_t = tgt_geom->resolution;
+    G.base_x = tgt_geom->pos_x + (0.5 * Ltx - 0.5 * G.r_t);
+    G.base_y = tgt_geom->pos_y + (0.5 * Lty - 0.5 * G.r_t);
+    G.r_s = src_geom->resolution;
+    G.rinv_s = 1.0 / G.r_s;
+    G.Lx = G.rows_s * G.r_s;
+    G.Ly = G.cols_s * G.r_s;
+    G.hLx = 0.5 * G.Lx;
+    G.hLy = 0.5 * G.Ly;
+    G.Psx = src_geom->pos_x;
+    G.Psy = src_geom->pos_y;
+    G.ratio = G.r_t / G.r_s;
+    G.mag = (std::fabs(G.base_x) + std::fabs(G.base_y) + Ltx + Lty + G.hLx + G.hLy + std::fabs(G.Psx) + std::fabs(G.Psy)) / G.r_s;
+    G.tiles_i = (G.rows_t + kTile - 1) / kTile;
+    G.tiles_j = (G.cols_t + kTile - 1) / kTile;
     return 0;
 }
 
@@ -414,32 +645,13 @@ int costmap_warp_batch(const float *src, const costmap_geom *src_geom, const cos
     if (P < 0 || P > 65535) return fail(CILQR_E_ARG, "P = %d outside [0, 65535]", P);
     if (variant < 0 || variant > 2) return fail(CILQR_E_ARG, "unknown variant %d", variant);
     WarpGeom G;
-    if (int rc = geom_size_host(src_geom, &G.rows_s, &G.cols_s)) return rc;
-    if (int rc = geom_size_host(tgt_geom, &G.rows_t, &G.cols_t)) return rc;
-    if ((long long)G.rows_s * G.cols_s > 2147483647LL) return fail(CILQR_E_ARG, "source map has more than 2^31-1 cells");
+    if (int rc = make_warp_geom(src_geom, tgt_geom, G)) return rc;
     if (P == 0) return 0;
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
         cudaGetLastError();
         return fail(CILQR_E_CUDA, "no CUDA device: this library has no CPU path");
     }
-    // setGeometry (GridMap.cpp:57-58): length_ = size * resolution; getVectorToFirstCell (GridMapMath.cpp:41-52)
-    const double Ltx = G.rows_t * tgt_geom->resolution, Lty = G.cols_t * tgt_geom->resolution;
-    G.r_t = tgt_geom->resolution;
-    G.base_x = tgt_geom->pos_x + (0.5 * Ltx - 0.5 * G.r_t);
-    G.base_y = tgt_geom->pos_y + (0.5 * Lty - 0.5 * G.r_t);
-    G.r_s = src_geom->resolution;
-    G.rinv_s = 1.0 / G.r_s;
-    G.Lx = G.rows_s * G.r_s;
-    G.Ly = G.cols_s * G.r_s;
-    G.hLx = 0.5 * G.Lx;
-    G.hLy = 0.5 * G.Ly;
-    G.Psx = src_geom->pos_x;
-    G.Psy = src_geom->pos_y;
-    G.ratio = G.r_t / G.r_s;
-    G.mag = (std::fabs(G.base_x) + std::fabs(G.base_y) + Ltx + Lty + G.hLx + G.hLy + std::fabs(G.Psx) + std::fabs(G.Psy)) / G.r_s;
-    G.tiles_i = (G.rows_t + kTile - 1) / kTile;
-    G.tiles_j = (G.cols_t + kTile - 1) / kTile;
 
     cudaStream_t st = (cudaStream_t)stream;
     const size_t cells = (size_t)G.rows_t * G.cols_t, scells = (size_t)G.rows_s * G.cols_s;
@@ -502,6 +714,78 @@ int costmap_warp_batch(const float *src, const costmap_geom *src_geom, const cos
         CILQR_CUDA(cudaStreamSynchronize(st));
     }
     return 0;
+}
+
+int costmap_warp_occupancy_batch(const int8_t *occ_src, const costmap_geom *src_geom, const costmap_geom *tgt_geom, const double *poses, int P,
+                                 const float *bbox, float data_min, float data_max, int8_t *occ_out, int32_t *idx, int mem, void *stream)
+{
+    if (!occ_src || !poses || !occ_out) return fail(CILQR_E_ARG, "null argument");
+    if (P < 0 || P > 65535) return fail(CILQR_E_ARG, "P = %d outside [0, 65535]", P);
+    WarpGeom G;
+    if (int rc = make_warp_geom(src_geom, tgt_geom, G)) return rc;
+    if (P == 0) return 0;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        return fail(CILQR_E_CUDA, "no CUDA device: this library has no CPU path");
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t cells = (size_t)G.rows_t * G.cols_t, scells = (size_t)G.rows_s * G.cols_s;
+    const int8_t *d_src = occ_src;
+    const float *d_bbox = bbox;
+    const double *d_poses = poses;
+    int8_t *d_out = occ_out;
+    int32_t *d_idx = idx;
+    DevBuf t_src, t_poses, t_bbox, t_out, t_idx; // host buffers: staging of this call only (no shared state between calls)
+    if (mem == CILQR_MEM_HOST) {
+        if (int rc = t_src.reserve(scells)) return rc;
+        if (int rc = t_poses.reserve((size_t)P * 4 * sizeof(double))) { t_src.release(); return rc; }
+        if (int rc = t_out.reserve(P * cells)) { t_src.release(); t_poses.release(); return rc; }
+        cudaMemcpyAsync(t_src.p, occ_src, scells, cudaMemcpyHostToDevice, st);
+        cudaMemcpyAsync(t_poses.p, poses, (size_t)P * 4 * sizeof(double), cudaMemcpyHostToDevice, st);
+        d_src = t_src.as<int8_t>();
+        d_poses = t_poses.as<double>();
+        d_out = t_out.as<int8_t>();
+        if (bbox && t_bbox.reserve(P * cells * sizeof(float)) == 0) {
+            cudaMemcpyAsync(t_bbox.p, bbox, P * cells * sizeof(float), cudaMemcpyHostToDevice, st);
+            d_bbox = t_bbox.as<float>();
+        }
+        if (idx && t_idx.reserve(P * cells * sizeof(int32_t)) == 0) d_idx = t_idx.as<int32_t>();
+    }
+    int rc = 0;
+    if ((bbox && d_bbox == bbox && mem == CILQR_MEM_HOST) || (idx && d_idx == idx && mem == CILQR_MEM_HOST)) {
+        rc = fail(CILQR_E_ALLOC, "out of device memory for the staging buffers");
+    } else {
+        dim3 grid(G.tiles_i * G.tiles_j, P);
+        // the TMA unit needs a 16-byte aligned base and a row pitch that is a multiple of 16 bytes (and the footprint of a tile has to
+        // fit the box: target resolution <= source resolution)
+        const bool staged = (G.rows_s % 16 == 0) && ((((uintptr_t)d_src) & 15) == 0) && (G.r_t <= G.r_s * (1.0 + 1e-9)) && encode_tiled_fn();
+        CUtensorMap tmap;
+        std::memset(&tmap, 0, sizeof(tmap));
+        CUresult cr = CUDA_SUCCESS;
+        if (staged) {
+            const cuuint64_t gdim[2] = {(cuuint64_t)G.rows_s, (cuuint64_t)G.cols_s};
+            const cuuint64_t gstride[1] = {(cuuint64_t)G.rows_s};
+            const cuuint32_t box[2] = {kOccBoxW, kOccBoxH};
+            const cuuint32_t estr[2] = {1, 1};
+            cr = encode_tiled_fn()(&tmap, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<int8_t *>(d_src), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                                   CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        }
+        if (staged && cr == CUDA_SUCCESS)
+            warp_occupancy_kernel<true><<<grid, kWarpThreads, 0, st>>>(tmap, G, d_src, d_poses, d_bbox, data_min, data_max, d_out, d_idx);
+        else
+            warp_occupancy_kernel<false><<<grid, kWarpThreads, 0, st>>>(tmap, G, d_src, d_poses, d_bbox, data_min, data_max, d_out, d_idx);
+        g_launches.fetch_add(1, std::memory_order_relaxed);
+        cudaError_t e = cudaGetLastError();
+        if (e == cudaSuccess && mem == CILQR_MEM_HOST) {
+            cudaMemcpyAsync(occ_out, d_out, P * cells, cudaMemcpyDeviceToHost, st);
+            if (idx) cudaMemcpyAsync(idx, d_idx, P * cells * sizeof(int32_t), cudaMemcpyDeviceToHost, st);
+            e = cudaStreamSynchronize(st);
+        }
+        if (e != cudaSuccess) rc = fail(CILQR_E_CUDA, "costmap_warp_occupancy_batch: %s", cudaGetErrorString(e));
+    }
+    t_src.release(); t_poses.release(); t_bbox.release(); t_out.release(); t_idx.release();
+    return rc;
 }
 
 } // extern "C"

@@ -43,16 +43,7 @@ __global__ void __launch_bounds__(256) from_occupancy_kernel(const int8_t *__res
         }
     }
 }
-// occ[n-1-index] = (int8) value, value = isnan(v) ? -1 : 0 + min(max(0, v), 1) * 100, v = (data - min) / (max - min)   (:291-306)
-__device__ __forceinline__ int8_t occupancy_cell(float d, float dmin, float dmax)
-{
-    float value = __fdiv_rn(__fsub_rn(d, dmin), __fsub_rn(dmax, dmin));
-    if (isnan(value))
-        value = -1.0f;
-    else
-        value = __fadd_rn(0.0f, __fmul_rn(fminf(fmaxf(0.0f, value), 1.0f), 100.0f));
-    return (int8_t)(int)value; // float -> integer conversion truncates, like the reference's assignment to int8_t
-}
+// occ[n-1-index] = occupancy_cell(data[index])   (GridMapRosConverter.cpp:291-306; occupancy_cell in common.cuh)
 __global__ void __launch_bounds__(256) to_occupancy_kernel(const float *__restrict__ data, long long n, float dmin, float dmax, int8_t *__restrict__ occ)
 {
     const long long stride = (long long)gridDim.x * blockDim.x;
