@@ -71,6 +71,8 @@ def parse_args():
     ap.add_argument("--e2e-threads", type=int, default=4, help="host threads (one solver handle each) in the end-to-end measurement")
     ap.add_argument("--fused", type=int, default=-1, help="CILQR_OPT_FUSED (-1 automatic, 1 fused on-chip kernel, 0 round kernels)")
     ap.add_argument("--fused-slots", type=int, default=0, help="CILQR_OPT_FUSED_SLOTS (0 automatic)")
+    ap.add_argument("--gather", default="peer", choices=["peer", "nccl"], help="the U* exchange at N > 1: peer-to-peer copies on the copy engines "
+                                                                                 "(cilqr_gather_copy) or NCCL's all-gather kernel")
     ap.add_argument("--no-graph", action="store_true", help="CILQR_OPT_GRAPH = 0: direct launches (for ncu launch lists)")
     return ap.parse_args()
 
@@ -338,7 +340,13 @@ def solve_case(args, p, device, rank, world, first_id, B, n_obs, n_alphas, steps
         # NVLink under step i+1's solve, which writes the other buffer (no snapshot copy).  The timed region ends with a
         # device-wide synchronize, so the last gather is inside it.
         U2 = torch.empty_like(U)
-        gathered = torch.empty((world * B, 2 * N), dtype=torch.float64, device=device)
+        peer = None
+        if args.gather == "peer":  # copy-engine exchange (cilqr_gather_copy): no kernel competes with the next step's solve
+            from cilqr_b200 import dist as cdist
+            peer = cdist.PeerGather(solver, B, 2 * N, device)
+            gathered = peer.gathered
+        else:
+            gathered = torch.empty((world * B, 2 * N), dtype=torch.float64, device=device)
         comm_stream = torch.cuda.Stream(device=device)
         solved, gathered_ev = torch.cuda.Event(), [torch.cuda.Event(), torch.cuda.Event()]
         for e in gathered_ev:
@@ -366,7 +374,10 @@ def solve_case(args, p, device, rank, world, first_id, B, n_obs, n_alphas, steps
             solved.record(cur)
             with torch.cuda.stream(comm_stream):
                 comm_stream.wait_event(solved)
-                torch.distributed.all_gather_into_tensor(gathered, Ub)
+                if peer is not None:
+                    peer.gather(Ub)
+                else:
+                    torch.distributed.all_gather_into_tensor(gathered, Ub)
                 gathered_ev[i % 2].record(comm_stream)
         return Ub
 
@@ -393,6 +404,12 @@ def solve_case(args, p, device, rank, world, first_id, B, n_obs, n_alphas, steps
     total_ms = max_over_ranks(e0.elapsed_time(e1), world, device)
     if do_gather:
         assert torch.equal(gathered[rank * B:(rank + 1) * B], last), "all-gather of U*: this rank's slice differs from its own result"
+        # every rank's slice, on every rank: the rows' sums agree with the owners' (exchanged with a plain NCCL all-gather)
+        sums = torch.empty(world * B, dtype=torch.float64, device=device)
+        torch.distributed.all_gather_into_tensor(sums, last.sum(dim=1))
+        assert torch.equal(gathered.sum(dim=1), sums), "gathered U*: a peer's slice differs from what the peer solved"
+        if peer is not None:
+            peer.close()
     launches = cilqr_b200.launch_count() - launches0
     kernel_ms = float(np.mean([a.elapsed_time(b) for a, b in kern_ev]))
     iters = solver.iterations.cpu().numpy()
@@ -762,7 +779,9 @@ def run_b200_arm(args):
                          % ("working set larger than L2" if B * (n_obs * 8 * (8 + N) + (18 + 18 * (N + 1)) * 8) > 126e6 else
                             "working set L2-resident: a parity-size configuration, not the headline", B * n_obs * 8 * (8 + N) / 1e9,
                             B * (18 + 18 * (N + 1)) * 8 / 1e9),
-                   "collective": "all_gather U* (NCCL), on its own stream under the next step's solve" if world > 1 else "none"},
+                   "collective": ("none" if world == 1 else "all-gather of U* by peer-to-peer copies on the copy engines (cilqr_gather_copy) + a one-element NCCL all-reduce "
+                                  "as the barrier, on its own stream under the next step's solve" if args.gather == "peer" else
+                                  "all_gather U* (NCCL), on its own stream under the next step's solve")},
         "clocks": clocks, "e2e": e2e, "gpu_launches": main["launches"],
         "roofline": roof,
         "hbm": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,

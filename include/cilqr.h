@@ -194,6 +194,24 @@ int cilqr_solve_batch(cilqr_handle h, int B, const double *x0, double *U, const 
  */
 int cilqr_gather(cilqr_handle h, void *nccl_comm, const double *local, int64_t count, double *gathered, void *stream);
 
+/*
+ * The same exchange on the copy engines (one process per GPU on one box; no reference counterpart): no kernel, so nothing is
+ * taken from the SMs while the next solve runs.  Every rank creates its `gathered` buffer (count x ranks doubles) with
+ * cilqr_gather_buffer_create, hands the 64-byte IPC handle to its peers (any host-side channel: MPI, torch.distributed, a
+ * pipe), opens theirs with cilqr_gather_buffer_open, and then calls cilqr_gather_copy after each solve: this rank's `count`
+ * doubles are written into slot `rank` of every buffer in gathered[0 .. n_ranks-1] (its own included) with peer-to-peer copies
+ * enqueued on `stream`.  The copies are one-sided: a rank knows that ITS writes have landed when `stream` reaches that point;
+ * that the PEERS' writes into its own buffer have landed is known after any stream-ordered barrier among the ranks (e.g. a
+ * one-element NCCL all-reduce enqueued after the copies; dist.PeerGather does that).
+ */
+#define CILQR_IPC_HANDLE_BYTES 64
+int cilqr_gather_buffer_create(int64_t bytes, void **dev_ptr, void *ipc_handle /* CILQR_IPC_HANDLE_BYTES out */);
+int cilqr_gather_buffer_open(const void *ipc_handle, void **peer_ptr);
+int cilqr_gather_buffer_close(void *peer_ptr);
+int cilqr_gather_buffer_destroy(void *dev_ptr);
+int cilqr_gather_copy(cilqr_handle h, int n_ranks, int rank, const double *local, int64_t count, void *const *gathered,
+                      void *stream);
+
 /* Work done by the last cilqr_solve_batch call with n_alphas == 1 (measurement helper, no reference counterpart): how many
  * times the cost (Constraints::get_J) and the derivative pass + backward/forward pass ran, summed over the scenarios, and
  * the number of solver rounds that had work (round kernels) plus the largest number of iterations any CTA of the fused kernel made.  The reference's own iteration counter (`iters`) also counts the iterations in

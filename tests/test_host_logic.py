@@ -81,6 +81,13 @@ if rank == 0:
     assert U.shape == (TOTAL, 100), U.shape
     assert np.array_equal(U.numpy(), want), "sharded + gathered result differs from the unsharded solve"
     print("GLOO_OK")
+# ragged shards (7 scenarios over 2 ranks: 4 + 3) with counts left to the ranks to exchange
+lo7, hi7 = dist.shard_range(7, rank, world)
+rows = torch.arange(lo7, hi7, dtype=torch.float64).reshape(-1, 1).repeat(1, 3)
+G7 = dist.gather_trajectories(rows)
+assert G7.shape == (7, 3) and torch.equal(G7[:, 0], torch.arange(7, dtype=torch.float64)), G7
+if rank == 0:
+    print("RAGGED_OK")
 td.barrier()
 td.destroy_process_group()
 """
@@ -93,7 +100,7 @@ def test_world_size_2_shard_and_gather_over_gloo(tmp_path, port):
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
                         "--master-port", "29611", str(script)], capture_output=True, text=True, env=env, timeout=600)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
-    assert "GLOO_OK" in r.stdout
+    assert "GLOO_OK" in r.stdout and "RAGGED_OK" in r.stdout
 
 
 # ------------------------------------------------------------------------------------------------ row N4: receding-horizon wrapper (host side)
