@@ -212,6 +212,24 @@ int cilqr_gather_buffer_destroy(void *dev_ptr);
 int cilqr_gather_copy(cilqr_handle h, int n_ranks, int rank, const double *local, int64_t count, void *const *gathered,
                       void *stream);
 
+/*
+ * A solve that allocates nothing.  No counterpart in the reference; added for callers
+ * that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * One step of the covariance-inflated solve — what cilqr_set_obstacles_cv followed by cilqr_solve_batch (n_alphas = 1) computes,
+ * bit for bit — on DEVICE buffers of the handle's device, enqueued on `stream`; arguments as in those two entry points
+ * (X, J, iters, status may be NULL).  Its scratch (the prepared obstacle records and the solve kernel's control block) is a
+ * static device array of CILQR_STATIC_SCRATCH_BYTES (16 MiB) that every GPU loading the library holds until exit:
+ * 256 + B * n_obs * (8 + horizon) * 8 bytes are needed (cilqr_static_scratch_bytes), e.g. 1 024 scenarios x 20 obstacles at
+ * N = 50; larger requests are rejected with CILQR_E_ARG.  The call itself makes no cudaMalloc / cudaFree and touches none of
+ * the handle's buffers or obstacle state.  All calls in a process share the array per GPU: calls that overlap on the same GPU
+ * (two streams, two handles, two threads) race — serialise them.
+ */
+#define CILQR_STATIC_SCRATCH_BYTES (16u << 20)
+int cilqr_static_scratch_bytes(int64_t *bytes_needed, const cilqr_params *p, int B, int n_obs);
+int cilqr_solve_cv_static(cilqr_handle h, int B, int n_obs, const double *state0, const double *LW, const double *sigma,
+                          double kappa, const double *x0, double *U, const double *poly, const double *xlp, double *X,
+                          double *J, int32_t *iters, int32_t *status, void *stream);
+
 /* Work done by the last cilqr_solve_batch call with n_alphas == 1 (measurement helper, no reference counterpart): how many
  * times the cost (Constraints::get_J) and the derivative pass + backward/forward pass ran, summed over the scenarios, and
  * the number of solver rounds that had work (round kernels) plus the largest number of iterations any CTA of the fused kernel made.  The reference's own iteration counter (`iters`) also counts the iterations in

@@ -1511,4 +1511,97 @@ int cilqr_gather_copy(cilqr_handle h, int n_ranks, int rank, const double *local
     return 0;
 }
 
+// ---- a solve that allocates nothing ------------------------------------------------------------------------------------
+// For callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it): one
+// step of the covariance-inflated solve — the work of cilqr_set_obstacles_cv + cilqr_solve_batch (n_alphas = 1) on device
+// buffers — whose scratch (the prepared obstacle records and the fused kernel's control block) lives in a file-scope device
+// array instead of the handle's grow-on-demand buffers.  Every GPU that loads the library holds the array until exit.
+// In host code `g_static_scratch` is a host-side stand-in, not a device address: the kernels get the address that
+// cudaGetSymbolAddress returns, looked up once per device with that device current.
+constexpr size_t kStaticScratchBytes = CILQR_STATIC_SCRATCH_BYTES;
+constexpr size_t kStaticCtlBytes = 256; // fused kernel's control block at the head of the array: scenario counter, 4 x uint64 tallies
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBytes];
+
+static int static_scratch_address(int device, unsigned char **out)
+{
+    constexpr int kMaxDevices = 64;
+    static std::mutex mu;
+    static unsigned char *addr[kMaxDevices] = {};
+    if (device < 0 || device >= kMaxDevices) return fail(CILQR_E_ARG, "device %d outside [0, %d)", device, kMaxDevices);
+    std::lock_guard<std::mutex> lock(mu);
+    if (!addr[device]) { // (the caller has made `device` current: DeviceScope)
+        void *p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_static_scratch);
+        if (e != cudaSuccess || !p) return fail(CILQR_E_CUDA, "cudaGetSymbolAddress(g_static_scratch) failed: %s", cudaGetErrorString(e));
+        addr[device] = static_cast<unsigned char *>(p);
+    }
+    *out = addr[device];
+    return 0;
+}
+
+int cilqr_static_scratch_bytes(int64_t *bytes_needed, const cilqr_params *p, int B, int n_obs)
+{
+    if (!bytes_needed || !p || B < 0 || n_obs < 0) return fail(CILQR_E_ARG, "bad argument");
+    *bytes_needed = (int64_t)kStaticCtlBytes + (int64_t)B * n_obs * (CV_FIELDS + p->horizon) * (int64_t)sizeof(double);
+    return 0;
+}
+
+int cilqr_solve_cv_static(cilqr_handle h, int B, int n_obs, const double *state0, const double *LW, const double *sigma, double kappa,
+                          const double *x0, double *U, const double *poly, const double *xlp, double *X, double *J, int32_t *iters,
+                          int32_t *status, void *stream)
+{
+    if (!h) return fail(CILQR_E_ARG, "null handle");
+    if (B < 0 || n_obs < 0) return fail(CILQR_E_ARG, "B and n_obs must be >= 0");
+    if (!x0 || !U || !poly || !xlp) return fail(CILQR_E_ARG, "null argument");
+    if (n_obs > 0 && (!state0 || !LW || !sigma)) return fail(CILQR_E_ARG, "null obstacle arrays");
+    if (B == 0) return 0;
+    const DevParams &P = h->dp;
+    const int N = P.N;
+    const size_t n_bj = (size_t)B * n_obs;
+    const size_t need = kStaticCtlBytes + n_bj * (CV_FIELDS + N) * sizeof(double);
+    if (need > kStaticScratchBytes)
+        return fail(CILQR_E_ARG, "cilqr_solve_cv_static: %d scenarios x %d obstacles x horizon %d need %zu bytes of scratch, the static array has %zu "
+                                 "(CILQR_STATIC_SCRATCH_BYTES); use cilqr_set_obstacles_cv + cilqr_solve_batch", B, n_obs, N, need, kStaticScratchBytes);
+    if (h->fused_slots_max < 1) return fail(CILQR_E_ARG, "horizon %d is too long for the fused solve kernel's shared memory", N);
+    DeviceScope scope(h->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    unsigned char *scratch = nullptr;
+    if (int rc = static_scratch_address(h->device, &scratch)) return rc;
+    double *ocv = reinterpret_cast<double *>(scratch + kStaticCtlBytes), *oib2 = ocv + n_bj * CV_FIELDS;
+    // the array keeps the last call's contents: the control block must start at zero; the obstacle records are rewritten whole
+    CILQR_CUDA(cudaMemsetAsync(scratch, 0, kStaticCtlBytes, st));
+    if (n_bj > 0) {
+        prep_obstacles_cv_kernel<<<prep_grid(n_bj, h->num_sms), 256, 0, st>>>(P, n_bj, state0, LW, sigma, kappa, ocv);
+        CILQR_LAUNCH_CHECK();
+        prep_obstacles_cv_ib2_kernel<<<prep_grid(n_bj * N, h->num_sms), 256, 0, st>>>(P, n_bj, LW, sigma, kappa, ocv, oib2);
+        CILQR_LAUNCH_CHECK();
+    }
+    FusedArgs F;
+    F.P = P;
+    F.B = B;
+    F.G = std::max(1, std::min(h->fused_slots_max, (B + 2 * h->num_sms - 1) / (2 * h->num_sms)));
+    F.x0 = x0;
+    F.poly = poly;
+    F.xlp = xlp;
+    F.U = U;
+    F.X = X;
+    F.J = J;
+    F.iters = iters;
+    F.status = status;
+    F.n_obs = n_obs;
+    F.ocv = ocv;
+    F.oib2 = oib2;
+    F.orec = nullptr;
+    F.counter = reinterpret_cast<int *>(scratch);
+    F.stats = reinterpret_cast<unsigned long long *>(scratch + 64);
+    const size_t smem = fused_smem_bytes(N, F.G);
+    int occ = 0;
+    CILQR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fused_solve_kernel<true>, kFusedThreads, smem));
+    if (occ < 1) return fail(CILQR_E_CUDA, "fused solve kernel does not fit on an SM (%zu B of shared memory)", smem);
+    const int grid = std::max(1, std::min((B + F.G - 1) / F.G, h->num_sms * occ));
+    fused_solve_kernel<true><<<grid, kFusedThreads, smem, st>>>(F);
+    CILQR_LAUNCH_CHECK();
+    return 0;
+}
+
 } // extern "C"

@@ -334,6 +334,22 @@ class iLQR:
         self.X_result, self.U_result, self.J_result, self.iterations, self.status = X, Uarr, J, it, stt
         return Uarr
 
+    def solve_cv_static(self, state0, LW, sigma, kappa, x_0, U, poly_coeffs, x_local_plan, outputs):
+        """cilqr_solve_cv_static: set_obstacles_cv + get_optimal_control_seq (n_alphas = 1) in one call that allocates nothing —
+        torch CUDA tensors only, results into the preallocated `outputs` ("X", "J", "iters", "status"; any may be missing), U
+        in place.  Scratch is the library's static 16 MiB array: overlapping calls on one GPU race."""
+        import torch
+        a = _Arg()
+        B, n = int(x_0.shape[0]), int(state0.shape[1]) if state0 is not None else 0
+        ps, pl, pg = (a.inp(state0), a.inp(LW), a.inp(sigma)) if n else (None, None, None)
+        px, pU, pp, pxl = a.inp(x_0), a.inp(U), a.inp(poly_coeffs), a.inp(x_local_plan)
+        po = {k: a.inp(outputs[k], np.int32 if k in ("iters", "status") else np.float64) if k in outputs else None for k in ("X", "J", "iters", "status")}
+        if a.mem != MEM_DEVICE:
+            raise ValueError("solve_cv_static takes torch CUDA tensors only")
+        _check(self.lib.cilqr_solve_cv_static(self._h, C.c_int(B), C.c_int(n), ps, pl, pg, C.c_double(kappa), px, pU, pp, pxl, po["X"], po["J"],
+                                              po["iters"], po["status"], C.c_void_p(torch.cuda.current_stream().cuda_stream)))
+        return U
+
     def solve_stats(self):
         """(cost passes, derivative + backward/forward passes, rounds with work) of the last n_alphas == 1 solve, summed
         over the batch; synchronises the current stream."""
