@@ -88,9 +88,11 @@ def traffic(path):
     for r in rows[1:]:
         if not r[mi].startswith("dram__bytes"):
             continue
-        k = per.setdefault(r[ii], [r[ki].split("(")[0].replace("void ", ""), 0.0])
+        k = per.setdefault(r[ii], [r[ki].split("(")[0].replace("void ", ""), 0.0, r[h.index("Grid Size")]])
         k[1] += float(r[vi].replace(",", "")) * scale.get(r[ui], 1.0)
     seq = list(per.values())
+    grids = [g for _, _, g in seq]
+    seq = [(k, v) for k, v, _ in seq]
     starts = [i for i, (k, _) in enumerate(seq) if k.startswith("prep_obstacles_cv_kernel")]
     out = {}
     if starts:
@@ -103,10 +105,18 @@ def traffic(path):
         out["solver_dram_bytes_by_kernel"] = {}
         for k, v in step:
             out["solver_dram_bytes_by_kernel"][k] = out["solver_dram_bytes_by_kernel"].get(k, 0.0) + v
-    warp = [v for k, v in seq if k.startswith("warp_")]
-    if warp:
-        out["warp_dram_bytes_per_launch"] = sum(warp) / len(warp)
-        out["warp_launches"] = len(warp)
+    # costmap warp (float value + index map): per launch, by target edge T — the grid is ((T / 64)^2 tiles, poses)
+    by_t = collections.OrderedDict()
+    for (k, v), g in zip(seq, grids):
+        if k.startswith("warp_tma_kernel") or k.startswith("warp_direct_kernel"):
+            tiles = int(g.strip("()").split(",")[0])
+            by_t.setdefault(64 * int(round(tiles ** 0.5)), []).append(v)
+    for t, vs in by_t.items():
+        vs = vs[len(vs) // 2:]  # the second half of a size's launches are the value + index passes (bench_warp's order)
+        out["warp_dram_bytes_per_launch_T%d" % t] = sum(vs) / len(vs)
+    fused = [v for k, v in seq if k.startswith("fused_solve_kernel")]
+    if fused:
+        out["fused_solve_dram_bytes_per_launch"] = sum(fused) / len(fused)
     print(json.dumps(out, indent=1))
 
 
