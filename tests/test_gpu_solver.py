@@ -123,13 +123,16 @@ def test_batched_solve_matches_checker(checker, n_obs, curved, first):
     s.close()
 
 
+@pytest.mark.parametrize("fused", [1, 0])
 @pytest.mark.parametrize("merit", [0, 1])
-def test_line_search_matches_port(port, merit):
-    """n_alphas = 8 (extension): parity with the plain-C port, which test_oracle_golden pins on reference functions."""
+def test_line_search_matches_port(port, merit, fused):
+    """n_alphas = 8 (extension): parity with the plain-C port, which test_oracle_golden pins on reference functions — on the fused
+    on-chip kernel (cilqr_fused_ls.cuh) and on the round kernels."""
     p = port.params_default(horizon=50)
     B, n_obs = 24, 10
     sc = scenarios.make_scenarios(p, 9000, B, n_obs, curved=True)
     s = make_solver(p, sc, B, n_obs)
+    s.set_option(cilqr_b200.OPT_FUSED, fused)
     U = sc["U0"].copy()
     s.get_optimal_control_seq(sc["x0"], U, sc["poly"], sc["xlp"], n_alphas=8, merit=merit)
     r = port.solve_batch(p, B, n_obs, sc["dim"], sc["pos"], sc["x0"], sc["U0"], sc["poly"], sc["xlp"], n_alphas=8, merit=merit)
@@ -182,6 +185,38 @@ def test_config3_at_size_matches_reference_functions(checker, port, merit):
     print("config 3 (merit %d): %d of %d scenarios checked, worst relative difference %.3g, status histogram of the batch %s, mean iterations %.2f"
           % (merit, sel.size, B, worst, hist.tolist(), float(ih.mean())))
     s.close()
+
+
+@pytest.mark.parametrize("B,n_obs,cv,na,merit", [(333, 6, True, 8, 1), (97, 3, False, 4, 0), (50, 0, True, 2, 1), (1000, 10, True, 8, 0)])
+def test_line_search_fused_kernel_against_the_round_kernels(B, n_obs, cv, na, merit):
+    """The two schedules of the line-search extension on the same inputs: equal iteration counts and status, U*, X*, J within 1e-9
+    (they call the same device functions; whether the compiler contracts every expression identically in both kernels is not
+    relied upon), with automatic and with 3 slots per CTA (slots refilled many times)."""
+    import torch
+    p = cilqr_b200.Parameters()
+    cilqr_b200.load_library().cilqr_params_default(__import__("ctypes").byref(p))
+    p = p.replace(horizon=50)
+    sc = scenarios.make_scenarios(p, 31337, B, n_obs, curved=True, dense=not cv)
+    dev = torch.device("cuda:0")
+    keys = ("x0", "U0", "poly", "xlp") + ((("obs_state0", "obs_LW", "obs_sigma") if cv else ("dim", "pos")) if n_obs else ())
+    t = {k: torch.from_numpy(sc[k]).to(dev) for k in keys}
+    res = []
+    for fused, slots in [(0, 0), (1, 0), (1, 3)]:
+        s = cilqr_b200.iLQR(p, max_batch=B, max_obs=max(n_obs, 1), options={cilqr_b200.OPT_FUSED: fused, cilqr_b200.OPT_FUSED_SLOTS: slots})
+        if n_obs:
+            if cv:
+                s.set_obstacles_cv(t["obs_state0"], t["obs_LW"], t["obs_sigma"], sc["kappa"])
+            else:
+                s.set_obstacles_dense(t["dim"], t["pos"])
+        U = t["U0"].clone()
+        s.get_optimal_control_seq(t["x0"], U, t["poly"], t["xlp"], n_alphas=na, merit=merit)
+        torch.cuda.synchronize()
+        res.append((U.cpu().numpy(), s.X_result.cpu().numpy(), s.J_result.cpu().numpy(), s.iterations.cpu().numpy(), s.status.cpu().numpy()))
+        s.close()
+    for got in res[1:]:
+        assert np.array_equal(got[3], res[0][3]) and np.array_equal(got[4], res[0][4])
+        for b in range(B):
+            assert rel(got[0][b], res[0][0][b]) < TOL and rel(got[1][b], res[0][1][b]) < TOL and abs(got[2][b] - res[0][2][b]) <= TOL * abs(res[0][2][b]), b
 
 
 def test_covariance_inflated_obstacles_on_device_match_host_expansion(checker):

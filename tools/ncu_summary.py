@@ -88,7 +88,7 @@ def traffic(path):
     for r in rows[1:]:
         if not r[mi].startswith("dram__bytes"):
             continue
-        k = per.setdefault(r[ii], [r[ki].split("(")[0].replace("void ", ""), 0.0, r[h.index("Grid Size")]])
+        k = per.setdefault(r[ii], [r[ki].split("(")[0].replace("void ", "").replace("cilqr::", ""), 0.0, r[h.index("Grid Size")]])
         k[1] += float(r[vi].replace(",", "")) * scale.get(r[ui], 1.0)
     seq = list(per.values())
     grids = [g for _, _, g in seq]

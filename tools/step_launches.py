@@ -15,7 +15,7 @@ def main():
     h = rows[0]
     ki, vi, gi = h.index("Kernel Name"), h.index("Metric Value"), h.index("Grid Size")
     mi = h.index("Metric Name")
-    seq = [(r[ki].split("(")[0].replace("void ", ""), float(r[vi]) / 1e3, r[gi]) for r in rows[1:] if r[mi] == "gpu__time_duration.sum"]
+    seq = [(r[ki].split("(")[0].replace("void ", "").replace("cilqr::", ""), float(r[vi]) / 1e3, r[gi]) for r in rows[1:] if r[mi] == "gpu__time_duration.sum"]
     idx = [i for i, (k, _, _) in enumerate(seq) if k.startswith(first)]
     start = idx[-1] if idx else 0
     tot, agg = 0.0, {}

@@ -141,9 +141,9 @@ __device__ __forceinline__ void fused_derivs_item(const DevParams &P, const Fuse
     st2(r + S_R + 8, luu0, luu1);
 }
 
-// Phase D for one slot: iLQR::backward_pass (iLQR.cpp:91-195) then iLQR::forward_pass (iLQR.cpp:68-86), full step, in place —
-// the arithmetic of batch_sweep_kernel on shared-memory records.  Returns false on the reference's `return false` path.
-__device__ __forceinline__ bool fused_sweep_slot(const DevParams &P, double *__restrict__ rec, double lamb)
+// iLQR::backward_pass (iLQR.cpp:91-195) for one slot: the gains overwrite the derivative records.  Returns false on the
+// reference's `return false` path.
+__device__ __forceinline__ bool fused_backward_slot(const DevParams &P, double *__restrict__ rec, double lamb)
 {
     const int N = P.N;
     RiccatiState S;
@@ -173,7 +173,15 @@ __device__ __forceinline__ bool fused_sweep_slot(const DevParams &P, double *__r
             st2(r + S_R + f, g[f], g[f + 1]);
         I.v = vt.x; I.c = cs.x; I.s = cs.y;
     }
-    if (!finite)
+    return finite;
+}
+
+// Phase D for one slot: iLQR::backward_pass then iLQR::forward_pass (iLQR.cpp:68-86), full step, in place — the arithmetic of
+// batch_sweep_kernel on shared-memory records.  Returns false on the reference's `return false` path.
+__device__ __forceinline__ bool fused_sweep_slot(const DevParams &P, double *__restrict__ rec, double lamb)
+{
+    const int N = P.N;
+    if (!fused_backward_slot(P, rec, lamb))
         return false;
     double n0, n1, n2, n3, c, s, o0, o1, o2, o3;
     {

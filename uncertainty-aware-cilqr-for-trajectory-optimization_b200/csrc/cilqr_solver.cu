@@ -12,6 +12,7 @@
 #include "cilqr_device.cuh"
 #include "cilqr_batch.cuh"
 #include "cilqr_fused.cuh"
+#include "cilqr_fused_ls.cuh"
 #include <cfloat>
 #include <cmath>
 #include <cstdlib>
@@ -462,6 +463,8 @@ static int raise_smem_limits(int dev, int optin)
     CILQR_CUDA(cudaFuncSetAttribute(ls_candidates_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
     CILQR_CUDA(cudaFuncSetAttribute(fused_solve_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
     CILQR_CUDA(cudaFuncSetAttribute(fused_solve_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
+    CILQR_CUDA(cudaFuncSetAttribute(fused_ls_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
+    CILQR_CUDA(cudaFuncSetAttribute(fused_ls_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
     done.push_back(dev);
     return 0;
 }
@@ -684,6 +687,10 @@ static int need_obstacles(cilqr_handle h, int B)
 // latency-bound (a sweep over a few thousand scenarios takes as long as the dependent chain of one thread), so the chunks'
 // sweeps, cost and derivative kernels overlap each other; (2) with host buffers each chunk's host->device copies, rounds and
 // device->host copies form a pipeline, so PCIe transfers run under the other chunks' kernels.
+// Compute token (cilqr_set_compute_token; host buffers): several handles driven from several host threads would otherwise
+// interleave their kernels on the GPU — every solve takes longer and all of them finish, and copy their results back, at about
+// the same time.  With the token the solves' kernels run one handle after the other at full speed, and a handle's host<->device
+// copies run under the other handles' kernels (solve_rounds).
 static std::mutex g_compute_token;
 
 struct HostIO { // caller's host arrays (CILQR_MEM_HOST) — null members when the caller's buffers are device memory
@@ -722,12 +729,6 @@ static int issue_rounds(cilqr_handle h, const SolveArgs &A, const HostIO *io, cu
     const double *ocv = h->obs_b.as<double>(), *oib2 = ocv ? ocv + (size_t)B * n_obs * CV_FIELDS : nullptr, *orec = h->obs.as<double>();
     const size_t trace_per_chunk = (size_t)n_cnt * kTraceKinds * 2;
     if (h->trace_on) CILQR_CUDA(cudaMemsetAsync(h->trace.p, 0xff, (size_t)kMaxChunks * trace_per_chunk * sizeof(unsigned long long), st));
-    // Compute token (host buffers, one chunk, direct launches): several handles driven from several host threads would otherwise
-    // interleave their kernels on the GPU — every solve takes longer and all of them finish, and copy their results back,
-    // at about the same time.  With the token the solves' kernels run one handle after the other at full speed, and a handle's
-    // host<->device copies run under the other handles' kernels.
-    const bool token = io && K == 1 && h->exclusive == 1;
-    std::unique_lock<std::mutex> compute_token(g_compute_token, std::defer_lock);
     cudaStream_t cs[kMaxChunks];
     if (K == 1) {
         cs[0] = st;
@@ -768,11 +769,6 @@ static int issue_rounds(cilqr_handle h, const SolveArgs &A, const HostIO *io, cu
             CILQR_CUDA(cudaMemcpyAsync(A.U + 2 * N * so, io->U_in + 2 * N * so, sb * 2 * N * sizeof(double), cudaMemcpyHostToDevice, cs[c]));
             CILQR_CUDA(cudaMemcpyAsync(const_cast<double *>(A.poly) + P.npoly * so, io->poly + P.npoly * so, sb * P.npoly * sizeof(double), cudaMemcpyHostToDevice, cs[c]));
             CILQR_CUDA(cudaMemcpyAsync(const_cast<double *>(A.xlp) + 2 * so, io->xlp + 2 * so, sb * 2 * sizeof(double), cudaMemcpyHostToDevice, cs[c]));
-        }
-        if (token) { // inputs are on the device before the token is taken: the copy runs under another handle's kernels
-            CILQR_CUDA(cudaEventRecord(h->ev_in, cs[c]));
-            CILQR_CUDA(cudaEventSynchronize(h->ev_in));
-            compute_token.lock();
         }
         CILQR_CUDA(cudaMemsetAsync(ctl, 0, ctl_stride(n_cnt), cs[c]));
         FusedArgs F;
@@ -821,7 +817,6 @@ static int issue_rounds(cilqr_handle h, const SolveArgs &A, const HostIO *io, cu
                 P, v, b, F.U, F.X, F.J, F.iters, F.status);
             CILQR_LAUNCH_CHECK();
         }
-        if (token) CILQR_CUDA(cudaEventRecord(h->ev_kdone, cs[c]));
         if (io) { // this chunk's results: staging -> host
             CILQR_CUDA(cudaMemcpyAsync(io->U + 2 * N * so, A.U + 2 * N * so, sb * 2 * N * sizeof(double), cudaMemcpyDeviceToHost, cs[c]));
             if (io->X) CILQR_CUDA(cudaMemcpyAsync(io->X + 4 * (N + 1) * so, A.X + 4 * (N + 1) * so, sb * 4 * (N + 1) * sizeof(double), cudaMemcpyDeviceToHost, cs[c]));
@@ -832,10 +827,6 @@ static int issue_rounds(cilqr_handle h, const SolveArgs &A, const HostIO *io, cu
         if (K > 1) {
             CILQR_CUDA(cudaEventRecord(h->ev_join[c], cs[c]));
             CILQR_CUDA(cudaStreamWaitEvent(st, h->ev_join[c], 0));
-        }
-        if (token) { // the kernels are done: the next handle may start while this one's results travel back
-            CILQR_CUDA(cudaEventSynchronize(h->ev_kdone));
-            compute_token.unlock();
         }
     }
     return 0;
@@ -863,6 +854,52 @@ static void drop_graph(cilqr_handle h)
 // benchmark) records its whole multi-stream sequence of copies and launches once as a CUDA graph and replays it with a single
 // launch afterwards (the round kernels are ~60 launches per chunk, most of them a few microseconds long); anything else is
 // issued directly.
+static int run_plan(cilqr_handle h, const SolveArgs &A, const HostIO *io, cudaStream_t st, const SolvePlan &plan, const std::vector<uintptr_t> &key)
+{
+    const int K = plan.K;
+    if (h->graph_exec && key == h->graph_key) {
+        CILQR_CUDA(cudaGraphLaunch(h->graph_exec, st));
+        g_launches.fetch_add(h->graph_kernels, std::memory_order_relaxed);
+        return 0;
+    }
+    // a graph pays for itself when there is more than one launch to replay: several chunks, or round kernels
+    bool record = h->use_graph && key == h->seen_key && (K > 1 || plan.r0 > 0 || io); // second call in a row with these arguments
+    h->seen_key = key;
+    if (record && io)
+        record = pinned_or_null(io->x0) && pinned_or_null(io->U) && pinned_or_null(io->poly) && pinned_or_null(io->xlp) && pinned_or_null(io->X) &&
+                 pinned_or_null(io->J) && pinned_or_null(io->iters) && pinned_or_null(io->status); // pageable copies are not recorded
+    if (!record) return issue_rounds(h, A, io, st, plan);
+
+    drop_graph(h);
+    const long long before = g_launches.load(std::memory_order_relaxed);
+    CILQR_CUDA(cudaStreamBeginCapture(h->cap_stream, cudaStreamCaptureModeRelaxed));
+    const int rc = issue_rounds(h, A, io, h->cap_stream, plan);
+    cudaGraph_t g = nullptr;
+    const cudaError_t e = cudaStreamEndCapture(h->cap_stream, &g);
+    const long long recorded = g_launches.load(std::memory_order_relaxed) - before;
+    g_launches.fetch_sub(recorded, std::memory_order_relaxed); // nothing has run yet
+    if (rc != 0 || e != cudaSuccess || !g) {
+        if (g) cudaGraphDestroy(g);
+        cudaGetLastError();
+        h->use_graph = false; // do not try again on this handle
+        if (rc != 0) return rc;
+        return issue_rounds(h, A, io, st, plan);
+    }
+    const cudaError_t ei = cudaGraphInstantiate(&h->graph_exec, g, 0);
+    cudaGraphDestroy(g);
+    if (ei != cudaSuccess) {
+        cudaGetLastError();
+        h->graph_exec = nullptr;
+        h->use_graph = false;
+        return issue_rounds(h, A, io, st, plan);
+    }
+    h->graph_key = key;
+    h->graph_kernels = recorded;
+    CILQR_CUDA(cudaGraphLaunch(h->graph_exec, st));
+    g_launches.fetch_add(h->graph_kernels, std::memory_order_relaxed);
+    return 0;
+}
+
 static int solve_rounds(cilqr_handle h, const SolveArgs &A, const HostIO *io, cudaStream_t st)
 {
     const DevParams &P = h->dp;
@@ -918,52 +955,39 @@ static int solve_rounds(cilqr_handle h, const SolveArgs &A, const HostIO *io, cu
         for (const void *q : {(const void *)io->x0, (const void *)io->U, (const void *)io->poly, (const void *)io->xlp, (const void *)io->X,
                               (const void *)io->J, (const void *)io->iters, (const void *)io->status})
             key.push_back((uintptr_t)q);
-    if (io && h->exclusive == 1) { // the token is taken and released by host code between the launches: no graph
+    if (io && h->exclusive == 1) {
+        // Compute token: the copies are issued by host code either side of the token, the KERNELS of the solve between lock and
+        // unlock go through run_plan without the host arrays — a repeated call replays them as one recorded graph (one launch
+        // instead of ~64 direct ones issued while the other handles' threads are inside the CUDA API; the staging buffers are the
+        // same from call to call even when the caller's host arrays are not).
         if (!h->ev_in) CILQR_CUDA(cudaEventCreateWithFlags(&h->ev_in, cudaEventDisableTiming));
         if (!h->ev_kdone) CILQR_CUDA(cudaEventCreateWithFlags(&h->ev_kdone, cudaEventDisableTiming));
-        return issue_rounds(h, A, io, st, plan);
+        const size_t sb = (size_t)B;
+        CILQR_CUDA(cudaMemcpyAsync(const_cast<double *>(A.x0), io->x0, sb * 4 * sizeof(double), cudaMemcpyHostToDevice, st));
+        CILQR_CUDA(cudaMemcpyAsync(A.U, io->U_in, sb * 2 * N * sizeof(double), cudaMemcpyHostToDevice, st));
+        CILQR_CUDA(cudaMemcpyAsync(const_cast<double *>(A.poly), io->poly, sb * P.npoly * sizeof(double), cudaMemcpyHostToDevice, st));
+        CILQR_CUDA(cudaMemcpyAsync(const_cast<double *>(A.xlp), io->xlp, sb * 2 * sizeof(double), cudaMemcpyHostToDevice, st));
+        CILQR_CUDA(cudaEventRecord(h->ev_in, st));
+        CILQR_CUDA(cudaEventSynchronize(h->ev_in)); // inputs are on the device before the token is taken: the copy ran under another handle's kernels
+        std::vector<uintptr_t> kkey(key.begin(), key.begin() + 19);
+        kkey.push_back(1); // (kernels only)
+        int rc;
+        {
+            std::lock_guard<std::mutex> compute_token(g_compute_token);
+            rc = run_plan(h, A, nullptr, st, plan, kkey);
+            if (rc == 0) {
+                CILQR_CUDA(cudaEventRecord(h->ev_kdone, st));
+                CILQR_CUDA(cudaMemcpyAsync(io->U, A.U, sb * 2 * N * sizeof(double), cudaMemcpyDeviceToHost, st));
+                if (io->X) CILQR_CUDA(cudaMemcpyAsync(io->X, A.X, sb * 4 * (N + 1) * sizeof(double), cudaMemcpyDeviceToHost, st));
+                if (io->J) CILQR_CUDA(cudaMemcpyAsync(io->J, A.J, sb * sizeof(double), cudaMemcpyDeviceToHost, st));
+                if (io->iters) CILQR_CUDA(cudaMemcpyAsync(io->iters, A.iters, sb * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+                if (io->status) CILQR_CUDA(cudaMemcpyAsync(io->status, A.status, sb * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+                CILQR_CUDA(cudaEventSynchronize(h->ev_kdone)); // the kernels are done: the next handle may start while this one's results travel back
+            }
+        }
+        return rc;
     }
-    if (h->graph_exec && key == h->graph_key) {
-        CILQR_CUDA(cudaGraphLaunch(h->graph_exec, st));
-        g_launches.fetch_add(h->graph_kernels, std::memory_order_relaxed);
-        return 0;
-    }
-    // a graph pays for itself when there is more than one launch to replay: several chunks, or round kernels
-    bool record = h->use_graph && key == h->seen_key && (K > 1 || plan.r0 > 0 || io); // second call in a row with these arguments
-    h->seen_key = key;
-    if (record && io)
-        record = pinned_or_null(io->x0) && pinned_or_null(io->U) && pinned_or_null(io->poly) && pinned_or_null(io->xlp) && pinned_or_null(io->X) &&
-                 pinned_or_null(io->J) && pinned_or_null(io->iters) && pinned_or_null(io->status); // pageable copies are not recorded
-    if (!record) return issue_rounds(h, A, io, st, plan);
-
-    drop_graph(h);
-    const long long before = g_launches.load(std::memory_order_relaxed);
-    CILQR_CUDA(cudaStreamBeginCapture(h->cap_stream, cudaStreamCaptureModeRelaxed));
-    const int rc = issue_rounds(h, A, io, h->cap_stream, plan);
-    cudaGraph_t g = nullptr;
-    const cudaError_t e = cudaStreamEndCapture(h->cap_stream, &g);
-    const long long recorded = g_launches.load(std::memory_order_relaxed) - before;
-    g_launches.fetch_sub(recorded, std::memory_order_relaxed); // nothing has run yet
-    if (rc != 0 || e != cudaSuccess || !g) {
-        if (g) cudaGraphDestroy(g);
-        cudaGetLastError();
-        h->use_graph = false; // do not try again on this handle
-        if (rc != 0) return rc;
-        return issue_rounds(h, A, io, st, plan);
-    }
-    const cudaError_t ei = cudaGraphInstantiate(&h->graph_exec, g, 0);
-    cudaGraphDestroy(g);
-    if (ei != cudaSuccess) {
-        cudaGetLastError();
-        h->graph_exec = nullptr;
-        h->use_graph = false;
-        return issue_rounds(h, A, io, st, plan);
-    }
-    h->graph_key = key;
-    h->graph_kernels = recorded;
-    CILQR_CUDA(cudaGraphLaunch(h->graph_exec, st));
-    g_launches.fetch_add(h->graph_kernels, std::memory_order_relaxed);
-    return 0;
+    return run_plan(h, A, io, st, plan, key);
 }
 
 // Line-search extension (n_alphas > 1) as rounds: cost (tracking gradient + list compaction) -> derivatives -> backward sweep ->
@@ -1065,6 +1089,62 @@ static int solve_rounds_ls(cilqr_handle h, const SolveArgs &A, cudaStream_t st)
     const size_t out_items = (size_t)B * (N + 1);
     batch_output_kernel<<<(int)std::min<size_t>((out_items + 255) / 256, (size_t)h->num_sms * 8), 256, 0, st>>>(P, v, B, A.U, A.X, A.J, A.iters,
                                                                                                                 A.status);
+    CILQR_LAUNCH_CHECK();
+    return 0;
+}
+
+// Line-search extension on chip (cilqr_fused_ls.cuh): one launch per solve; candidates and the shorter steps' merit terms in an
+// L2-resident scratch (per CTA: G x n_alphas x (N + 1) x 64 B + G x n_alphas x N x 8 B).
+static int solve_fused_ls(cilqr_handle h, const SolveArgs &A, cudaStream_t st)
+{
+    const DevParams &P = h->dp;
+    const int N = P.N, B = A.B, na = A.n_alphas, n_cnt = P.max_iter + 3;
+    int G = h->fused_slots > 0 ? std::min(h->fused_slots, h->fused_slots_max) : h->fused_slots_max;
+    if (h->fused_slots == 0) G = std::max(1, std::min(G, (B + 2 * h->num_sms - 1) / (2 * h->num_sms)));
+    while (G > 1 && 2 * (fused_ls_smem_bytes(N, G) + 1024) > (size_t)h->smem_per_sm && fused_ls_smem_bytes(N, G) > fused_smem_bytes(N, h->fused_slots_max)) --G;
+    const size_t smem = fused_ls_smem_bytes(N, G);
+    int occ = 0;
+    if (h->obs_cv)
+        CILQR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fused_ls_kernel<true>, kFusedThreads, smem));
+    else
+        CILQR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fused_ls_kernel<false>, kFusedThreads, smem));
+    if (occ < 1) return fail(CILQR_E_CUDA, "fused line-search kernel does not fit on an SM (%zu B of shared memory)", smem);
+    const int grid = std::max(1, std::min((B + G - 1) / G, h->num_sms * occ));
+    const size_t n_cand = (size_t)grid * fused_ls_cand_doubles(N, G, na), n_merit = (size_t)grid * fused_ls_merit_doubles(N, G, na);
+    if (int rc = h->scratch.reserve((n_cand + n_merit) * sizeof(double))) return rc;
+    if (int rc = h->ctl.reserve((size_t)kMaxChunks * ctl_stride(n_cnt))) return rc;
+    h->last_chunks = 1;
+    h->last_r0 = 0;
+    drop_graph(h);
+    h->seen_key.clear();
+    unsigned char *ctl = h->ctl.as<unsigned char>();
+    CILQR_CUDA(cudaMemsetAsync(ctl, 0, ctl_stride(n_cnt), st));
+    FusedLsArgs F;
+    F.P = P;
+    F.B = B;
+    F.G = G;
+    F.x0 = A.x0;
+    F.poly = A.poly;
+    F.xlp = A.xlp;
+    F.U = A.U;
+    F.X = A.X;
+    F.J = A.J;
+    F.iters = A.iters;
+    F.status = A.status;
+    F.n_obs = h->cur_nobs;
+    F.ocv = h->obs_b.as<double>();
+    F.oib2 = F.ocv ? F.ocv + (size_t)B * h->cur_nobs * CV_FIELDS : nullptr;
+    F.orec = h->obs.as<double>();
+    F.counter = reinterpret_cast<int *>(ctl) + n_cnt;
+    F.stats = reinterpret_cast<unsigned long long *>(ctl + ctl_ints(n_cnt) * sizeof(int));
+    F.n_alphas = na;
+    F.merit_total = A.merit == CILQR_MERIT_TOTAL;
+    F.cand = h->scratch.as<double>();
+    F.gmerit = F.cand + n_cand;
+    if (h->obs_cv)
+        fused_ls_kernel<true><<<grid, kFusedThreads, smem, st>>>(F);
+    else
+        fused_ls_kernel<false><<<grid, kFusedThreads, smem, st>>>(F);
     CILQR_LAUNCH_CHECK();
     return 0;
 }
@@ -1185,7 +1265,9 @@ int cilqr_solve_batch(cilqr_handle h, int B, const double *x0, double *U, const 
     if (!h->obs_cv && h->cur_nobs > 0) {
         if (int rc = ensure_records(h, st)) return rc;
     }
-    if (int rc = solve_rounds_ls(h, A, st)) return rc;
+    // small batches on chip (one launch), large ones as rounds; CILQR_OPT_FUSED forces the choice
+    const bool ls_fused = h->fused_slots_max >= 1 && (h->fused_from >= 0 ? h->fused_from != 0 : B <= 16384);
+    if (int rc = ls_fused ? solve_fused_ls(h, A, st) : solve_rounds_ls(h, A, st)) return rc;
     if (int rc = fetch_out(U, A.U, (size_t)B * 2 * N, mem, st)) return rc;
     if (int rc = fetch_out(X, A.X, (size_t)B * 4 * (N + 1), mem, st)) return rc;
     if (int rc = fetch_out(J, A.J, (size_t)B, mem, st)) return rc;
