@@ -146,6 +146,12 @@ __global__ void __launch_bounds__(kFusedThreads, 2) fused_ls_kernel(const __grid
     bool exhausted = false; // per warp: the counter has run past the batch
     unsigned long long n_cost = 0, n_deriv = 0, n_iter = 0; // thread 0's tallies
     __syncthreads();
+#ifdef CILQR_FUSED_PROFILE
+    long long pc[12] = {0}, pt = clock64();
+#define LS_TICK(i) do { if (tid == 0) { const long long now = clock64(); pc[i] += now - pt; pt = now; } } while (0)
+#else
+#define LS_TICK(i) do { } while (0)
+#endif
 
     for (;;) {
         // ------------------------------------------------------------------ A: tracking gradient; J of finished slots, merit of fresh nominals
@@ -172,6 +178,7 @@ __global__ void __launch_bounds__(kFusedThreads, 2) fused_ls_kernel(const __grid
             st2(r + S_R + 2, 2.0 * P.w_vel * ev, 0.0);
         }
         __syncthreads();
+        LS_TICK(0);
         // ------------------------------------------------------------------ B: J = get_J(X_result, U_result); J_cur of fresh slots
         if (warp == 0) {
             bool iterating = false;
@@ -195,6 +202,7 @@ __global__ void __launch_bounds__(kFusedThreads, 2) fused_ls_kernel(const __grid
             }
         }
         __syncthreads();
+        LS_TICK(1);
         // ------------------------------------------------------------------ C: derivatives
         const unsigned am = ctl[0];
         const int n_a = __popc(am);
@@ -209,6 +217,7 @@ __global__ void __launch_bounds__(kFusedThreads, 2) fused_ls_kernel(const __grid
             n_iter += 1;
         }
         __syncthreads();
+        LS_TICK(2);
         // ------------------------------------------------------------------ D: backward pass (warp 0) | retire, refill, rollout (other warps)
         if (warp == 0) {
             bool finite = false;
@@ -324,6 +333,7 @@ __global__ void __launch_bounds__(kFusedThreads, 2) fused_ls_kernel(const __grid
             }
         }
         __syncthreads();
+        LS_TICK(3);
         // ------------------------------------------------------------------ E: every step length rolled out, lane = (slot, alpha)
         const unsigned rm = ctl[1];
         const int n_r = __popc(rm);
@@ -333,6 +343,7 @@ __global__ void __launch_bounds__(kFusedThreads, 2) fused_ls_kernel(const __grid
             fused_ls_rollout(P, rec + s * slot_stride, ldexp(1.0, -a), cand_of(s, a));
         }
         __syncthreads();
+        LS_TICK(4);
         // ------------------------------------------------------------------ F1 / G1: the full step, accepted at once when it improves
         for (int idx = tid; idx < n_r * N; idx += kFusedThreads) {
             const int k = idx / N, t = idx - k * N;
@@ -340,6 +351,7 @@ __global__ void __launch_bounds__(kFusedThreads, 2) fused_ls_kernel(const __grid
             sJ[s * N + t] = fused_ls_merit_term<CV>(P, A, H[s], t, cand_of(s, 0) + (size_t)t * kCandD, merit_total);
         }
         __syncthreads();
+        LS_TICK(5);
         if (warp == 0) {
             bool retry = false;
             if (lane < G && ((rm >> lane) & 1u)) {
@@ -358,6 +370,7 @@ __global__ void __launch_bounds__(kFusedThreads, 2) fused_ls_kernel(const __grid
                 ctl[2] = m;
         }
         __syncthreads();
+        LS_TICK(6);
         // ------------------------------------------------------------------ F2 / G2: the shorter steps of the slots that need them
         const unsigned tm = ctl[2];
         const int n_t = __popc(tm);
@@ -369,6 +382,7 @@ __global__ void __launch_bounds__(kFusedThreads, 2) fused_ls_kernel(const __grid
                 gmerit[((size_t)s * NA + a) * N + t] = fused_ls_merit_term<CV>(P, A, H[s], t, cand_of(s, a) + (size_t)t * kCandD, merit_total);
             }
             __syncthreads();
+        LS_TICK(7);
             for (int k = warp; k < n_t; k += kFusedWarps) {
                 const int s = __fns(tm, 0, k + 1);
                 SlotHdr &h = H[s];
@@ -388,6 +402,7 @@ __global__ void __launch_bounds__(kFusedThreads, 2) fused_ls_kernel(const __grid
             }
         }
         __syncthreads();
+        LS_TICK(8);
         // ------------------------------------------------------------------ H: the winner becomes the nominal; lamb and termination (ls_select_kernel)
         for (int k = warp; k < n_r; k += kFusedWarps) {
             const int s = __fns(rm, 0, k + 1);
@@ -431,10 +446,18 @@ __global__ void __launch_bounds__(kFusedThreads, 2) fused_ls_kernel(const __grid
         // every slot empty and nothing left to take: done.  (The predicate is evaluated before the barrier inside
         // __syncthreads_or, so the phase is closed by a barrier of its own first.)
         __syncthreads();
+        LS_TICK(9);
         const int live = __syncthreads_or(tid < G && H[tid].mode != SLOT_EMPTY);
         if (!live)
             break;
     }
+#ifdef CILQR_FUSED_PROFILE
+    if (tid == 0 && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1)) {
+        printf("fused ls cta %d: %llu iterations; cycles per phase (A B C D E F1 G1 F2+G2 H ...):", blockIdx.x, n_iter);
+        for (int i = 0; i < 12; ++i) printf(" %lld", pc[i]);
+        printf("\n");
+    }
+#endif
     if (tid == 0 && A.stats) {
         atomicAdd(A.stats + 0, n_cost);
         atomicAdd(A.stats + 1, n_deriv);
