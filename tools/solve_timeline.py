@@ -1,21 +1,20 @@
 """Timeline of one batched solve from the kernels' own %globaltimer stamps (no profiler): which launches overlap.
 
-    CILQR_TRACE=1 [CILQR_CHUNKS=k] PYTHONPATH=. python tools/solve_timeline.py [B] [n_obs] [host]
+    PYTHONPATH=. python tools/solve_timeline.py [B] [n_obs] [host|dev] [chunks]
 """
 import ctypes as C
-import os
 import sys
 
 import numpy as np
 import torch
 
-os.environ.setdefault("CILQR_TRACE", "1")
 import cilqr_b200  # noqa: E402
 from cilqr_b200 import scenarios  # noqa: E402
 
 B = int(sys.argv[1]) if len(sys.argv) > 1 else 65536
 n_obs = int(sys.argv[2]) if len(sys.argv) > 2 else 20
 host = len(sys.argv) > 3 and sys.argv[3] == "host"
+chunks = int(sys.argv[4]) if len(sys.argv) > 4 else 0
 dev = torch.device("cuda:0")
 lib = cilqr_b200.load_library()
 p = cilqr_b200.Parameters()
@@ -24,7 +23,7 @@ p = p.replace(horizon=50)
 N = 50
 sc = scenarios.make_scenarios(p, 0, B, n_obs, dense=False)
 keys = ("x0", "U0", "poly", "xlp", "obs_state0", "obs_LW", "obs_sigma")
-s = cilqr_b200.iLQR(p, max_batch=B, max_obs=n_obs)
+s = cilqr_b200.iLQR(p, max_batch=B, max_obs=n_obs, options={cilqr_b200.OPT_TRACE: 1, cilqr_b200.OPT_CHUNKS: chunks})
 if host:
     d = {k: torch.from_numpy(sc[k]).pin_memory().numpy() for k in keys}
     U = torch.empty((B, 2 * N), dtype=torch.float64).pin_memory().numpy()
