@@ -238,9 +238,10 @@ int cilqr_solve_stats(cilqr_handle h, int64_t *cost_passes, int64_t *deriv_passe
                       void *stream);
 
 /* Several handles driven from several host threads with host buffers (CILQR_MEM_HOST): with `on` != 0 this handle's
- * cilqr_solve_batch calls copy their inputs, take a process-wide compute token, run their rounds (one chunk, direct launches),
- * release the token when the last kernel has finished and then copy the results back — the handles' kernels run one solve after
- * the other at full speed, their copies under each other's kernels.  Off by default (a single caller is faster with the
+ * cilqr_solve_batch calls copy their inputs, take a process-wide compute token, enqueue their kernels (one chunk; a repeated
+ * call replays a recorded graph) behind the kernels of the token's previous holder on the same device, release the token and
+ * copy the results back — the handles' kernels run one solve after the other at full speed with no host round trip between
+ * them, their copies under each other's kernels.  Off by default (a single caller is faster with the
  * chunked, graph-replayed path); CILQR_EXCLUSIVE=1 in the environment turns it on for every handle created afterwards.
  * Results are bit-identical either way.  No reference counterpart (the reference's node is single-threaded,
  * ilqr_uncertainty_node.cpp:111-130). */

@@ -1,0 +1,11 @@
+#!/bin/bash
+# Measurement build: the product sources with -DCILQR_PROBE_ENV (environment knobs for probes) -> build/libcilqr_probe.so,
+# loaded with CILQR_B200_LIB=build/libcilqr_probe.so.  The product library is rebuilt afterwards.
+set -e
+cd "$(dirname "$0")/.."
+P=uncertainty-aware-cilqr-for-trajectory-optimization_b200
+CILQR_NVCC_EXTRA="-DCILQR_PROBE_ENV $*" python $P/build.py --force > /dev/null
+mkdir -p build
+cp $P/libcilqr_b200.so build/libcilqr_probe.so
+python $P/build.py --force > /dev/null
+ls -la build/libcilqr_probe.so $P/libcilqr_b200.so

@@ -489,6 +489,11 @@ static int create_impl(cilqr_solver *h, int dev)
         h->occ_cost = std::max(1, o0);
         h->occ_deriv = std::max(1, std::min(o1, o2));
         h->occ_sweep = std::max(1, o3);
+#ifdef CILQR_PROBE_ENV // measurement builds only (tools/build_probe.sh): knobs that are not part of the ABI
+        if (const char *e = getenv("CILQR_PROBE_SWEEP_OCC")) h->occ_sweep = std::max(1, std::min(h->occ_sweep, atoi(e)));
+        if (const char *e = getenv("CILQR_PROBE_DERIV_OCC")) h->occ_deriv = std::max(1, std::min(h->occ_deriv, atoi(e)));
+        if (const char *e = getenv("CILQR_PROBE_COST_OCC")) h->occ_cost = std::max(1, std::min(h->occ_cost, atoi(e)));
+#endif
     }
     { // slots per CTA of the fused kernel: two CTAs per SM (1 KB per CTA is the system's), else one CTA with what fits
         const size_t two = (size_t)h->smem_per_sm / 2 - 1024, one = (size_t)h->smem_optin;
@@ -553,6 +558,11 @@ int cilqr_create(const cilqr_params *p, int max_batch, int max_obs, cilqr_handle
     return cilqr_create_on(p, max_batch, max_obs, -1, out);
 }
 
+// Compute token (see solve_rounds).
+static std::mutex g_compute_token;
+constexpr int kTokenDevices = 64;
+static cudaEvent_t g_token_tail[kTokenDevices] = {}; // per device: end of the kernels of the last solve that took the token
+
 int cilqr_destroy(cilqr_handle h)
 {
     if (!h) return 0;
@@ -569,7 +579,15 @@ int cilqr_destroy(cilqr_handle h)
         if (h->ev_join[c]) cudaEventDestroy(h->ev_join[c]);
     }
     if (h->ev_in) cudaEventDestroy(h->ev_in);
-    if (h->ev_kdone) cudaEventDestroy(h->ev_kdone);
+    if (h->ev_kdone) {
+        {
+            std::lock_guard<std::mutex> compute_token(g_compute_token);
+            for (cudaEvent_t &tail : g_token_tail)
+                if (tail == h->ev_kdone) tail = nullptr;
+        }
+        cudaEventSynchronize(h->ev_kdone); // a later holder's wait on it has been enqueued at most; the event itself may go once it has fired
+        cudaEventDestroy(h->ev_kdone);
+    }
     if (h->ev_fork) cudaEventDestroy(h->ev_fork);
     if (h->ev_copied) cudaEventDestroy(h->ev_copied);
     if (h->graph_exec) cudaGraphExecDestroy(h->graph_exec);
@@ -690,8 +708,9 @@ static int need_obstacles(cilqr_handle h, int B)
 // Compute token (cilqr_set_compute_token; host buffers): several handles driven from several host threads would otherwise
 // interleave their kernels on the GPU — every solve takes longer and all of them finish, and copy their results back, at about
 // the same time.  With the token the solves' kernels run one handle after the other at full speed, and a handle's host<->device
-// copies run under the other handles' kernels (solve_rounds).
-static std::mutex g_compute_token;
+// copies run under the other handles' kernels (solve_rounds).  The order is kept on the DEVICE: the mutex is held only while a
+// solve's kernels are enqueued, behind a wait on the event that marks the end of the previous holder's kernels on that device —
+// no host round trip between two solves, the next one's kernels are already queued when the last one's finish.
 
 struct HostIO { // caller's host arrays (CILQR_MEM_HOST) — null members when the caller's buffers are device memory
     const double *x0 = nullptr, *U_in = nullptr, *poly = nullptr, *xlp = nullptr;
@@ -971,21 +990,21 @@ static int solve_rounds(cilqr_handle h, const SolveArgs &A, const HostIO *io, cu
         CILQR_CUDA(cudaEventSynchronize(h->ev_in)); // inputs are on the device before the token is taken: the copy ran under another handle's kernels
         std::vector<uintptr_t> kkey(key.begin(), key.begin() + 19);
         kkey.push_back(1); // (kernels only)
-        int rc;
         {
             std::lock_guard<std::mutex> compute_token(g_compute_token);
-            rc = run_plan(h, A, nullptr, st, plan, kkey);
-            if (rc == 0) {
-                CILQR_CUDA(cudaEventRecord(h->ev_kdone, st));
-                CILQR_CUDA(cudaMemcpyAsync(io->U, A.U, sb * 2 * N * sizeof(double), cudaMemcpyDeviceToHost, st));
-                if (io->X) CILQR_CUDA(cudaMemcpyAsync(io->X, A.X, sb * 4 * (N + 1) * sizeof(double), cudaMemcpyDeviceToHost, st));
-                if (io->J) CILQR_CUDA(cudaMemcpyAsync(io->J, A.J, sb * sizeof(double), cudaMemcpyDeviceToHost, st));
-                if (io->iters) CILQR_CUDA(cudaMemcpyAsync(io->iters, A.iters, sb * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
-                if (io->status) CILQR_CUDA(cudaMemcpyAsync(io->status, A.status, sb * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
-                CILQR_CUDA(cudaEventSynchronize(h->ev_kdone)); // the kernels are done: the next handle may start while this one's results travel back
-            }
+            cudaEvent_t &tail = g_token_tail[h->device < kTokenDevices ? h->device : kTokenDevices - 1];
+            if (tail && tail != h->ev_kdone) CILQR_CUDA(cudaStreamWaitEvent(st, tail, 0)); // behind the previous holder's kernels
+            if (int rc = run_plan(h, A, nullptr, st, plan, kkey)) return rc;
+            CILQR_CUDA(cudaEventRecord(h->ev_kdone, st));
+            tail = h->ev_kdone;
         }
-        return rc;
+        // the results travel back under the next holder's kernels
+        CILQR_CUDA(cudaMemcpyAsync(io->U, A.U, sb * 2 * N * sizeof(double), cudaMemcpyDeviceToHost, st));
+        if (io->X) CILQR_CUDA(cudaMemcpyAsync(io->X, A.X, sb * 4 * (N + 1) * sizeof(double), cudaMemcpyDeviceToHost, st));
+        if (io->J) CILQR_CUDA(cudaMemcpyAsync(io->J, A.J, sb * sizeof(double), cudaMemcpyDeviceToHost, st));
+        if (io->iters) CILQR_CUDA(cudaMemcpyAsync(io->iters, A.iters, sb * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+        if (io->status) CILQR_CUDA(cudaMemcpyAsync(io->status, A.status, sb * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+        return 0;
     }
     return run_plan(h, A, io, st, plan, key);
 }
