@@ -13,10 +13,14 @@
 //                                                   (only for accepted scenarios: a rejected nominal never needs derivatives)
 //     batch_sweep_kernel   thread = scenario        Riccati sweep with V_x / V_xx in registers, then the closed-loop rollout
 //
-// State lives in HBM scenario-major: one 144-byte header and N+1 step records of 144 bytes per scenario.  The (scenario, t)
-// kernels index the work list flat, g = entry * N + t, so a warp's lanes walk consecutive timesteps of one or two scenarios
-// (coalesced, obstacle constants warp-uniform); the sweep kernel's lanes each stream through their own scenario's records.
-// Either way every sector that is fetched is used, however sparse the set of still-active scenarios has become.
+// State lives in HBM scenario-major, in three arrays that the kernels stream independently (each kernel moves only what it
+// uses, and every array is written in whole 32-byte sectors): the state records [scenario][t = 0..N] of 64 bytes (state column,
+// cos/sin of the heading, control column), the tracking-gradient records [scenario][t < N] of 32 bytes (cost pass -> derivative
+// pass) and the derivative records [scenario][t < N] of 80 bytes, which the sweep overwrites with the gains; plus one 144-byte
+// header per scenario.  The (scenario, t) kernels index the work list flat, g = entry * N + t, so a warp's lanes walk
+// consecutive timesteps of one or two scenarios (coalesced, obstacle constants warp-uniform); the sweep kernel's lanes each
+// stream through their own scenario's records.  Either way every sector that is fetched is used, however sparse the set of
+// still-active scenarios has become.
 // Work lists are compacted on the device; the host launches a fixed sequence of kernels, no synchronisation, no read-back.
 //
 // Same per-step device functions as the fused kernels (cilqr_device.cuh) — same arithmetic, same quirks.
@@ -28,14 +32,18 @@ namespace cilqr
 {
 enum { MODE_ITERATE = 0, MODE_FINAL = 1, MODE_DONE = 2, MODE_LS = 3 }; // MODE_LS: iterating with the line-search extension
 
-// Step record of (scenario, t), t = 0..N: state column t, cos/sin of its heading, control column t, and the derivative
-// record of step t (overwritten by the gains in the sweep).  16-byte aligned pairs -> 128-bit loads.
-// kStepD may be padded beyond kStepUsed: tried 160-byte records (every write group on whole 32-byte sectors) — the derivative
-// kernel lost 45 % to it (826 vs 562 us in round 0), so records stay packed at 144 bytes.
+// Step record of (scenario, t) as the on-chip kernels (cilqr_fused*.cuh) and the sweep's shared-memory ring hold it: state
+// column t, cos/sin of its heading, control column t, and the derivative record of step t (overwritten by the gains in the
+// sweep).  16-byte aligned pairs -> 128-bit accesses.  In HBM the round kernels keep the two halves in separate arrays:
+// kStateD doubles of state, kRec doubles of derivatives / gains, and in between the kTrackD doubles the cost pass hands to the
+// derivative pass.  (One 144-byte record per step was the first layout: the cost pass, the set-up and the output kernel then
+// moved 144 bytes per step for the 40-64 they use; 160-byte records, every field group on whole sectors, cost the derivative
+// kernel 45 %.)
 enum { S_X = 0, S_Y, S_V, S_TH, S_C, S_S, S_U0, S_U1, S_R, kStepUsed = S_R + kRec, kStepD = kStepUsed };
+enum { kStateD = S_R, kTrackD = 4 };
 // Scenario header.
 enum { H_XF = 0, H_DXS, H_POLY, H_LAMB = H_POLY + kMaxPoly, H_JOLD, H_JNEW, H_JRES, H_ITERS_MODE, H_CONV_STATUS, H_LIP, H_PAD, kHdrD };
-static_assert(kStepD % 2 == 0 && kHdrD % 2 == 0, "records are accessed with 128-bit loads");
+static_assert(kStepD % 2 == 0 && kHdrD % 2 == 0 && kStateD % 4 == 0 && kTrackD % 4 == 0, "records are accessed with 128-bit loads; state and tracking records are whole sectors");
 
 // Compact constant-velocity obstacle: [scenario][obstacle][8] constants + [scenario][obstacle][t] 1/b^2.
 enum { CV_X0 = 0, CV_Y0, CV_VC, CV_VS, CV_C, CV_S, CV_IA2, CV_V, CV_FIELDS };
@@ -43,7 +51,9 @@ enum { CV_X0 = 0, CV_Y0, CV_VC, CV_VS, CV_C, CV_S, CV_IA2, CV_V, CV_FIELDS };
 struct BatchView {
     int N;
     double *hdr; // [B][kHdrD]
-    double *rec; // [B][N+1][kStepD]
+    double *st;  // [B][N+1][kStateD]  state records
+    double *tr;  // [B][N][kTrackD]    tracking gradient (2 w_pos ex, 2 w_pos ey, 2 w_vel ev, -)
+    double *dr;  // [B][N][kRec]       derivative records, then gains
     int *list0, *list1; // work lists (ping-pong)
     int *cnt;           // [max_iter + 3] list lengths per round
     int n_obs, cv;
@@ -53,7 +63,9 @@ struct BatchView {
     unsigned long long *trace; // diagnostics (cilqr_solve_trace): [max_iter + 3][kTraceKinds][2] first-start / last-end per launch, or null
     __device__ __forceinline__ int *list(int r) const { return (r & 1) ? list1 : list0; }
     __device__ __forceinline__ double *header(int b) const { return hdr + (size_t)b * kHdrD; }
-    __device__ __forceinline__ double *step(int b, int t) const { return rec + ((size_t)b * (N + 1) + t) * kStepD; }
+    __device__ __forceinline__ double *state(int b, int t) const { return st + ((size_t)b * (N + 1) + t) * kStateD; }
+    __device__ __forceinline__ double *track(int b, int t) const { return tr + ((size_t)b * N + t) * kTrackD; }
+    __device__ __forceinline__ double *deriv(int b, int t) const { return dr + ((size_t)b * N + t) * kRec; }
 };
 // Timeline of one solve without a profiler: every CTA's thread 0 folds %globaltimer into (min start, ~max end) of its launch.
 enum { TRACE_COST = 0, TRACE_DERIVS, TRACE_SWEEP, TRACE_IO, kTraceKinds };
@@ -226,8 +238,8 @@ __global__ void __launch_bounds__(256) expand_cv_records_kernel(DevParams P, siz
 // X = get_nominal_trajectory(x_0, U) (iLQR.cpp:203, :51-62), J_old = DBL_MAX, lamb = 1 (iLQR.cpp:205-209), work list = all.
 //
 // One scenario per lane (the rollout is a sincos chain), but memory is moved by the warp: a lane writing its own 64 bytes of a
-// step record is 32 cache lines per store instruction, and the first version of this kernel spent 320 us on that.  Headers and
-// step records are staged in shared memory and written in 16-byte pieces, consecutive lanes -> consecutive bytes (the 32
+// state record is 32 cache lines per store instruction, and the first version of this kernel spent 320 us on that.  Headers and
+// state records are staged in shared memory and written in 16-byte pieces, consecutive lanes -> consecutive bytes (the 32
 // headers of a warp are one contiguous 4.6 KB block); the controls are read as 128-byte row segments, kInitTile steps at a time.
 constexpr int kInitThreads = 128;
 constexpr int kInitTile = 8; // timesteps of U per shared-memory tile
@@ -287,26 +299,25 @@ __global__ void __launch_bounds__(kInitThreads) batch_init_kernel(DevParams P, B
     double n0 = x0[4 * (size_t)b], n1 = x0[4 * (size_t)b + 1], n2 = x0[4 * (size_t)b + 2], n3 = x0[4 * (size_t)b + 3];
     double c, s;
     sincos(n3, &s, &c);
-    double2 *rec16 = reinterpret_cast<double2 *>(V.rec);
-    const size_t stride16 = (size_t)(N + 1) * (kStepD / 2);
-    // Whole records are written, derivative fields zeroed: a record is 4.5 sectors, and sectors left partly written would make
-    // the memory system merge them with their old contents on eviction.  Piece p = k * 32 + lane of a step: scenario p / 9,
-    // piece p % 9 — (x, y), (v, theta), (cos, sin), (u0, u1) from the staging row, zeros for the rest.
-    constexpr int kPiecesPerRec = kStepD / 2;
+    double2 *rec16 = reinterpret_cast<double2 *>(V.st);
+    const size_t stride16 = (size_t)(N + 1) * (kStateD / 2);
+    // Piece p = k * 32 + lane of a step: scenario p / 4, piece p % 4 — (x, y), (v, theta), (cos, sin), (u0, u1) from the staging
+    // row; the 64 bytes of a record are two whole sectors.
+    constexpr int kPiecesPerRec = kStateD / 2;
     size_t st_off[kPiecesPerRec];
-    int st_src[kPiecesPerRec]; // staging piece to copy, -1: zeros, -2: nothing (inactive lane)
+    int st_src[kPiecesPerRec]; // staging piece to copy, -2: nothing (inactive lane)
 #pragma unroll
     for (int k = 0; k < kPiecesPerRec; ++k) {
         const int p = k * 32 + lane, src = p / kPiecesPerRec, f = p - src * kPiecesPerRec;
         st_off[k] = (size_t)(b0 + src) * stride16 + f;
-        st_src[k] = src >= nact ? -2 : (f < 4 ? src * 5 + f : -1);
+        st_src[k] = src >= nact ? -2 : src * 5 + f;
     }
-    auto flush = [&](int t) { // staged step t -> records t
+    auto flush = [&](int t) { // staged step t -> state records t
         const double2 *o = reinterpret_cast<const double2 *>(&sm.out[t & 1][0][0]);
 #pragma unroll
         for (int k = 0; k < kPiecesPerRec; ++k)
             if (st_src[k] != -2)
-                rec16[st_off[k] + (size_t)t * kPiecesPerRec] = st_src[k] >= 0 ? o[st_src[k]] : make_double2(0.0, 0.0);
+                rec16[st_off[k] + (size_t)t * kPiecesPerRec] = o[st_src[k]];
     };
     for (int t0 = 0; t0 < N; t0 += kInitTile) {
         const int nt = min(kInitTile, N - t0);
@@ -352,7 +363,7 @@ __global__ void __launch_bounds__(256) batch_output_kernel(DevParams P, BatchVie
     const size_t total = (size_t)B * (N + 1);
     for (size_t g = blockIdx.x * (size_t)blockDim.x + threadIdx.x; g < total; g += (size_t)gridDim.x * blockDim.x) {
         const int b = (int)(g / (N + 1)), t = (int)(g - (size_t)b * (N + 1));
-        const double *r = V.rec + g * kStepD;
+        const double *r = V.st + g * kStateD;
         if (X) {
             const double2 a = ld2(r + S_X), c = ld2(r + S_V);
             X[4 * g] = a.x; X[4 * g + 1] = a.y; X[4 * g + 2] = c.x; X[4 * g + 3] = c.y;
@@ -424,15 +435,16 @@ __global__ void __launch_bounds__(kCostThreads) batch_cost_kernel(DevParams P, B
                 yf.c[k] = c2.x;
                 yf.c[k + 1] = c2.y;
             }
-            double *r = V.step(b, t);
+            const double *r = V.state(b, t);
             const double2 xy = ld2(r + S_X), u = ld2(r + S_U0);
             const double v = r[S_V];
             double cx, cy;
             closest_point_lip(P, yf.pl, yf, h[H_LIP], xy.x, xy.y, cx, cy);
             const double ex = xy.x - cx, ey = xy.y - cy, ev = v - P.v_des;
             sJ[idx] = tracking_cost(P, ex, ey, ev, u.x, u.y);
-            st2(r + S_R, 2.0 * P.w_pos * ex, 2.0 * P.w_pos * ey);
-            st2(r + S_R + 2, 2.0 * P.w_vel * ev, 0.0); // (R3 is rewritten by the derivative kernel; the sector is written whole)
+            double *g = V.track(b, t); // one sector, written whole
+            st2(g, 2.0 * P.w_pos * ex, 2.0 * P.w_pos * ey);
+            st2(g + 2, 2.0 * P.w_vel * ev, 0.0);
         }
         __syncthreads();
         // ---- per scenario: J in the reference's summation order, then iLQR.cpp:217-239
@@ -538,7 +550,7 @@ __global__ void __launch_bounds__(kDerivThreads, 2) batch_derivs_kernel(DevParam
         const int e = (int)(g / N);
         t = (int)(g - (long long)e * N);
         b = list[e];
-        const double *r = V.step(b, t);
+        const double *r = V.state(b, t);
         xy = ld2(r + S_X); cs = ld2(r + S_C); u = ld2(r + S_U0); v = r[S_V];
         if (g + stride < total)
             b_next = list[(int)((g + stride) / N)];
@@ -548,12 +560,13 @@ __global__ void __launch_bounds__(kDerivThreads, 2) batch_derivs_kernel(DevParam
         }
     }
     for (; g < total; g += stride) {
-        double *r = V.step(b, t);
+        const double *trk = V.track(b, t);
+        double *r = V.deriv(b, t);
         const double x = xy.x, y = xy.y, ce = cs.x, se = cs.y, vv = v;
         const double2 uu = u;
         const int bn = b_next, tn = (int)((g + stride) % N);
         if (g + stride < total) {
-            const double *rn = V.step(bn, tn);
+            const double *rn = V.state(bn, tn);
             xy = ld2(rn + S_X); cs = ld2(rn + S_C); u = ld2(rn + S_U0); v = rn[S_V];
             if (g + 2 * stride < total)
                 b_next = list[(int)((g + 2 * stride) / N)];
@@ -620,12 +633,12 @@ __global__ void __launch_bounds__(kDerivThreads, 2) batch_derivs_kernel(DevParam
         }
         double lu0, lu1, luu0, luu1, bc;
         control_terms<true>(P, vv, uu.x, uu.y, lu0, lu1, luu0, luu1, bc);
-        const double2 tr = ld2(r + S_R), tr2 = ld2(r + S_R + 2); // tracking part written by batch_cost_kernel
-        st2(r + S_R, tr.x + P.w_obs * g0, tr.y + P.w_obs * g1);
-        st2(r + S_R + 2, tr2.x, 2.0 * P.w_pos + P.w_obs * h00); // every sector is written whole
-        st2(r + S_R + 4, P.w_obs * h01, 2.0 * P.w_pos + P.w_obs * h11);
-        st2(r + S_R + 6, lu0, lu1);
-        st2(r + S_R + 8, luu0, luu1);
+        const double2 tr = ld2(trk), tr2 = ld2(trk + 2); // tracking part written by batch_cost_kernel
+        st2(r, tr.x + P.w_obs * g0, tr.y + P.w_obs * g1);
+        st2(r + 2, tr2.x, 2.0 * P.w_pos + P.w_obs * h00); // consecutive lanes, consecutive records: every sector is written whole
+        st2(r + 4, P.w_obs * h01, 2.0 * P.w_pos + P.w_obs * h11);
+        st2(r + 6, lu0, lu1);
+        st2(r + 8, luu0, luu1);
         b = bn;
         t = tn;
         stage ^= 1;
@@ -645,7 +658,7 @@ __device__ __forceinline__ void prefetch_step(const double *r)
 //
 // The 32 scenarios of a warp sit anywhere in the batch (work-list order), so "lane l loads its own record" is 32 cache lines per
 // warp instruction: measured (tools/stream_micro.cu) that costs ~2.9 cycles per line in the load/store unit and bounds the sweep
-// at ~5600 cycles per step with 12 warps per SM.  Instead the warp moves the 32 records of a step together: 32 x 9 pieces of
+// at ~5600 cycles per step with 12 warps per SM.  Instead the warp moves the 32 records of a step together: 32 x (4 + 5) pieces of
 // 16 bytes, lane l taking pieces l, l + 32, ... — consecutive lanes read consecutive bytes of one record, ~6 lines per instruction.
 // The pieces go to a shared-memory ring with cp.async (kRing records deep, i.e. kRing - 1 steps ahead of the arithmetic), each
 // lane reads its own record back from the ring (144-byte rows: conflict-free 128-bit reads), and results return the same way:
@@ -653,8 +666,9 @@ __device__ __forceinline__ void prefetch_step(const double *r)
 // is the HBM rate for this traffic.
 constexpr int kSweepThreads = 32;
 constexpr int kRing = 3;                       // records in flight per lane
-constexpr int kPieces = kStepUsed / 2;         // 16-byte pieces of a step record that carry data
-constexpr int kRecPieces = kStepD / 2;         // 16-byte pieces from one record to the next
+constexpr int kStatePieces = kStateD / 2;      // 16-byte pieces of a state record
+constexpr int kGainPieces = kRec / 2;          // 16-byte pieces of a derivative / gain record
+constexpr int kRowPieces = kStepUsed / 2;      // pieces of a ring row: the state record, then the derivative record of the step
 constexpr int kOutD = 10;                      // doubles per staged result row (80-byte rows: conflict-free 128-bit accesses)
 static_assert(kOutD >= kRec && kOutD % 2 == 0, "a result row holds the gains of one step");
 
@@ -675,7 +689,7 @@ __global__ void __launch_bounds__(kSweepThreads, 11) batch_sweep_kernel(DevParam
     const int lane = threadIdx.x;
     const uint32_t ring0 = (uint32_t)__cvta_generic_to_shared(&sm.ring[0][0][0]);
     constexpr uint32_t kSlotBytes = kSweepThreads * kStepUsed * 8;
-    const size_t stride16 = (size_t)(N + 1) * kRecPieces; // 16-byte pieces per scenario
+    const size_t st_stride16 = (size_t)(N + 1) * kStatePieces, dr_stride16 = (size_t)N * kGainPieces; // 16-byte pieces per scenario
 
     for (int i0 = blockIdx.x * kSweepThreads; i0 < cnt; i0 += gridDim.x * kSweepThreads) {
         const int nact = min(kSweepThreads, cnt - i0);
@@ -683,46 +697,51 @@ __global__ void __launch_bounds__(kSweepThreads, 11) batch_sweep_kernel(DevParam
         const int b = list[i0 + (active ? lane : 0)];
         double *h = V.header(b);
         const double lamb = h[H_LAMB];
-        const double2 *rec16 = reinterpret_cast<const double2 *>(V.rec);
-        // piece p = k * 32 + lane of a step belongs to the scenario of lane p / pieces-per-row
-        size_t ld_off[kPieces]; // load pieces: record (lane p / 9), piece p % 9
-        bool ld_on[kPieces];
+        const double2 *st16 = reinterpret_cast<const double2 *>(V.st), *dr16 = reinterpret_cast<const double2 *>(V.dr);
+        // The warp moves the 32 records of a step together.  State records: piece p = k * 32 + lane belongs to the scenario of
+        // lane p / 4 (piece p % 4); derivative / gain records: lane p / 5, piece p % 5.  Both land in the lane's ring row.
+        size_t s_off[kStatePieces], d_off[kGainPieces];
+        uint32_t s_dst[kStatePieces], d_dst[kGainPieces]; // byte offsets inside a ring slot
+        bool s_on[kStatePieces], d_on[kGainPieces];
 #pragma unroll
-        for (int k = 0; k < kPieces; ++k) {
-            const int p = k * kSweepThreads + lane, src = p / kPieces, f = p - src * kPieces;
-            ld_off[k] = (size_t)__shfl_sync(0xffffffffu, b, src) * stride16 + f;
-            ld_on[k] = src < nact;
+        for (int k = 0; k < kStatePieces; ++k) {
+            const int p = k * kSweepThreads + lane, src = p / kStatePieces, f = p - src * kStatePieces;
+            s_off[k] = (size_t)__shfl_sync(0xffffffffu, b, src) * st_stride16 + f;
+            s_dst[k] = (uint32_t)(src * kRowPieces + f) * 16;
+            s_on[k] = src < nact;
         }
-        auto fetch = [&](int t, int slot) { // record t of every active lane -> ring[slot]
-#pragma unroll
-            for (int k = 0; k < kPieces; ++k)
-                if (ld_on[k])
-                    cp_async16(ring0 + slot * kSlotBytes + (k * kSweepThreads + lane) * 16, rec16 + ld_off[k] + (size_t)t * kRecPieces);
-        };
-
-        // ---- iLQR::backward_pass (iLQR.cpp:91-195): gains overwrite the derivative records
-        constexpr int kGainPieces = kRec / 2;
-        static_assert(kGainPieces * 2 == kOutD, "staged gain rows are dense: piece p of the warp sits at byte 16 p");
-        size_t st_off[kGainPieces];
-        bool st_on[kGainPieces];
 #pragma unroll
         for (int k = 0; k < kGainPieces; ++k) {
             const int p = k * kSweepThreads + lane, src = p / kGainPieces, f = p - src * kGainPieces;
-            st_off[k] = (size_t)__shfl_sync(0xffffffffu, b, src) * stride16 + S_R / 2 + f;
-            st_on[k] = src < nact;
+            d_off[k] = (size_t)__shfl_sync(0xffffffffu, b, src) * dr_stride16 + f;
+            d_dst[k] = (uint32_t)(src * kRowPieces + kStatePieces + f) * 16;
+            d_on[k] = src < nact;
         }
-        auto flush_gains = [&](int j) { // staged gains of step j -> records j
-            const double2 *o = reinterpret_cast<const double2 *>(&sm.out[j & 1][0][0]);
-            double2 *g16 = reinterpret_cast<double2 *>(V.rec);
+        auto fetch = [&](int t, int slot) { // state and derivative / gain record t of every active lane -> ring[slot]
+#pragma unroll
+            for (int k = 0; k < kStatePieces; ++k)
+                if (s_on[k])
+                    cp_async16(ring0 + slot * kSlotBytes + s_dst[k], st16 + s_off[k] + (size_t)t * kStatePieces);
 #pragma unroll
             for (int k = 0; k < kGainPieces; ++k)
-                if (st_on[k])
-                    g16[st_off[k] + (size_t)j * kRecPieces] = o[k * kSweepThreads + lane];
+                if (d_on[k])
+                    cp_async16(ring0 + slot * kSlotBytes + d_dst[k], dr16 + d_off[k] + (size_t)t * kGainPieces);
+        };
+
+        // ---- iLQR::backward_pass (iLQR.cpp:91-195): gains overwrite the derivative records
+        static_assert(kGainPieces * 2 == kOutD, "staged gain rows are dense: piece p of the warp sits at byte 16 p");
+        auto flush_gains = [&](int j) { // staged gains of step j -> records j
+            const double2 *o = reinterpret_cast<const double2 *>(&sm.out[j & 1][0][0]);
+            double2 *g16 = reinterpret_cast<double2 *>(V.dr);
+#pragma unroll
+            for (int k = 0; k < kGainPieces; ++k)
+                if (d_on[k])
+                    g16[d_off[k] + (size_t)j * kGainPieces] = o[k * kSweepThreads + lane];
         };
         RiccatiState S;
         RiccatiIn I;
         {
-            const double *rN = V.step(b, N);
+            const double *rN = V.state(b, N);
             const double2 vt = ld2(rN + S_V), cs = ld2(rN + S_C);
             I.v = vt.x; I.c = cs.x; I.s = cs.y;
         }
@@ -791,22 +810,22 @@ __global__ void __launch_bounds__(kSweepThreads, 11) batch_sweep_kernel(DevParam
         // ---- iLQR::forward_pass (iLQR.cpp:68-86), full step, in place: the candidate is accepted by construction (lagged test)
         // Step t reads record t (old state column, control, gains) and produces U(:, t) and column t + 1; they are written one
         // step later, when record t + 1 — whose old column is still needed — is known to be in the ring.
-        constexpr int kRollPieces = 4; // (u0, u1) -> record t; (x, y), (v, theta), (cos, sin) -> record t + 1
+        constexpr int kRollPieces = 4; // (u0, u1) -> state record t; (x, y), (v, theta), (cos, sin) -> state record t + 1
         size_t ro_off[kRollPieces];
         bool ro_on[kRollPieces];
 #pragma unroll
         for (int k = 0; k < kRollPieces; ++k) {
             const int p = k * kSweepThreads + lane, src = p / kRollPieces, f = p - src * kRollPieces;
-            ro_off[k] = (size_t)__shfl_sync(0xffffffffu, b, src) * stride16 + (f == 0 ? S_U0 / 2 : kRecPieces + f - 1);
+            ro_off[k] = (size_t)__shfl_sync(0xffffffffu, b, src) * st_stride16 + (f == 0 ? S_U0 / 2 : kStatePieces + f - 1);
             ro_on[k] = (roll_mask >> src) & 1u;
         }
         auto flush_roll = [&](int t) {
-            double2 *g16 = reinterpret_cast<double2 *>(V.rec);
+            double2 *g16 = reinterpret_cast<double2 *>(V.st);
 #pragma unroll
             for (int k = 0; k < kRollPieces; ++k) {
                 const int p = k * kSweepThreads + lane, src = p / kRollPieces, f = p - src * kRollPieces;
                 if (ro_on[k])
-                    g16[ro_off[k] + (size_t)t * kRecPieces] = *reinterpret_cast<const double2 *>(&sm.out[t & 1][src][2 * f]);
+                    g16[ro_off[k] + (size_t)t * kStatePieces] = *reinterpret_cast<const double2 *>(&sm.out[t & 1][src][2 * f]);
             }
         };
         slot = 0;
@@ -880,9 +899,10 @@ __global__ void __launch_bounds__(kSweepThreads, 11) batch_sweep_kernel(DevParam
 // Same arithmetic as the first-pass fused kernel (cilqr_solver.cu: solve_kernel<true>, pinned on the plain-C port), in the
 // shape of the round kernels: every phase parallel over what it can be parallel over.
 //
-// Candidate trajectories: cand[b][a][t][8] = (x, y, v, theta, cos, sin, u0, u1) — the first 8 fields of a step record, so the
-// merit kernel reads nominal records (round 0: J of the initial nominal) and candidates through the same strides.
-constexpr int kCandD = S_R;
+// Candidate trajectories: cand[b][a][t][8] = (x, y, v, theta, cos, sin, u0, u1) — the layout of the state records, so the
+// merit kernel reads nominal records (round 0: J of the initial nominal) and candidates alike, and the winning candidate
+// replaces the nominal as one contiguous copy.
+constexpr int kCandD = kStateD;
 struct LsView {
     double *cand;   // [B][n_alphas][N + 1][kCandD]
     double *merit;  // [B][n_alphas][N]
@@ -946,9 +966,9 @@ __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.
 // One warp per CTA.  The chain of a step is short (gains, bicycle step, one sincos); what a warp cannot do fast is fetch 32
 // scattered records per step: 14 per-lane 16-byte loads per step cost ~1 800 cycles in the load/store unit, and the same
 // pieces moved cooperatively with cp.async still keep only one warp's worth of requests in flight per SM (46 / 52 us per
-// launch, with or without the arithmetic).  So the TMA unit moves them: kLsT consecutive steps of one scenario are one
-// contiguous run (kLsT x 144 bytes), one `cp.async.bulk` per scenario and chunk issued by the scenario's lane, completion
-// on an mbarrier, one chunk ahead of the arithmetic.  Each lane reads its scenario's row (the lanes of one scenario:
+// launch, with or without the arithmetic).  So the TMA unit moves them: kLsT consecutive steps of one scenario are two
+// contiguous runs (kLsT x 64 bytes of state records, kLsT x 80 bytes of gains), two `cp.async.bulk` per scenario and chunk
+// issued by the scenario's lane, completion on one mbarrier, one chunk ahead of the arithmetic.  Each lane reads its scenario's row (the lanes of one scenario:
 // broadcast; rows 16 bytes apart modulo 128: no bank conflicts on 128-bit accesses) and leaves its candidate the same way:
 // kLsT x 64 bytes staged in its own shared-memory row, one bulk store per lane and chunk.
 constexpr int kLsT = 8; // 92 KB of shared memory: two CTAs per SM
@@ -987,12 +1007,14 @@ __global__ void __launch_bounds__(32) ls_candidates_kernel(DevParams P, BatchVie
         const int b_slot = lane < n_slots ? w.list[e_first + lane] : 0; // scenario of row `lane`
         auto stage = [&](int c) {
             const int t0 = c * kLsT;
-            const uint32_t bytes = (uint32_t)min(kLsT, N - t0) * kStepD * 8, bar = bar0 + 8 * (c & 1);
+            const uint32_t steps = (uint32_t)min(kLsT, N - t0), bar = bar0 + 8 * (c & 1);
             if (lane == 0)
-                mbar_expect_tx(bar, bytes * n_slots);
+                mbar_expect_tx(bar, steps * (kStateD + kRec) * 8 * n_slots);
             __syncwarp();
-            if (lane < n_slots)
-                bulk_g2s((uint32_t)__cvta_generic_to_shared(&sm.in[c & 1][lane][0]), V.step(b_slot, t0), bytes, bar);
+            if (lane < n_slots) { // row: kLsT state records, then kLsT gain records
+                bulk_g2s((uint32_t)__cvta_generic_to_shared(&sm.in[c & 1][lane][0]), V.state(b_slot, t0), steps * kStateD * 8, bar);
+                bulk_g2s((uint32_t)__cvta_generic_to_shared(&sm.in[c & 1][lane][kLsT * kStateD]), V.deriv(b_slot, t0), steps * kRec * 8, bar);
+            }
         };
         stage(0);
         double n0 = 0, n1 = 0, n2 = 0, n3 = 0, co = 1, si = 0;
@@ -1002,7 +1024,7 @@ __global__ void __launch_bounds__(32) ls_candidates_kernel(DevParams P, BatchVie
                 stage(c + 1); // its buffer was read two chunks ago (the __syncwarp below)
             mbar_wait(bar0 + 8 * (c & 1), (parity >> (c & 1)) & 1);
             parity ^= 1u << (c & 1);
-            const double *__restrict__ row = &sm.in[c & 1][slot][0];
+            const double *__restrict__ row = &sm.in[c & 1][slot][0], *__restrict__ grow = row + kLsT * kStateD;
             double *__restrict__ orow = &sm.out[lane][0];
             if (c == 0) {
                 const double2 xy = ld2(row + S_X), vt = ld2(row + S_V), cs = ld2(row + S_C);
@@ -1011,10 +1033,9 @@ __global__ void __launch_bounds__(32) ls_candidates_kernel(DevParams P, BatchVie
             if (run) {
                 if (c > 0)
                     bulk_wait_read(); // this lane's previous bulk store has read its row
-                for (int tt = 0; tt < steps; ++tt, row += kStepD, orow += kCandD) {
+                for (int tt = 0; tt < steps; ++tt, row += kStateD, grow += kRec, orow += kCandD) {
                     const double2 xy = ld2(row + S_X), vt = ld2(row + S_V), u = ld2(row + S_U0);
-                    const double2 k = ld2(row + S_R), K0 = ld2(row + S_R + 2), K1 = ld2(row + S_R + 4), K2 = ld2(row + S_R + 6),
-                                  K3 = ld2(row + S_R + 8);
+                    const double2 k = ld2(grow), K0 = ld2(grow + 2), K1 = ld2(grow + 4), K2 = ld2(grow + 6), K3 = ld2(grow + 8);
                     const double d0 = n0 - xy.x, d1 = n1 - xy.y, d2 = n2 - vt.x, d3 = n3 - vt.y;
                     const double u0 = (u.x + alpha * k.x) + (K0.x * d0 + K1.x * d1 + K2.x * d2 + K3.x * d3);
                     const double u1 = (u.y + alpha * k.y) + (K0.y * d0 + K1.y * d1 + K2.y * d2 + K3.y * d3);
@@ -1060,7 +1081,7 @@ __global__ void __launch_bounds__(256) ls_merit_kernel(DevParams P, BatchView V,
         const double *h = V.header(b);
         if (hdr_ints(const_cast<double *>(h), H_ITERS_MODE).y != MODE_LS)
             continue;
-        const double *c = nominal ? V.step(b, t) : L.cand + (((size_t)b * L.n_alphas + a) * (N + 1) + t) * kCandD;
+        const double *c = nominal ? V.state(b, t) : L.cand + (((size_t)b * L.n_alphas + a) * (N + 1) + t) * kCandD;
         const double2 xy = ld2(c + S_X), cs = ld2(c + S_C), u = ld2(c + S_U0);
         const double v = c[S_V];
         PolyY yf;
@@ -1140,11 +1161,9 @@ __global__ void __launch_bounds__(128) ls_select_kernel(DevParams P, BatchView V
             const int a = __ffs(ok) - 1;
             const double Jw = __shfl_sync(0xffffffffu, Ja, a);
             const double2 *win = reinterpret_cast<const double2 *>(L.cand + ((size_t)b * A + a) * (N + 1) * kCandD);
-            double2 *rec = reinterpret_cast<double2 *>(V.step(b, 0));
-            for (int p = lane; p < (N + 1) * (kCandD / 2); p += 32) { // X, cos/sin, U of every step: the first four pieces of its record
-                const int t = p / (kCandD / 2), f = p - t * (kCandD / 2);
-                rec[(size_t)t * (kStepD / 2) + f] = win[p];
-            }
+            double2 *rec = reinterpret_cast<double2 *>(V.state(b, 0));
+            for (int p = lane; p < (N + 1) * (kCandD / 2); p += 32) // X, cos/sin, U of every step: the scenario's state records
+                rec[p] = win[p];
             const double dJ = J_cur - Jw;
             lamb = lamb / P.lamb_factor;
             if (lane == 0)

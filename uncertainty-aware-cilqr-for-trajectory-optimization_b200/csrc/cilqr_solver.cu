@@ -737,14 +737,32 @@ static int launch_fused(cilqr_handle h, const FusedArgs &F, int work, const Solv
 }
 
 // The launches of one solve, relative to stream `st` (the caller's stream, or the capture stream when a graph is recorded).
+// Work space of the round kernels for B scenarios (cilqr_batch.cuh): headers, state / tracking / derivative records, two work lists.
+static size_t rounds_hdr_doubles(int B) { return ((size_t)B * kHdrD + 3) / 4 * 4; } // the record arrays start on a sector boundary
+static size_t rounds_ws_doubles(int B, int N) { return rounds_hdr_doubles(B) + (size_t)B * (N + 1) * kStateD + (size_t)B * N * (kTrackD + kRec); }
+static size_t rounds_ws_bytes(int B, int N) { return rounds_ws_doubles(B, N) * sizeof(double) + (size_t)2 * B * sizeof(int); }
+// View of scenarios [o, o + ...) of a work space laid out for B scenarios.
+static BatchView rounds_view(void *ws, int B, int N, int o)
+{
+    BatchView v{};
+    v.N = N;
+    double *hdr = static_cast<double *>(ws), *st = hdr + rounds_hdr_doubles(B), *tr = st + (size_t)B * (N + 1) * kStateD, *dr = tr + (size_t)B * N * kTrackD;
+    int *list0 = reinterpret_cast<int *>(dr + (size_t)B * N * kRec);
+    v.hdr = hdr + (size_t)o * kHdrD;
+    v.st = st + (size_t)o * (N + 1) * kStateD;
+    v.tr = tr + (size_t)o * N * kTrackD;
+    v.dr = dr + (size_t)o * N * kRec;
+    v.list0 = list0 + o;
+    v.list1 = list0 + B + o;
+    return v;
+}
+
 static int issue_rounds(cilqr_handle h, const SolveArgs &A, const HostIO *io, cudaStream_t st, const SolvePlan &plan)
 {
     const DevParams &P = h->dp;
     const int N = P.N, B = A.B, n_obs = h->cur_nobs, K = plan.K, Bc = plan.Bc, r0 = plan.r0;
     const int n_cnt = P.max_iter + 3;
     const bool rounds = r0 > 0;
-    double *hdr = rounds ? h->bws.as<double>() : nullptr, *rec = rounds ? hdr + (size_t)B * kHdrD : nullptr;
-    int *list0 = rounds ? reinterpret_cast<int *>(rec + (size_t)B * (N + 1) * kStepD) : nullptr, *list1 = rounds ? list0 + B : nullptr;
     const double *ocv = h->obs_b.as<double>(), *oib2 = ocv ? ocv + (size_t)B * n_obs * CV_FIELDS : nullptr, *orec = h->obs.as<double>();
     const size_t trace_per_chunk = (size_t)n_cnt * kTraceKinds * 2;
     if (h->trace_on) CILQR_CUDA(cudaMemsetAsync(h->trace.p, 0xff, (size_t)kMaxChunks * trace_per_chunk * sizeof(unsigned long long), st));
@@ -769,12 +787,9 @@ static int issue_rounds(cilqr_handle h, const SolveArgs &A, const HostIO *io, cu
     for (int c = 0; c < K; ++c) {
         const int o = c * Bc, b = std::min(Bc, B - o);
         unsigned char *ctl = h->ctl.as<unsigned char>() + (size_t)c * ctl_stride(n_cnt);
-        BatchView v;
+        BatchView v{};
         v.N = N;
-        v.hdr = rounds ? hdr + (size_t)o * kHdrD : nullptr;
-        v.rec = rounds ? rec + (size_t)o * (N + 1) * kStepD : nullptr;
-        v.list0 = rounds ? list0 + o : nullptr;
-        v.list1 = rounds ? list1 + o : nullptr;
+        if (rounds) v = rounds_view(h->bws.p, B, N, o);
         v.cnt = reinterpret_cast<int *>(ctl);
         v.n_obs = n_obs;
         v.cv = h->obs_cv;
@@ -957,8 +972,7 @@ static int solve_rounds(cilqr_handle h, const SolveArgs &A, const HostIO *io, cu
         plan.fused_grid = std::max(1, std::min((std::min(plan.Bc, B) + G - 1) / G, h->num_sms * occ));
     }
     if (plan.r0 > 0) {
-        const size_t n_dbl = (size_t)B * kHdrD + (size_t)B * (N + 1) * kStepD;
-        if (int rc = h->bws.reserve(n_dbl * sizeof(double) + (size_t)2 * B * sizeof(int))) return rc;
+        if (int rc = h->bws.reserve(rounds_ws_bytes(B, N))) return rc;
     }
     if (int rc = h->ctl.reserve((size_t)kMaxChunks * ctl_stride(n_cnt))) return rc;
     if (h->trace_on)
@@ -1016,19 +1030,13 @@ static int solve_rounds_ls(cilqr_handle h, const SolveArgs &A, cudaStream_t st)
     const DevParams &P = h->dp;
     const int N = P.N, B = A.B, n_obs = h->cur_nobs, na = A.n_alphas;
     const int n_cnt = P.max_iter + 3;
-    const size_t n_dbl = (size_t)B * kHdrD + (size_t)B * (N + 1) * kStepD;
-    if (int rc = h->bws.reserve(n_dbl * sizeof(double) + (size_t)2 * B * sizeof(int))) return rc;
+    if (int rc = h->bws.reserve(rounds_ws_bytes(B, N))) return rc;
     if (int rc = h->ctl.reserve((size_t)kMaxChunks * ctl_stride(n_cnt))) return rc;
     const size_t n_cand = (size_t)B * na * (N + 1) * kCandD, n_merit = (size_t)B * na * N;
     if (int rc = h->scratch.reserve((n_cand + n_merit) * sizeof(double) + ((size_t)B + n_cnt) * sizeof(int))) return rc;
     if (h->trace_on)
         if (int rc = h->trace.reserve((size_t)kMaxChunks * n_cnt * kTraceKinds * 2 * sizeof(unsigned long long))) return rc;
-    BatchView v;
-    v.N = N;
-    v.hdr = h->bws.as<double>();
-    v.rec = v.hdr + (size_t)B * kHdrD;
-    v.list0 = reinterpret_cast<int *>(v.rec + (size_t)B * (N + 1) * kStepD);
-    v.list1 = v.list0 + B;
+    BatchView v = rounds_view(h->bws.p, B, N, 0);
     v.cnt = h->ctl.as<int>();
     v.n_obs = n_obs;
     v.cv = h->obs_cv;
