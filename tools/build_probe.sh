@@ -4,8 +4,9 @@
 set -e
 cd "$(dirname "$0")/.."
 P=uncertainty-aware-cilqr-for-trajectory-optimization_b200
+OUT=${CILQR_PROBE_OUT:-build/libcilqr_probe.so}
 CILQR_NVCC_EXTRA="-DCILQR_PROBE_ENV $*" python $P/build.py --force > /dev/null
 mkdir -p build
-cp $P/libcilqr_b200.so build/libcilqr_probe.so
+cp $P/libcilqr_b200.so $OUT
 python $P/build.py --force > /dev/null
-ls -la build/libcilqr_probe.so $P/libcilqr_b200.so
+ls -la $OUT $P/libcilqr_b200.so

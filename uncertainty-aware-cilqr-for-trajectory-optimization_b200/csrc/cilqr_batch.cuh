@@ -646,13 +646,6 @@ __global__ void __launch_bounds__(kDerivThreads, 2) batch_derivs_kernel(DevParam
 }
 
 // ------------------------------------------------------------------------------------------------- Riccati sweep + rollout
-// A prefetch brings one 32-byte sector: a step record (144 bytes, 16-byte aligned) lies in the five sectors touched here.
-__device__ __forceinline__ void prefetch_step(const double *r)
-{
-#pragma unroll
-    for (int k = 0; k < 5; ++k)
-        prefetch_l2(r + 4 * k);
-}
 
 // ---- Riccati sweep + rollout: one scenario per lane, one warp per CTA.
 //
