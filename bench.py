@@ -122,6 +122,13 @@ def solver_flops(N, n_obs, cost_passes, deriv_passes):
     return cost_passes * per_cost + deriv_passes * per_deriv, per_cost, per_deriv
 
 
+def propagation_flops(N, n_obs):
+    """Covariance-inflated obstacle set of one scenario (cilqr_set_obstacles_cv; square root and division counted once each):
+    per obstacle a sincos and the longitudinal axis (20 + 12), per (obstacle, timestep) the lever arm, the lateral sigma and
+    1/b^2 (19)."""
+    return n_obs * (32 + N * 19)
+
+
 # ------------------------------------------------------------------------------------------------ clocks during the timed region
 class ClockSampler:
     """nvidia-smi sampler (B200_PROFILING.md's clocks line).  Started before the warm-up — nvidia-smi needs a second or two to
@@ -361,11 +368,11 @@ def solve_case(args, p, device, rank, world, first_id, B, n_obs, n_alphas, steps
         cur = torch.cuda.current_stream()
         if do_gather:
             cur.wait_event(gathered_ev[i % 2])  # the gather that read this buffer two steps ago has finished
-        solver.set_obstacles_cv(d["obs_state0"], d["obs_LW"], d["obs_sigma"], sc["kappa"])  # covariance propagation on device
         Ub.copy_(d["U0"])
-        if timed:
-            ev = event_pair()
+        if timed:  # kernel_ms: the library's device work of the step — covariance propagation (its per-timestep half runs as the
+            ev = event_pair()  # first kernel of the solve) and the solve
             ev[0].record()
+        solver.set_obstacles_cv(d["obs_state0"], d["obs_LW"], d["obs_sigma"], sc["kappa"])  # covariance propagation on device
         solver.get_optimal_control_seq(d["x0"], Ub, d["poly"], d["xlp"], n_alphas=n_alphas, merit=merit, outputs=res)
         if timed:
             ev[1].record()
@@ -425,12 +432,15 @@ def solve_case(args, p, device, rank, world, first_id, B, n_obs, n_alphas, steps
 
 def fp64_block(lib, N, n_obs, B, stats, kernel_ms):
     flops_launch, per_cost, per_deriv = solver_flops(N, n_obs, stats[0], stats[1])
+    flops_launch += B * propagation_flops(N, n_obs)
     peak = fp64_peak(lib)
     tf = flops_launch / (kernel_ms * 1e-3) / 1e12
     return {"bound": "fp64", "achieved": tf, "peak": peak, "unit": "TFLOP/s", "frac": tf / peak if peak else None,
             "peak_source": "builder-measured: DFMA micro-benchmark on this GPU (cilqr_measure_fp64_peak); MEASURED_PEAKS.json has no FP64 figure",
             "flops_per_cost_pass": per_cost, "flops_per_derivative_pass": per_deriv, "cost_passes_per_solve": stats[0] / B,
             "derivative_passes_per_solve": stats[1] / B, "rounds": stats[2], "kernel_ms": kernel_ms,
+            "flops_covariance_propagation_per_solve": propagation_flops(N, n_obs),
+            "covers": "cilqr_set_obstacles_cv + cilqr_solve_batch (every kernel of the step)",
             "counting": "each operation once, exp / sincos = 20 flops (DESIGN.md section 5)"}
 
 
@@ -765,9 +775,9 @@ def run_b200_arm(args):
     bytes_launch = B * solver_bytes_per_solve(N, n_obs)
     achieved = bytes_launch / (kernel_ms * 1e-3) / 1e9
     roof = fp64_block(lib, N, n_obs, B, stats, kernel_ms)
-    roof["kernel"] = ("cilqr_solve_batch: one 'launch' = one solve of the batch (fused_solve_kernel for batches up to 16 384 scenarios; batch_init + "
-                      "<= %d rounds of batch_cost / batch_derivs / batch_sweep + batch_output for larger ones; batch_derivs_kernel dominates, "
-                      "see profiles/)" % (p.max_iterations + 1))
+    roof["kernel"] = ("cilqr_set_obstacles_cv + cilqr_solve_batch: one 'launch' = one step of the batch (obstacle prep, then fused_solve_kernel for "
+                      "batches up to 16 384 scenarios; batch_init + <= %d rounds of batch_cost / batch_derivs / batch_sweep + batch_output for "
+                      "larger ones; batch_derivs_kernel dominates, see profiles/)" % (p.max_iterations + 1))
     roof["traffic"] = recorded_traffic("solver_dram_bytes_per_step")
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -778,7 +788,7 @@ def run_b200_arm(args):
                    "l2": "%s (%.2f GB of obstacle data re-generated every step + %.2f GB of solver state)"
                          % ("working set larger than L2" if B * (n_obs * 8 * (8 + N) + (18 + 18 * (N + 1)) * 8) > 126e6 else
                             "working set L2-resident: a parity-size configuration, not the headline", B * n_obs * 8 * (8 + N) / 1e9,
-                            B * (18 + 18 * (N + 1)) * 8 / 1e9),
+                            B * (18 + 8 * (N + 1) + 14 * N) * 8 / 1e9),
                    "collective": ("none" if world == 1 else "all-gather of U* by peer-to-peer copies on the copy engines (cilqr_gather_copy) + a one-element NCCL all-reduce "
                                   "as the barrier, on its own stream under the next step's solve" if args.gather == "peer" else
                                   "all_gather U* (NCCL), on its own stream under the next step's solve")},

@@ -160,6 +160,8 @@ int cilqr_set_obstacles(cilqr_handle h, int B, int n_obs, const double *dim, con
  * (lever-arm covariance propagation of map_engine/include/ARBIT.cuh:58-68, kappa = 2.4477 at
  * ARBIT.cuh:87).
  *   state0 [B][n_obs][4] (x0, y0, v, theta);  LW [B][n_obs][2];  sigma [B][n_obs][3] (sx, sy, sth)
+ * The arrays are consumed by this call (stream-ordered for device memory).  The per-timestep half of the expansion (the lateral
+ * axis of every ellipse) is run by the first call that uses the obstacle set, on that call's stream, as its first kernel.
  */
 int cilqr_set_obstacles_cv(cilqr_handle h, int B, int n_obs, const double *state0, const double *LW,
                            const double *sigma, double kappa, int mem, void *stream);

@@ -168,9 +168,12 @@ __global__ void __launch_bounds__(256) prep_obstacles_dense_kernel(DevParams P, 
 // Constant-velocity obstacles with covariance-inflated size (ARBIT.cuh:58-68, :87): per obstacle the
 // constants of the prediction, per timestep only 1/b^2 (the lateral sigma grows with the lever arm v t).
 // Two passes so that sincos runs once per obstacle, not once per (obstacle, t).
+// `aux` (may be null): [obstacle][4] = (width, sigma_y, sigma_theta, -), what the 1/b^2 pass needs of the caller's arrays — the
+// handle runs that pass later, beside the first kernels of the solve (cilqr_solver.cu: launch_ib2), when the caller's arrays may
+// have changed.
 __global__ void __launch_bounds__(256) prep_obstacles_cv_kernel(DevParams P, size_t n_bj, const double *__restrict__ state0,
                                                                 const double *__restrict__ LW, const double *__restrict__ sigma, double kappa,
-                                                                double *__restrict__ ocv)
+                                                                double *__restrict__ ocv, double *__restrict__ aux)
 {
     for (size_t bj = blockIdx.x * (size_t)blockDim.x + threadIdx.x; bj < n_bj; bj += (size_t)gridDim.x * blockDim.x) {
         const double v = state0[4 * bj + 2], th = state0[4 * bj + 3];
@@ -187,11 +190,16 @@ __global__ void __launch_bounds__(256) prep_obstacles_cv_kernel(DevParams P, siz
         o[CV_S] = s;
         o[CV_IA2] = 1.0 / a / a; // Obstacle.cpp:45
         o[CV_V] = v;
+        if (aux) {
+            st2(aux + 4 * bj, LW[2 * bj + 1], sigma[3 * bj + 1]);
+            st2(aux + 4 * bj + 2, sigma[3 * bj + 2], 0.0);
+        }
     }
 }
-__global__ void __launch_bounds__(256) prep_obstacles_cv_ib2_kernel(DevParams P, size_t n_bj, const double *__restrict__ LW,
-                                                                    const double *__restrict__ sigma, double kappa, const double *__restrict__ ocv,
-                                                                    double *__restrict__ oib2)
+// width[obstacle * w_stride], (sigma_y, sigma_theta) = sg[obstacle * sg_stride + 0 / 1]: the caller's LW / sigma arrays or `aux`.
+__global__ void __launch_bounds__(256) prep_obstacles_cv_ib2_kernel(DevParams P, size_t n_bj, const double *__restrict__ width, int w_stride,
+                                                                    const double *__restrict__ sg, int sg_stride, double kappa,
+                                                                    const double *__restrict__ ocv, double *__restrict__ oib2)
 {
     const int N = P.N;
     const size_t total = n_bj * N;
@@ -199,9 +207,9 @@ __global__ void __launch_bounds__(256) prep_obstacles_cv_ib2_kernel(DevParams P,
         const size_t bj = i / N;
         const int t = (int)(i - bj * N);
         const double *o = ocv + bj * CV_FIELDS;
-        const double sy = sigma[3 * bj + 1], sth = sigma[3 * bj + 2];
+        const double sy = sg[bj * sg_stride], sth = sg[bj * sg_stride + 1];
         const double arm = o[CV_V] * (t * P.dt);
-        const double dim1 = LW[2 * bj + 1] + 2.0 * kappa * sqrt(sy * sy + sth * sth * arm * arm);
+        const double dim1 = width[bj * w_stride] + 2.0 * kappa * sqrt(sy * sy + sth * sth * arm * arm);
         const double b = dim1 / 2.0 + fabs(o[CV_VS]) * P.t_safe + P.s_safe_b + P.ego_rad + 1.0; // Obstacle.cpp:43 (hard-coded +1)
         oib2[i] = 1.0 / b / b;                                                                  // Obstacle.cpp:46
     }

@@ -261,6 +261,8 @@ struct cilqr_solver {
     bool obs_ready = false;
     DevBuf obs_b;                // compact constant-velocity obstacles (cilqr_batch.cuh)
     int obs_cv = 0;              // obs_b holds the compact constant-velocity form
+    bool ib2_pending = false;    // the 1/b^2 table of obs_b has not been filled yet (launch_ib2)
+    double ib2_kappa = 0.0;
     DevBuf bws;                  // state of the batch-synchronous rounds (headers, step records, work lists)
     DevBuf ctl;                  // per chunk: work-list lengths, the fused kernel's scenario counter and pass tallies
     int last_chunks = 0;         // chunks of the last n_alphas == 1 solve (0: none yet)
@@ -626,9 +628,28 @@ int cilqr_set_option(cilqr_handle h, int option, int value)
 static int prep_grid(size_t total, int num_sms) { return (int)std::min<size_t>((total + 255) / 256, (size_t)num_sms * 8); }
 // The fused kernels and the stage entry points read [scenario][obstacle][field][t] records: expanded from the compact
 // constant-velocity form when first needed.
+// 1/b^2 of every (obstacle, timestep) of the compact constant-velocity form (see cilqr_set_obstacles_cv), at most once per
+// obstacle set; `ctas_per_sm` bounds the grid.
+static int launch_ib2(cilqr_handle h, cudaStream_t st, int ctas_per_sm)
+{
+    const size_t n_bj = (size_t)h->cur_B * h->cur_nobs, N = h->dp.N;
+    double *ocv = h->obs_b.as<double>(), *oib2 = ocv + n_bj * CV_FIELDS, *aux = oib2 + n_bj * N;
+    const int grid = (int)std::min<size_t>((n_bj * N + 255) / 256, (size_t)h->num_sms * ctas_per_sm);
+    prep_obstacles_cv_ib2_kernel<<<grid, 256, 0, st>>>(h->dp, n_bj, aux, 4, aux + 1, 4, h->ib2_kappa, ocv, oib2);
+    CILQR_LAUNCH_CHECK();
+    h->ib2_pending = false;
+    return 0;
+}
+static int ensure_ib2(cilqr_handle h, cudaStream_t st)
+{
+    if (!h->ib2_pending || !h->obs_cv || h->cur_nobs == 0 || h->cur_B == 0) return 0;
+    return launch_ib2(h, st, 8);
+}
+
 static int ensure_records(cilqr_handle h, cudaStream_t st)
 {
     if (h->obs_ready || h->cur_nobs == 0 || h->cur_B == 0) return 0;
+    if (int rc = ensure_ib2(h, st)) return rc;
     const size_t n_bj = (size_t)h->cur_B * h->cur_nobs, N = h->dp.N;
     if (int rc = h->obs.reserve(n_bj * OB_FIELDS * N * sizeof(double))) return rc;
     const double *ocv = h->obs_b.as<double>();
@@ -656,6 +677,7 @@ int cilqr_set_obstacles(cilqr_handle h, int B, int n_obs, const double *dim, con
     prep_obstacles_dense_kernel<<<prep_grid(n_bj * N, h->num_sms), 256, 0, st>>>(h->dp, n_bj, d_dim, d_pos, h->obs.as<double>());
     CILQR_LAUNCH_CHECK();
     h->obs_cv = 0;
+    h->ib2_pending = false;
     h->obs_ready = true;
     if (mem == CILQR_MEM_HOST) CILQR_CUDA(cudaStreamSynchronize(st));
     return 0;
@@ -678,15 +700,18 @@ int cilqr_set_obstacles_cv(cilqr_handle h, int B, int n_obs, const double *state
     if (int rc = stage_in(h, 1, LW, n_bj * 2, mem, st, &d_lw)) return rc;
     if (int rc = stage_in(h, 2, sigma, n_bj * 3, mem, st, &d_sg)) return rc;
     if (mem == CILQR_MEM_HOST) CILQR_CUDA(cudaEventRecord(h->ev_copied, st));
-    if (int rc = h->obs_b.reserve(n_bj * (CV_FIELDS + N) * sizeof(double))) return rc;
-    double *ocv = h->obs_b.as<double>(), *oib2 = ocv + n_bj * CV_FIELDS;
-    prep_obstacles_cv_kernel<<<prep_grid(n_bj, h->num_sms), 256, 0, st>>>(h->dp, n_bj, d_s, d_lw, d_sg, kappa, ocv);
+    if (int rc = h->obs_b.reserve(n_bj * (CV_FIELDS + N + 4) * sizeof(double))) return rc;
+    double *ocv = h->obs_b.as<double>(), *aux = ocv + n_bj * (CV_FIELDS + N);
+    prep_obstacles_cv_kernel<<<prep_grid(n_bj, h->num_sms), 256, 0, st>>>(h->dp, n_bj, d_s, d_lw, d_sg, kappa, ocv, aux);
     CILQR_LAUNCH_CHECK();
-    prep_obstacles_cv_ib2_kernel<<<prep_grid(n_bj * N, h->num_sms), 256, 0, st>>>(h->dp, n_bj, d_lw, d_sg, kappa, ocv, oib2);
-    CILQR_LAUNCH_CHECK();
+    // The per-(obstacle, timestep) 1/b^2 table (the expensive part: a square root and two divisions per entry) is filled by the
+    // first consumer, on its stream: a solve runs it as its first kernel — inside the recorded graph, and inside the compute token
+    // when several handles share the GPU (end to end with four host threads: 11.2 -> 11.8 M solves/s).
+    h->ib2_pending = true;
+    h->ib2_kappa = kappa;
     h->obs_cv = 1;
     h->obs_ready = false;
-    // host arrays: the caller may reuse them once they have been copied; the two kernels stay in flight on `stream`
+    // host arrays: the caller may reuse them once they have been copied; the kernel stays in flight on `stream`
     if (mem == CILQR_MEM_HOST) CILQR_CUDA(cudaEventSynchronize(h->ev_copied));
     return 0;
 }
@@ -723,6 +748,7 @@ struct HostIO { // caller's host arrays (CILQR_MEM_HOST) — null members when t
 struct SolvePlan {
     int K, Bc, r0, G, fused_grid;
     size_t fused_smem;
+    bool prep; // the obstacle set's 1/b^2 table is still to be filled (launch_ib2): this solve does it
 };
 
 static int launch_fused(cilqr_handle h, const FusedArgs &F, int work, const SolvePlan &plan, cudaStream_t st)
@@ -766,6 +792,11 @@ static int issue_rounds(cilqr_handle h, const SolveArgs &A, const HostIO *io, cu
     const double *ocv = h->obs_b.as<double>(), *oib2 = ocv ? ocv + (size_t)B * n_obs * CV_FIELDS : nullptr, *orec = h->obs.as<double>();
     const size_t trace_per_chunk = (size_t)n_cnt * kTraceKinds * 2;
     if (h->trace_on) CILQR_CUDA(cudaMemsetAsync(h->trace.p, 0xff, (size_t)kMaxChunks * trace_per_chunk * sizeof(unsigned long long), st));
+    // The 1/b^2 table, if this obstacle set does not have it yet: ahead of the solve's kernels, inside the recorded graph and
+    // inside the compute token.  (Run on its own stream beside the set-up kernel and the first cost pass it gains nothing:
+    // 5.25 ms per step either way with a full grid, 5.38 / 5.76 with half / a quarter of the SMs' slots — it needs the machine.)
+    if (plan.prep)
+        if (int rc = launch_ib2(h, st, 8)) return rc;
     cudaStream_t cs[kMaxChunks];
     if (K == 1) {
         cs[0] = st;
@@ -979,8 +1010,9 @@ static int solve_rounds(cilqr_handle h, const SolveArgs &A, const HostIO *io, cu
         if (int rc = h->trace.reserve((size_t)kMaxChunks * n_cnt * kTraceKinds * 2 * sizeof(unsigned long long))) return rc;
     h->last_chunks = K;
     h->last_r0 = plan.r0;
+    plan.prep = h->ib2_pending && h->obs_cv && h->cur_nobs > 0 && B > 0;
 
-    std::vector<uintptr_t> key = {(uintptr_t)B, (uintptr_t)h->cur_nobs, (uintptr_t)h->obs_cv, (uintptr_t)K, (uintptr_t)plan.r0, (uintptr_t)plan.G,
+    std::vector<uintptr_t> key = {(uintptr_t)B, (uintptr_t)h->cur_nobs, (uintptr_t)(h->obs_cv | (plan.prep ? 2 : 0)), (uintptr_t)K, (uintptr_t)plan.r0, (uintptr_t)plan.G,
                                   (uintptr_t)h->bws.p, (uintptr_t)h->ctl.p, (uintptr_t)h->obs_b.p, (uintptr_t)h->obs.p, (uintptr_t)h->trace.p,
                                   (uintptr_t)A.x0, (uintptr_t)A.U, (uintptr_t)A.poly, (uintptr_t)A.xlp, (uintptr_t)A.X, (uintptr_t)A.J,
                                   (uintptr_t)A.iters, (uintptr_t)A.status};
@@ -1009,6 +1041,7 @@ static int solve_rounds(cilqr_handle h, const SolveArgs &A, const HostIO *io, cu
             cudaEvent_t &tail = g_token_tail[h->device < kTokenDevices ? h->device : kTokenDevices - 1];
             if (tail && tail != h->ev_kdone) CILQR_CUDA(cudaStreamWaitEvent(st, tail, 0)); // behind the previous holder's kernels
             if (int rc = run_plan(h, A, nullptr, st, plan, kkey)) return rc;
+            if (plan.prep) h->ib2_pending = false; // (filled by the launches, or by the replayed graph that was recorded with the pass in it)
             CILQR_CUDA(cudaEventRecord(h->ev_kdone, st));
             tail = h->ev_kdone;
         }
@@ -1020,13 +1053,16 @@ static int solve_rounds(cilqr_handle h, const SolveArgs &A, const HostIO *io, cu
         if (io->status) CILQR_CUDA(cudaMemcpyAsync(io->status, A.status, sb * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
         return 0;
     }
-    return run_plan(h, A, io, st, plan, key);
+    if (int rc = run_plan(h, A, io, st, plan, key)) return rc;
+    if (plan.prep) h->ib2_pending = false; // (filled by the launches, or by the replayed graph that was recorded with the pass in it)
+    return 0;
 }
 
 // Line-search extension (n_alphas > 1) as rounds: cost (tracking gradient + list compaction) -> derivatives -> backward sweep ->
 // candidates (one lane per step length) -> merits (one thread per candidate step) -> select (one warp per scenario).
 static int solve_rounds_ls(cilqr_handle h, const SolveArgs &A, cudaStream_t st)
 {
+    if (int rc = ensure_ib2(h, st)) return rc;
     const DevParams &P = h->dp;
     const int N = P.N, B = A.B, n_obs = h->cur_nobs, na = A.n_alphas;
     const int n_cnt = P.max_iter + 3;
@@ -1124,6 +1160,7 @@ static int solve_rounds_ls(cilqr_handle h, const SolveArgs &A, cudaStream_t st)
 // L2-resident scratch (per CTA: G x n_alphas x (N + 1) x 64 B + G x n_alphas x N x 8 B).
 static int solve_fused_ls(cilqr_handle h, const SolveArgs &A, cudaStream_t st)
 {
+    if (int rc = ensure_ib2(h, st)) return rc;
     const DevParams &P = h->dp;
     const int N = P.N, B = A.B, na = A.n_alphas, n_cnt = P.max_iter + 3;
     int G = h->fused_slots > 0 ? std::min(h->fused_slots, h->fused_slots_max) : h->fused_slots_max;
@@ -1680,9 +1717,9 @@ int cilqr_solve_cv_static(cilqr_handle h, int B, int n_obs, const double *state0
     // the array keeps the last call's contents: the control block must start at zero; the obstacle records are rewritten whole
     CILQR_CUDA(cudaMemsetAsync(scratch, 0, kStaticCtlBytes, st));
     if (n_bj > 0) {
-        prep_obstacles_cv_kernel<<<prep_grid(n_bj, h->num_sms), 256, 0, st>>>(P, n_bj, state0, LW, sigma, kappa, ocv);
+        prep_obstacles_cv_kernel<<<prep_grid(n_bj, h->num_sms), 256, 0, st>>>(P, n_bj, state0, LW, sigma, kappa, ocv, nullptr);
         CILQR_LAUNCH_CHECK();
-        prep_obstacles_cv_ib2_kernel<<<prep_grid(n_bj * N, h->num_sms), 256, 0, st>>>(P, n_bj, LW, sigma, kappa, ocv, oib2);
+        prep_obstacles_cv_ib2_kernel<<<prep_grid(n_bj * N, h->num_sms), 256, 0, st>>>(P, n_bj, LW + 1, 2, sigma + 1, 3, kappa, ocv, oib2);
         CILQR_LAUNCH_CHECK();
     }
     FusedArgs F;
