@@ -524,6 +524,10 @@ __global__ void __launch_bounds__(kCostThreads) batch_cost_kernel(DevParams P, B
 // the current item is evaluated: n_obs x 8 bytes in flight per thread for the length of an item, no barrier needed (a thread
 // reads only what it copied itself).
 constexpr int kDerivThreads = 256;
+#ifndef CILQR_DERIV_UNROLL
+#define CILQR_DERIV_UNROLL 2
+#endif
+constexpr int kDerivUnroll = CILQR_DERIV_UNROLL; // obstacles evaluated side by side in the derivative kernel's loop
 __host__ __device__ inline size_t deriv_stage_bytes(int n_obs) { return (size_t)2 * n_obs * kDerivThreads * sizeof(double); }
 
 template <bool CV, bool STAGED = false>
@@ -606,7 +610,7 @@ __global__ void __launch_bounds__(kDerivThreads, 2) batch_derivs_kernel(DevParam
                 double2 n0 = ld2(oc), n1 = ld2(oc + 2), n2 = ld2(oc + 4), n3 = ld2(oc + 6);
                 const double *col = deriv_smem + (size_t)stage * n_obs * kDerivThreads + threadIdx.x;
                 double nib = STAGED ? col[0] : ld_stream(ob, stream_policy), nib2 = STAGED || n_obs < 2 ? 0.0 : ld_stream(ob + N, stream_policy);
-#pragma unroll 2
+#pragma unroll kDerivUnroll
                 for (int j = 0; j < n_obs; ++j) {
                     const double xo = n0.x + n1.x * tt, yo = n0.y + n1.y * tt; // cv_position
                     const double co = n2.x, so = n2.y, ia2 = n3.x, ib2 = nib;
@@ -690,7 +694,9 @@ __global__ void __launch_bounds__(kSweepThreads, 11) batch_sweep_kernel(DevParam
     const int lane = threadIdx.x;
     const uint32_t ring0 = (uint32_t)__cvta_generic_to_shared(&sm.ring[0][0][0]);
     constexpr uint32_t kSlotBytes = kSweepThreads * kStepUsed * 8;
-    const size_t st_stride16 = (size_t)(N + 1) * kStatePieces, dr_stride16 = (size_t)N * kGainPieces; // 16-byte pieces per scenario
+    // 16-byte pieces per scenario; piece indices are 32-bit (a chunk's state records stay below 2^32 pieces = 64 GB): one add
+    // and one widening multiply-add per address instead of 64-bit arithmetic in the warp's dependent instruction stream
+    const uint32_t st_stride16 = (uint32_t)(N + 1) * kStatePieces, dr_stride16 = (uint32_t)N * kGainPieces;
 
     for (int i0 = blockIdx.x * kSweepThreads; i0 < cnt; i0 += gridDim.x * kSweepThreads) {
         const int nact = min(kSweepThreads, cnt - i0);
@@ -701,20 +707,20 @@ __global__ void __launch_bounds__(kSweepThreads, 11) batch_sweep_kernel(DevParam
         const double2 *st16 = reinterpret_cast<const double2 *>(V.st), *dr16 = reinterpret_cast<const double2 *>(V.dr);
         // The warp moves the 32 records of a step together.  State records: piece p = k * 32 + lane belongs to the scenario of
         // lane p / 4 (piece p % 4); derivative / gain records: lane p / 5, piece p % 5.  Both land in the lane's ring row.
-        size_t s_off[kStatePieces], d_off[kGainPieces];
+        uint32_t s_off[kStatePieces], d_off[kGainPieces];
         uint32_t s_dst[kStatePieces], d_dst[kGainPieces]; // byte offsets inside a ring slot
         bool s_on[kStatePieces], d_on[kGainPieces];
 #pragma unroll
         for (int k = 0; k < kStatePieces; ++k) {
             const int p = k * kSweepThreads + lane, src = p / kStatePieces, f = p - src * kStatePieces;
-            s_off[k] = (size_t)__shfl_sync(0xffffffffu, b, src) * st_stride16 + f;
+            s_off[k] = (uint32_t)__shfl_sync(0xffffffffu, b, src) * st_stride16 + f;
             s_dst[k] = (uint32_t)(src * kRowPieces + f) * 16;
             s_on[k] = src < nact;
         }
 #pragma unroll
         for (int k = 0; k < kGainPieces; ++k) {
             const int p = k * kSweepThreads + lane, src = p / kGainPieces, f = p - src * kGainPieces;
-            d_off[k] = (size_t)__shfl_sync(0xffffffffu, b, src) * dr_stride16 + f;
+            d_off[k] = (uint32_t)__shfl_sync(0xffffffffu, b, src) * dr_stride16 + f;
             d_dst[k] = (uint32_t)(src * kRowPieces + kStatePieces + f) * 16;
             d_on[k] = src < nact;
         }
@@ -722,11 +728,11 @@ __global__ void __launch_bounds__(kSweepThreads, 11) batch_sweep_kernel(DevParam
 #pragma unroll
             for (int k = 0; k < kStatePieces; ++k)
                 if (s_on[k])
-                    cp_async16(ring0 + slot * kSlotBytes + s_dst[k], st16 + s_off[k] + (size_t)t * kStatePieces);
+                    cp_async16(ring0 + slot * kSlotBytes + s_dst[k], st16 + (s_off[k] + (uint32_t)t * kStatePieces));
 #pragma unroll
             for (int k = 0; k < kGainPieces; ++k)
                 if (d_on[k])
-                    cp_async16(ring0 + slot * kSlotBytes + d_dst[k], dr16 + d_off[k] + (size_t)t * kGainPieces);
+                    cp_async16(ring0 + slot * kSlotBytes + d_dst[k], dr16 + (d_off[k] + (uint32_t)t * kGainPieces));
         };
 
         // ---- iLQR::backward_pass (iLQR.cpp:91-195): gains overwrite the derivative records
@@ -737,7 +743,7 @@ __global__ void __launch_bounds__(kSweepThreads, 11) batch_sweep_kernel(DevParam
 #pragma unroll
             for (int k = 0; k < kGainPieces; ++k)
                 if (d_on[k])
-                    g16[d_off[k] + (size_t)j * kGainPieces] = o[k * kSweepThreads + lane];
+                    g16[d_off[k] + (uint32_t)j * kGainPieces] = o[k * kSweepThreads + lane];
         };
         RiccatiState S;
         RiccatiIn I;
@@ -812,12 +818,12 @@ __global__ void __launch_bounds__(kSweepThreads, 11) batch_sweep_kernel(DevParam
         // Step t reads record t (old state column, control, gains) and produces U(:, t) and column t + 1; they are written one
         // step later, when record t + 1 — whose old column is still needed — is known to be in the ring.
         constexpr int kRollPieces = 4; // (u0, u1) -> state record t; (x, y), (v, theta), (cos, sin) -> state record t + 1
-        size_t ro_off[kRollPieces];
+        uint32_t ro_off[kRollPieces];
         bool ro_on[kRollPieces];
 #pragma unroll
         for (int k = 0; k < kRollPieces; ++k) {
             const int p = k * kSweepThreads + lane, src = p / kRollPieces, f = p - src * kRollPieces;
-            ro_off[k] = (size_t)__shfl_sync(0xffffffffu, b, src) * st_stride16 + (f == 0 ? S_U0 / 2 : kStatePieces + f - 1);
+            ro_off[k] = (uint32_t)__shfl_sync(0xffffffffu, b, src) * st_stride16 + (f == 0 ? S_U0 / 2 : kStatePieces + f - 1);
             ro_on[k] = (roll_mask >> src) & 1u;
         }
         auto flush_roll = [&](int t) {
@@ -826,7 +832,7 @@ __global__ void __launch_bounds__(kSweepThreads, 11) batch_sweep_kernel(DevParam
             for (int k = 0; k < kRollPieces; ++k) {
                 const int p = k * kSweepThreads + lane, src = p / kRollPieces, f = p - src * kRollPieces;
                 if (ro_on[k])
-                    g16[ro_off[k] + (size_t)t * kStatePieces] = *reinterpret_cast<const double2 *>(&sm.out[t & 1][src][2 * f]);
+                    g16[ro_off[k] + (uint32_t)t * kStatePieces] = *reinterpret_cast<const double2 *>(&sm.out[t & 1][src][2 * f]);
             }
         };
         slot = 0;
