@@ -643,6 +643,7 @@ __global__ void __launch_bounds__(kDerivThreads, 2) batch_derivs_kernel(DevParam
                 }
             }
         }
+        obstacle_sums_scale(g0, g1, h00, h01, h11);
         double lu0, lu1, luu0, luu1, bc;
         control_terms<true>(P, vv, uu.x, uu.y, lu0, lu1, luu0, luu1, bc);
         const double2 tr = ld2(trk), tr2 = ld2(trk + 2); // tracking part written by batch_cost_kernel
@@ -670,7 +671,10 @@ __global__ void __launch_bounds__(kDerivThreads, 2) batch_derivs_kernel(DevParam
 // staged in shared memory, written by the warp in 16-byte pieces.  Same probe: ~3300 cycles per step at 12 warps per SM, which
 // is the HBM rate for this traffic.
 constexpr int kSweepThreads = 32;
-constexpr int kRing = 3;                       // records in flight per lane
+#ifndef CILQR_SWEEP_RING
+#define CILQR_SWEEP_RING 3
+#endif
+constexpr int kRing = CILQR_SWEEP_RING;        // records in flight per lane
 constexpr int kStatePieces = kStateD / 2;      // 16-byte pieces of a state record
 constexpr int kGainPieces = kRec / 2;          // 16-byte pieces of a derivative / gain record
 constexpr int kRowPieces = kStepUsed / 2;      // pieces of a ring row: the state record, then the derivative record of the step

@@ -131,6 +131,7 @@ __device__ __forceinline__ void fused_derivs_item(const DevParams &P, const Fuse
             }
         }
     }
+    obstacle_sums_scale(g0, g1, h00, h01, h11);
     double lu0, lu1, luu0, luu1, bc;
     control_terms<true>(P, vv, uu.x, uu.y, lu0, lu1, luu0, luu1, bc);
     const double2 tr = ld2(r + S_R), tr2 = ld2(r + S_R + 2); // tracking part written by phase A
