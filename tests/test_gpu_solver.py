@@ -236,6 +236,61 @@ def test_covariance_inflated_obstacles_on_device_match_host_expansion(checker):
     s.close()
 
 
+def test_obstacle_set_is_complete_whoever_uses_it_first():
+    """cilqr_set_obstacles_cv leaves the per-timestep half of the expansion (the 1/b^2 table) to the first consumer of the
+    obstacle set.  Whatever that consumer is — round kernels, on-chip kernel, line search (both schedules), a stage entry point —
+    and even when the caller's device arrays are overwritten right after the call, the results are those of the dense form
+    built on the host from the same obstacles."""
+    import torch
+    p = cilqr_b200.Parameters()
+    cilqr_b200.load_library().cilqr_params_default(__import__("ctypes").byref(p))
+    p = p.replace(horizon=50)
+    B, n_obs = 97, 7
+    sc = scenarios.make_scenarios(p, 4242, B, n_obs, curved=True, dense=True)
+    dev = torch.device("cuda:0")
+    t = {k: torch.from_numpy(sc[k]).to(dev) for k in ("x0", "U0", "poly", "xlp", "obs_state0", "obs_LW", "obs_sigma", "dim", "pos")}
+
+    def cv_set(s):
+        st, lw, sg = t["obs_state0"].clone(), t["obs_LW"].clone(), t["obs_sigma"].clone()
+        s.set_obstacles_cv(st, lw, sg, sc["kappa"])
+        st.fill_(float("nan")); lw.fill_(float("nan")); sg.fill_(float("nan"))  # stream-ordered after the call: must not be seen
+
+    def solve(s, **kw):
+        U = t["U0"].clone()
+        s.get_optimal_control_seq(t["x0"], U, t["poly"], t["xlp"], **kw)
+        torch.cuda.synchronize()
+        return U.cpu().numpy(), s.J_result.cpu().numpy(), s.iterations.cpu().numpy()
+
+    ref = {}
+    for fused in (0, 1):  # the dense form on both schedules is the reference of this test
+        s = cilqr_b200.iLQR(p, max_batch=B, max_obs=n_obs, options={cilqr_b200.OPT_FUSED: fused})
+        s.set_obstacles_dense(t["dim"], t["pos"])
+        ref[1] = solve(s)
+        ref[8] = solve(s, n_alphas=8, merit=cilqr_b200.MERIT_TOTAL)
+        X = s.get_nominal_trajectory(t["x0"], t["U0"])
+        ref["lx"] = [a.cpu().numpy() for a in s.get_state_cost(X, t["poly"], t["xlp"])]
+        s.close()
+        for first in ("solve", "line_search", "stage", "solve_twice"):
+            s = cilqr_b200.iLQR(p, max_batch=B, max_obs=n_obs, options={cilqr_b200.OPT_FUSED: fused})
+            cv_set(s)
+            if first == "stage":
+                got = [a.cpu().numpy() for a in s.get_state_cost(X, t["poly"], t["xlp"])]
+                for a, b in zip(got, ref["lx"]):
+                    assert rel(a, b) < TOL, (fused, first)
+            elif first == "line_search":
+                got = solve(s, n_alphas=8, merit=cilqr_b200.MERIT_TOTAL)
+                assert np.array_equal(got[2], ref[8][2]) and rel(got[0], ref[8][0]) < TOL, (fused, first)
+            got = solve(s)
+            assert np.array_equal(got[2], ref[1][2]) and rel(got[0], ref[1][0]) < TOL and rel(got[1], ref[1][1]) < TOL, (fused, first)
+            if first == "solve_twice":  # the same obstacle set again (no pending pass), then a fresh set on the same handle
+                again = solve(s)
+                assert all(np.array_equal(a, b) for a, b in zip(got, again))
+                cv_set(s)
+                again = solve(s)
+                assert all(np.array_equal(a, b) for a, b in zip(got, again))
+            s.close()
+
+
 def test_warm_start_is_carried_unshifted_like_the_reference(checker):
     """run_step twice: the second solve starts from the first one's U (iLQR.cpp:201,222,253)."""
     p = checker.params_default(horizon=50)
