@@ -73,6 +73,7 @@ def parse_args():
     ap.add_argument("--fused-slots", type=int, default=0, help="CILQR_OPT_FUSED_SLOTS (0 automatic)")
     ap.add_argument("--gather", default="peer", choices=["peer", "nccl"], help="the U* exchange at N > 1: peer-to-peer copies on the copy engines "
                                                                                  "(cilqr_gather_copy) or NCCL's all-gather kernel")
+    ap.add_argument("--chunks", type=int, default=0, help="CILQR_OPT_CHUNKS (0 automatic: one chunk for device buffers)")
     ap.add_argument("--no-graph", action="store_true", help="CILQR_OPT_GRAPH = 0: direct launches (for ncu launch lists)")
     return ap.parse_args()
 
@@ -742,7 +743,7 @@ def run_b200_arm(args):
     N, B, n_obs = HORIZON, args.batch, args.n_obs
     hbm_peak, peak_kind = measured_peaks()
     opts = {cilqr_b200.OPT_FUSED: args.fused, cilqr_b200.OPT_FUSED_SLOTS: args.fused_slots,
-            cilqr_b200.OPT_GRAPH: 0 if args.no_graph else 1}
+            cilqr_b200.OPT_GRAPH: 0 if args.no_graph else 1, cilqr_b200.OPT_CHUNKS: args.chunks}
 
     # ---- the headline: every rank solves its own B scenarios (ids rank*B ...), weak scaling
     main = solve_case(args, p, device, rank, world, rank * B, B, n_obs, args.n_alphas, args.steps, args.warmup, opts, True, sampler)
