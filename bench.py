@@ -642,7 +642,7 @@ def bench_e2e(args, p, device, world, sc, U_dev, opts, n_obs):
     d2h_u = 8 * B * (2 * N + 1) + 4 * B * 2
     merit = cilqr_b200.MERIT_TRACKING
     n_thr = max(1, args.e2e_threads)
-    ksteps = max(n_thr, min(args.steps, 48))
+    ksteps = max(n_thr, min(args.steps, 48 if world == 1 else 24))  # (every step has its own 52 MB pinned in/out buffer on every rank)
     each = max(1, (ksteps + n_thr - 1) // n_thr)
 
     class Worker:
