@@ -1003,6 +1003,9 @@ static int solve_rounds(cilqr_handle h, const SolveArgs &A, const HostIO *io, cu
         plan.fused_grid = std::max(1, std::min((std::min(plan.Bc, B) + G - 1) / G, h->num_sms * occ));
     }
     if (plan.r0 > 0) {
+        // (the sweep kernel addresses a chunk's state records with 32-bit indices of 16-byte pieces)
+        if ((size_t)plan.Bc * (N + 1) * (kStateD / 2) >= ((size_t)1 << 32))
+            return fail(CILQR_E_ARG, "%d scenarios x %d steps per chunk exceed the round kernels' 64 GB of state records", plan.Bc, N + 1);
         if (int rc = h->bws.reserve(rounds_ws_bytes(B, N))) return rc;
     }
     if (int rc = h->ctl.reserve((size_t)kMaxChunks * ctl_stride(n_cnt))) return rc;
@@ -1066,6 +1069,8 @@ static int solve_rounds_ls(cilqr_handle h, const SolveArgs &A, cudaStream_t st)
     const DevParams &P = h->dp;
     const int N = P.N, B = A.B, n_obs = h->cur_nobs, na = A.n_alphas;
     const int n_cnt = P.max_iter + 3;
+    if ((size_t)B * (N + 1) * (kStateD / 2) >= ((size_t)1 << 32))
+        return fail(CILQR_E_ARG, "%d scenarios x %d steps exceed the round kernels' 64 GB of state records", B, N + 1);
     if (int rc = h->bws.reserve(rounds_ws_bytes(B, N))) return rc;
     if (int rc = h->ctl.reserve((size_t)kMaxChunks * ctl_stride(n_cnt))) return rc;
     const size_t n_cand = (size_t)B * na * (N + 1) * kCandD, n_merit = (size_t)B * na * N;
