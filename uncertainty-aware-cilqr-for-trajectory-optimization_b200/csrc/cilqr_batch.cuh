@@ -603,6 +603,7 @@ __global__ void __launch_bounds__(kDerivThreads, 2) batch_derivs_kernel(DevParam
             cp_async_wait<1>(); // this item's column has landed; the next item's stays in flight
         }
         double g0 = 0, g1 = 0, h00 = 0, h01 = 0, h11 = 0, bo = 0;
+        const EgoCircles ego = ego_circles(P, x, y, ce, se);
         if (n_obs > 0) {
             if (CV) {
                 const double tt = t * P.dt;
@@ -628,7 +629,7 @@ __global__ void __launch_bounds__(kDerivThreads, 2) batch_derivs_kernel(DevParam
                     }
                     if (!STAGED && j + 2 < n_obs)
                         nib2 = ld_stream(ob + (size_t)(j + 2) * N, stream_policy);
-                    obstacle_terms<true>(P, x, y, ce, se, xo, yo, co, so, ia2, ib2, g0, g1, h00, h01, h11, bo);
+                    obstacle_terms<true>(P, ego, xo, yo, co, so, ia2, ib2, g0, g1, h00, h01, h11, bo);
                 }
             } else {
                 const double *o = V.orec + (size_t)b * n_obs * OB_FIELDS * N + t;
@@ -639,7 +640,7 @@ __global__ void __launch_bounds__(kDerivThreads, 2) batch_derivs_kernel(DevParam
                     const double xo = nx[OB_X], yo = nx[OB_Y], co = nx[OB_C], so = nx[OB_S], ia2 = nx[OB_IA2], ib2 = nx[OB_IB2];
                     if (j + 1 < n_obs)
                         load_record(o + (size_t)(j + 1) * OB_FIELDS * N, N, nx);
-                    obstacle_terms<true>(P, x, y, ce, se, xo, yo, co, so, ia2, ib2, g0, g1, h00, h01, h11, bo);
+                    obstacle_terms<true>(P, ego, xo, yo, co, so, ia2, ib2, g0, g1, h00, h01, h11, bo);
                 }
             }
         }

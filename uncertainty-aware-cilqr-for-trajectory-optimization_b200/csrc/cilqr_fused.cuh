@@ -99,6 +99,7 @@ __device__ __forceinline__ void fused_derivs_item(const DevParams &P, const Fuse
     const double2 xy = ld2(r + S_X), cs = ld2(r + S_C), uu = ld2(r + S_U0);
     const double x = xy.x, y = xy.y, ce = cs.x, se = cs.y, vv = r[S_V];
     double g0 = 0, g1 = 0, h00 = 0, h01 = 0, h11 = 0, bo = 0;
+    const EgoCircles ego = ego_circles(P, x, y, ce, se);
     if (n_obs > 0) {
         if (CV) {
             const double tt = t * P.dt;
@@ -116,7 +117,7 @@ __device__ __forceinline__ void fused_derivs_item(const DevParams &P, const Fuse
                 }
                 if (j + 2 < n_obs)
                     nib2 = ld_stream(ob + (size_t)(j + 2) * N, stream_policy);
-                obstacle_terms<true>(P, x, y, ce, se, xo, yo, co, so, ia2, ib2, g0, g1, h00, h01, h11, bo);
+                obstacle_terms<true>(P, ego, xo, yo, co, so, ia2, ib2, g0, g1, h00, h01, h11, bo);
             }
         } else {
             const double *o = A.orec + (size_t)b * n_obs * OB_FIELDS * N + t;
@@ -127,7 +128,7 @@ __device__ __forceinline__ void fused_derivs_item(const DevParams &P, const Fuse
                 const double xo = nx[OB_X], yo = nx[OB_Y], co = nx[OB_C], so = nx[OB_S], ia2 = nx[OB_IA2], ib2 = nx[OB_IB2];
                 if (j + 1 < n_obs)
                     load_record(o + (size_t)(j + 1) * OB_FIELDS * N, N, nx);
-                obstacle_terms<true>(P, x, y, ce, se, xo, yo, co, so, ia2, ib2, g0, g1, h00, h01, h11, bo);
+                obstacle_terms<true>(P, ego, xo, yo, co, so, ia2, ib2, g0, g1, h00, h01, h11, bo);
             }
         }
     }
