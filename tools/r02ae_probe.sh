@@ -1,4 +1,6 @@
 #!/bin/bash
+# NOTE: probe of an experiment that was reverted (tail split, bench flag --no-tail-split, option CILQR_OPT_TAIL_SPLIT): kept as the
+# record of how profiles/r02ae_* were taken; it does not run against the current tree.
 # tail split: parity, timing, timeline
 set -u
 mkdir -p gpurun_out

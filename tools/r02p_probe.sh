@@ -1,4 +1,6 @@
 #!/bin/bash
+# NOTE: probe of an experiment that was reverted (merged cost + derivative kernel, bench flag --split-eval): kept as the record of
+# how profiles/r02p_* were taken; it does not run against the current tree.
 # merged cost+derivative kernel (batch_eval_kernel): parity first, then A/B against the two-kernel rounds
 set -u
 mkdir -p gpurun_out
